@@ -1,0 +1,99 @@
+/* vcn_b200.h - C ABI of libvcn_b200.so: B200 (sm_100a) kernels for the StyleGAN2-ADA synthesis
+ * hot path of VisCoIN-Next.
+ *
+ * Drop-in boundary.  The reference binds its two CUDA plugins through pybind11 torch extensions
+ * (stylegan2_ada/torch_utils/ops/bias_act.cpp:32,94-97 and upfirdn2d.cpp:16,98-101) and calls
+ * ATen/cuDNN for the convolution (conv2d_gradfix.py:38,43).  This library replaces all three with
+ * plain-C entry points: raw device pointers, sizes, a dtype code and the CUDA stream; no torch
+ * types.  The caller allocates every output and workspace (reference: bias_act.cpp:55 and
+ * upfirdn2d.cpp:35 allocate inside C++); a NULL pointer means "absent" (reference: empty tensor,
+ * bias_act.py:39).  Every function returns 0 on success and a non-zero vcn_status otherwise, with
+ * a thread-local message in vcn_last_error() (reference: TORCH_CHECK exceptions).  Launches are
+ * asynchronous on the stream given; nothing here synchronises the device or allocates device
+ * memory.  There is no CPU fallback.
+ */
+#ifndef VCN_B200_H_
+#define VCN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VCN_ABI_VERSION 1
+
+typedef enum {
+  VCN_OK = 0,
+  VCN_ERR_INVALID = 1,      /* bad argument (shape, dtype, alignment, NULL) */
+  VCN_ERR_UNSUPPORTED = 2,  /* valid request this build has no kernel for */
+  VCN_ERR_CUDA = 3,         /* CUDA runtime / driver error, text in vcn_last_error() */
+  VCN_ERR_DEVICE = 4        /* device is not sm_100 */
+} vcn_status;
+
+typedef enum { VCN_F32 = 0, VCN_F16 = 1, VCN_BF16 = 2, VCN_F64 = 3 } vcn_dtype;
+
+/* Activation ids = the reference's cuda_idx column (bias_act.py:23-33). */
+typedef enum {
+  VCN_ACT_LINEAR = 1, VCN_ACT_RELU = 2, VCN_ACT_LRELU = 3, VCN_ACT_TANH = 4, VCN_ACT_SIGMOID = 5,
+  VCN_ACT_ELU = 6, VCN_ACT_SELU = 7, VCN_ACT_SOFTPLUS = 8, VCN_ACT_SWISH = 9
+} vcn_act;
+
+/* ---- library ---------------------------------------------------------------------------- */
+int vcn_abi_version(void);
+const char* vcn_last_error(void);
+/* 0 iff `device` exists and is compute capability 10.x; fills sm count / L2 bytes when non-NULL. */
+int vcn_device_info(int device, int* sm_count, int64_t* l2_bytes, int* cc_major, int* cc_minor);
+
+/* ---- bias_act ---------------------------------------------------------------------------
+ * Replaces `bias_act(x, b, xref, yref, dy, grad, dim, act, alpha, gain, clamp)`
+ * (bias_act.cpp:32-90, kernel bias_act.cu:23-147).  x is a dense tensor seen as a flat array of
+ * size_x elements; the bias index of flat element i is (i / step_b) % size_b (bias_act.cu:44),
+ * step_b = x.stride(dim).
+ *   grad 0: y = clamp(act(x + b) * gain)
+ *   grad 1: x holds dy;        y = dx   (needs yref, or xref(+b) for swish)
+ *   grad 2: x holds d_dx, dy;  y = d_x  (second-order; only acts with a 2nd grad)
+ * New vs the reference: when `db` is non-NULL the per-channel sum of the result (the reference's
+ * separate `dx.sum(...)`, bias_act.py:173,204) is produced by the same call; it needs a
+ * workspace of vcn_bias_act_workspace() bytes.  db has size_b elements of `dtype`.
+ */
+size_t vcn_bias_act_workspace(int dtype, int64_t size_x, int64_t size_b, int64_t step_b);
+int vcn_bias_act(const void* x, const void* b, const void* xref, const void* yref, const void* dy,
+                 void* y, void* db, void* workspace, size_t workspace_bytes,
+                 int dtype, int grad, int act, float alpha, float gain, float clamp,
+                 int64_t size_x, int64_t size_b, int64_t step_b, void* stream);
+
+/* ---- upfirdn2d ---------------------------------------------------------------------------
+ * Replaces `upfirdn2d(x, f, upx, upy, downx, downy, padx0, padx1, pady0, pady1, flip, gain)`
+ * (upfirdn2d.cpp:16-94, kernels upfirdn2d.cu:29-200).  x is [n, c, in_h, in_w] with element
+ * strides xs[4]; y is [n, c, out_h, out_w] with strides ys[4]; out_w must equal
+ * (in_w*upx + padx0 + padx1 - fw + downx) / downx (upfirdn2d.cpp:32-33) and likewise out_h.
+ * f is a dense fp32 [fh, fw] filter in device memory.  flip != 0 = correlation with f as given,
+ * flip == 0 = true convolution (upfirdn2d.cu:125-127).
+ * Optional fused epilogue (new; all NULL/0 = plain reference semantics):
+ *   y = upfirdn(x) * scale[n*c_idx] + noise[n?, h, w]   then   bias_act(b, act, ...)
+ * used by the up=2 modulated convolution (networks.py:69-71 fma + :302-304 bias_act).
+ */
+typedef struct {
+  const float* scale;        /* fp32 [n, c] per-sample per-channel multiplier (demod coefs) or NULL */
+  const float* noise;        /* fp32 [noise_n, out_h, out_w] added after scaling, or NULL */
+  int64_t noise_stride_n;    /* elements between samples; 0 = one plane broadcast over n */
+  const float* bias;         /* fp32 [c] or NULL */
+  int act;                   /* vcn_act; 0 = no bias/activation stage at all */
+  float alpha, act_gain, clamp;  /* as vcn_bias_act; clamp < 0 disables */
+} vcn_upfirdn2d_epilogue;
+
+int vcn_upfirdn2d(const void* x, const float* f, void* y, int dtype,
+                  int n, int c, int in_h, int in_w, const int64_t xs[4],
+                  int out_h, int out_w, const int64_t ys[4],
+                  int fh, int fw, int upx, int upy, int downx, int downy,
+                  int padx0, int padx1, int pady0, int pady1, int flip, float gain,
+                  const vcn_upfirdn2d_epilogue* epi, void* stream);
+
+/* @@MODCONV@@ */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VCN_B200_H_ */

@@ -1,0 +1,384 @@
+// upfirdn2d.cu - pad -> zero-insert upsample -> 2-D FIR -> decimate, for sm_100a.
+//
+// Replaces upfirdn2d_kernel_small / upfirdn2d_kernel_large (stylegan2_ada/torch_utils/ops/upfirdn2d.cu:29-200)
+// and the spec table of upfirdn2d.cu:205-341.  Index contract (upfirdn2d.cu:141-144,176-183):
+//   out[oy,ox] = gain * sum_{fy,fx} f'[fy,fx] * U[oy*down + fy - pad0, ...],  U = zero-inserted input,
+//   f' = f flipped unless `flip` (flip=0 is true convolution).
+//
+// Two kernels:
+//   tile    : dense NCHW, filter <= 4x4, (up,down) in {(1,1),(2,1),(1,2)}.  One CTA stages the input halo tile of
+//             TP planes x IH x IWp in shared memory - by ONE TMA box load (cp.async.bulk.tensor.3d; out-of-bounds
+//             zero fill IS the op's zero padding, negative coordinates included) when the row pitch is 16-byte
+//             aligned, else by coalesced loads - then every thread produces a 4 x MC register micro-tile from
+//             16-byte shared-memory reads and writes it with 16-byte stores.
+//   generic : any filter / factors / strides (channels_last included): one output per thread, gather.
+// HBM-bound: algorithmic bytes = (N*C*Hin*Win + N*C*Hout*Wout) * e.
+#include <string.h>
+
+#include "act_math.cuh"
+
+namespace vcn {
+namespace {
+
+struct UpfirdnArgs {
+  const void* x;
+  const float* f;
+  void* y;
+  int n, c, in_h, in_w, out_h, out_w;
+  int64_t xs[4], ys[4];
+  int fh, fw, upx, upy, downx, downy, padx0, pady0, flip;
+  float gain;
+  // fused epilogue (all optional)
+  const float* scale;
+  const float* noise;
+  int64_t noise_stride_n;
+  const float* bias;
+  int act;
+  float alpha, act_gain, clamp;
+};
+
+template <typename S>
+__device__ __forceinline__ S epilogue(const UpfirdnArgs& a, S v, int plane, int oy, int ox) {
+  v *= S(a.gain);
+  if (a.scale) v *= S(a.scale[plane]);
+  if (a.noise) v += S(a.noise[(int64_t)(plane / a.c) * a.noise_stride_n + (int64_t)oy * a.out_w + ox]);
+  if (a.act) {
+    if (a.bias) v += S(a.bias[plane % a.c]);
+    v = act_eval<S, 0>(v, S(0), S(0), S(1), a.act, 0, S(a.alpha), S(a.act_gain), S(a.clamp));
+  }
+  return v;
+}
+
+__device__ __forceinline__ int floor_div(int a, int b) {
+  const int q = a / b;
+  return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q;
+}
+
+// ---------------------------------------------------------------------------------------------
+// generic gather kernel
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) upfirdn2d_generic_kernel(const UpfirdnArgs a, const int channels_fastest) {
+  using S = typename Acc<T>::type;
+  const int64_t total = (int64_t)a.n * a.c * a.out_h * a.out_w;
+  const T* __restrict__ px = static_cast<const T*>(a.x);
+  T* __restrict__ py = static_cast<T*>(a.y);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int ox, oy, ch, nb;
+    int64_t r = i;
+    if (channels_fastest) {
+      ch = (int)(r % a.c); r /= a.c;
+      ox = (int)(r % a.out_w); r /= a.out_w;
+      oy = (int)(r % a.out_h); nb = (int)(r / a.out_h);
+    } else {
+      ox = (int)(r % a.out_w); r /= a.out_w;
+      oy = (int)(r % a.out_h); r /= a.out_h;
+      ch = (int)(r % a.c); nb = (int)(r / a.c);
+    }
+    const T* xb = px + nb * a.xs[0] + ch * a.xs[1];
+    S acc = S(0);
+    const int my = oy * a.downy - a.pady0, mx = ox * a.downx - a.padx0;
+    for (int fy = 0; fy < a.fh; ++fy) {
+      const int uy = my + fy;
+      if (uy < 0 || uy % a.upy != 0) continue;
+      const int iy = uy / a.upy;
+      if (iy >= a.in_h) continue;
+      for (int fx = 0; fx < a.fw; ++fx) {
+        const int ux = mx + fx;
+        if (ux < 0 || ux % a.upx != 0) continue;
+        const int ix = ux / a.upx;
+        if (ix >= a.in_w) continue;
+        const float w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
+        acc += S(w) * to_acc<T>(xb[iy * a.xs[2] + ix * a.xs[3]]);
+      }
+    }
+    acc = epilogue<S>(a, acc, nb * a.c + ch, oy, ox);
+    py[nb * a.ys[0] + ch * a.ys[1] + oy * a.ys[2] + ox * a.ys[3]] = from_acc<T>(acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// tile kernel
+// ---------------------------------------------------------------------------------------------
+constexpr int kF = 4;   // filter taps per axis (smaller filters are zero-extended)
+constexpr int kMR = 4;  // output rows per thread
+
+struct TileGeom {
+  int tw, th, tp;        // output tile: cols, rows, planes
+  int tx, ty;            // threads along cols / rows (tp along planes)
+  int iw, ih, iwp;       // staged input tile: valid cols, rows, pitch (elements)
+  int tiles_x, tiles_y, tiles_p;
+  int use_tma, vec_store;
+};
+
+template <typename T, int UP, int DOWN, int PHX, int PHY>
+__global__ void __launch_bounds__(256)
+upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_constant__ CUtensorMap tmap) {
+  using S = typename Acc<T>::type;
+  constexpr int V = Vec16<T>::N;   // elements per 16 bytes
+  constexpr int MC = V;            // output cols per thread
+  constexpr int WR = ((kMR - 1) * DOWN + kF - 1 - PHY) / UP + 1;  // window rows a thread reads
+  constexpr int WC = ((MC - 1) * DOWN + kF - 1 - PHX) / UP + 1;   // window cols
+  constexpr int NV = (UP == 1) ? (WC + V - 1) / V : 0;             // 16-byte loads per window row (UP==1)
+  constexpr int WCL = (UP == 1) ? NV * V : WC;
+
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  T* tile = reinterpret_cast<T*>(smem_raw);
+  const int tile_elems = g.tp * g.ih * g.iwp;
+  float* sflt = reinterpret_cast<float*>(smem_raw + (((size_t)tile_elems * sizeof(T) + 15) & ~(size_t)15));
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sflt + kF * kF);
+
+  const int tid = threadIdx.x;
+  int bid = blockIdx.x;
+  const int bx = bid % g.tiles_x; bid /= g.tiles_x;
+  const int by = bid % g.tiles_y;
+  const int bp = bid / g.tiles_y;
+  const int tile_ox = bx * g.tw, tile_oy = by * g.th, plane0 = bp * g.tp;
+  const int planes = a.n * a.c;
+  // first staged input column/row: ceil((tile_o*DOWN - pad0) / UP)
+  const int ix0 = -floor_div(-(tile_ox * DOWN - a.padx0), UP);
+  const int iy0 = -floor_div(-(tile_oy * DOWN - a.pady0), UP);
+
+  if (g.use_tma) {
+    if (tid == 0) {
+      mbar_init(bar, 1);
+      fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+      mbar_expect_tx(bar, (uint32_t)(tile_elems * sizeof(T)));
+      tma_load_3d(tile, &tmap, bar, ix0, iy0, plane0);
+    }
+  }
+  if (tid < kF * kF) {
+    const int fy = tid / kF, fx = tid % kF;
+    float w = 0.f;
+    if (fy < a.fh && fx < a.fw) w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
+    sflt[tid] = w;
+  }
+  if (!g.use_tma) {
+    const T* __restrict__ px = static_cast<const T*>(a.x);
+    const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
+    for (int rr = warp; rr < g.tp * g.ih; rr += nwarps) {
+      const int p = rr / g.ih, r = rr - p * g.ih;
+      const int gy = iy0 + r, pl = plane0 + p;
+      const bool row_ok = gy >= 0 && gy < a.in_h && pl < planes;
+      const T* src = px + ((int64_t)pl * a.in_h + gy) * a.in_w;
+      T* dst = tile + (size_t)rr * g.iwp;
+      for (int cc = lane; cc < g.iwp; cc += 32) {
+        const int gx = ix0 + cc;
+        dst[cc] = (row_ok && gx >= 0 && gx < a.in_w) ? src[gx] : from_acc<T>(S(0));
+      }
+    }
+  }
+  __syncthreads();
+  if (g.use_tma) mbar_wait(bar, 0);
+
+  S flt[kF][kF];
+#pragma unroll
+  for (int i = 0; i < kF; ++i)
+#pragma unroll
+    for (int j = 0; j < kF; ++j) flt[i][j] = S(sflt[i * kF + j]);
+
+  const int t_x = tid % g.tx;
+  const int t_y = (tid / g.tx) % g.ty;
+  const int t_p = tid / (g.tx * g.ty);
+  const int rx = t_x * MC, ry = t_y * kMR;
+  const T* wbase = tile + ((size_t)t_p * g.ih + (ry * DOWN) / UP) * g.iwp + (rx * DOWN) / UP;
+
+  S acc[kMR][MC];
+#pragma unroll
+  for (int r = 0; r < kMR; ++r)
+#pragma unroll
+    for (int c = 0; c < MC; ++c) acc[r][c] = S(0);
+
+#pragma unroll
+  for (int wr = 0; wr < WR; ++wr) {
+    S w[WCL];
+    const T* srow = wbase + (size_t)wr * g.iwp;
+    if constexpr (UP == 1) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const Vec16<T> v = *reinterpret_cast<const Vec16<T>*>(srow + k * V);
+#pragma unroll
+        for (int j = 0; j < V; ++j) w[k * V + j] = to_acc<T>(v.v[j]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < WC; ++j) w[j] = to_acc<T>(srow[j]);
+    }
+#pragma unroll
+    for (int r = 0; r < kMR; ++r) {
+      const int fy = UP * wr + PHY - r * DOWN;
+      if (fy < 0 || fy >= kF) continue;
+#pragma unroll
+      for (int c = 0; c < MC; ++c) {
+#pragma unroll
+        for (int wc = 0; wc < WC; ++wc) {
+          const int fx = UP * wc + PHX - c * DOWN;
+          if (fx < 0 || fx >= kF) continue;
+          acc[r][c] = fma(w[wc], flt[fy][fx], acc[r][c]);
+        }
+      }
+    }
+  }
+
+  const int plane = plane0 + t_p;
+  const int ox = tile_ox + rx, oy_base = tile_oy + ry;
+  if (plane >= planes || ox >= a.out_w) return;
+  T* __restrict__ py = static_cast<T*>(a.y) + (int64_t)plane * a.out_h * a.out_w;
+#pragma unroll
+  for (int r = 0; r < kMR; ++r) {
+    const int oy = oy_base + r;
+    if (oy >= a.out_h) break;
+    Vec16<T> out;
+#pragma unroll
+    for (int c = 0; c < MC; ++c) {
+      const int oxc = ox + c < a.out_w ? ox + c : a.out_w - 1;
+      out.v[c] = from_acc<T>(epilogue<S>(a, acc[r][c], plane, oy, oxc));
+    }
+    T* dst = py + (int64_t)oy * a.out_w + ox;
+    if (g.vec_store && ox + MC <= a.out_w) {
+      st_stream(dst, out);
+    } else {
+#pragma unroll
+      for (int c = 0; c < MC; ++c)
+        if (ox + c < a.out_w) dst[c] = out.v[c];
+    }
+  }
+}
+
+inline int pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+template <typename T>
+TileGeom make_geom(const UpfirdnArgs& a, int up, int down) {
+  constexpr int V = Vec16<T>::N;
+  constexpr int MC = V;
+  TileGeom g{};
+  const int tw_cap = down == 2 ? 64 : 128;
+  g.tw = pow2_ceil(a.out_w); if (g.tw > tw_cap) g.tw = tw_cap; if (g.tw < MC) g.tw = MC;
+  g.tx = g.tw / MC;
+  const int max_threads = down == 2 ? 128 : 256;
+  int ty_cap = max_threads / g.tx;
+  g.th = pow2_ceil(a.out_h); if (g.th < kMR) g.th = kMR;
+  if (g.th > kMR * ty_cap) g.th = kMR * ty_cap;
+  g.ty = g.th / kMR;
+  g.tp = max_threads / (g.tx * g.ty);
+  const int planes = a.n * a.c;
+  while (g.tp > 1 && g.tp / 2 >= planes && g.tx * g.ty * (g.tp / 2) >= 32) g.tp /= 2;
+  const int span_x = (g.tw - 1) * down + kF, span_y = (g.th - 1) * down + kF;
+  g.iw = (span_x + up - 1) / up + (up > 1 ? 1 : 0);
+  g.ih = (span_y + up - 1) / up + (up > 1 ? 1 : 0);
+  // pitch: 16-byte multiple, and wide enough for the last thread's vector window reads
+  const int wc = ((MC - 1) * down + kF - 1) / up + 1;
+  const int nv = (wc + V - 1) / V;
+  int need = ((g.tw - MC) * down) / up + (up == 1 ? nv * V : wc);
+  if (need < g.iw) need = g.iw;
+  g.iwp = (need + V - 1) / V * V;
+  g.tiles_x = (a.out_w + g.tw - 1) / g.tw;
+  g.tiles_y = (a.out_h + g.th - 1) / g.th;
+  g.tiles_p = (planes + g.tp - 1) / g.tp;
+  return g;
+}
+
+template <typename T, int UP, int DOWN, int PHX, int PHY>
+int launch_tile(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st) {
+  const size_t e = sizeof(T);
+  const int planes = a.n * a.c;
+  CUtensorMap tmap;
+  memset(&tmap, 0, sizeof(tmap));
+  g.use_tma = aligned16(a.x) && ((size_t)a.in_w * e) % 16 == 0 && g.iwp <= 256 && g.ih <= 256 && g.tp <= 256;
+  if (g.use_tma) {
+    const uint64_t dims[3] = {(uint64_t)a.in_w, (uint64_t)a.in_h, (uint64_t)planes};
+    const uint64_t strides[2] = {(uint64_t)a.in_w * e, (uint64_t)a.in_w * a.in_h * e};
+    const uint32_t box[3] = {(uint32_t)g.iwp, (uint32_t)g.ih, (uint32_t)g.tp};
+    const int rc = make_tensor_map(&tmap, dtype, 3, a.x, dims, strides, box, nullptr, 0);
+    if (rc) return rc;
+  }
+  g.vec_store = aligned16(a.y) && ((size_t)a.out_w * e) % 16 == 0;
+  const size_t smem = (((size_t)g.tp * g.ih * g.iwp * e + 15) & ~(size_t)15) + kF * kF * sizeof(float) + 16;
+  auto kern = upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY>;
+  if (smem > 48 * 1024) VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t grid = (int64_t)g.tiles_x * g.tiles_y * g.tiles_p;
+  if (grid > 0x7fffffffLL) { set_error("upfirdn2d: grid too large"); return VCN_ERR_INVALID; }
+  kern<<<(unsigned)grid, g.tx * g.ty * g.tp, smem, st>>>(a, g, tmap);
+  VCN_LAUNCH_CHECK("upfirdn2d_tile_kernel");
+  return VCN_OK;
+}
+
+template <typename T>
+int run(const UpfirdnArgs& a, int dtype, cudaStream_t st) {
+  const bool dense_in = a.xs[3] == 1 && a.xs[2] == a.in_w && a.xs[1] == (int64_t)a.in_h * a.in_w &&
+                        (a.n == 1 || a.xs[0] == (int64_t)a.c * a.in_h * a.in_w);
+  const bool dense_out = a.ys[3] == 1 && a.ys[2] == a.out_w && a.ys[1] == (int64_t)a.out_h * a.out_w &&
+                         (a.n == 1 || a.ys[0] == (int64_t)a.c * a.out_h * a.out_w);
+  const bool small_f = a.fw <= kF && a.fh <= kF;
+  const bool sq = a.upx == a.upy && a.downx == a.downy;
+  const int up = a.upx, down = a.downx;
+  const bool combo = (up == 1 && down == 1) || (up == 2 && down == 1) || (up == 1 && down == 2);
+  if constexpr (sizeof(T) != 8)
+  if (dense_in && dense_out && small_f && sq && combo && a.out_w >= 4 && a.out_h >= 4) {
+    const TileGeom g = make_geom<T>(a, up, down);
+    if (up == 1 && down == 1) return launch_tile<T, 1, 1, 0, 0>(a, g, dtype, st);
+    if (up == 1 && down == 2) return launch_tile<T, 1, 2, 0, 0>(a, g, dtype, st);
+    const int phx = ((a.padx0 % 2) + 2) % 2, phy = ((a.pady0 % 2) + 2) % 2;
+    if (phx == 0 && phy == 0) return launch_tile<T, 2, 1, 0, 0>(a, g, dtype, st);
+    if (phx == 1 && phy == 0) return launch_tile<T, 2, 1, 1, 0>(a, g, dtype, st);
+    if (phx == 0 && phy == 1) return launch_tile<T, 2, 1, 0, 1>(a, g, dtype, st);
+    return launch_tile<T, 2, 1, 1, 1>(a, g, dtype, st);
+  }
+  const int64_t total = (int64_t)a.n * a.c * a.out_h * a.out_w;
+  int64_t grid = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (grid > cap) grid = cap;
+  const int channels_fastest = (a.ys[1] == 1 && a.c > 1) ? 1 : 0;
+  upfirdn2d_generic_kernel<T><<<(unsigned)grid, 256, 0, st>>>(a, channels_fastest);
+  VCN_LAUNCH_CHECK("upfirdn2d_generic_kernel");
+  return VCN_OK;
+}
+
+}  // namespace
+}  // namespace vcn
+
+extern "C" int vcn_upfirdn2d(const void* x, const float* f, void* y, int dtype, int n, int c, int in_h, int in_w,
+                             const int64_t xs[4], int out_h, int out_w, const int64_t ys[4], int fh, int fw, int upx,
+                             int upy, int downx, int downy, int padx0, int padx1, int pady0, int pady1, int flip,
+                             float gain, const vcn_upfirdn2d_epilogue* epi, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(dtype_size(dtype) != 0, "upfirdn2d: unknown dtype %d", dtype);
+  VCN_REQUIRE(n >= 0 && c >= 0 && in_h >= 1 && in_w >= 1, "upfirdn2d: bad input shape [%d,%d,%d,%d]", n, c, in_h, in_w);
+  VCN_REQUIRE(fh >= 1 && fw >= 1, "upfirdn2d: filter must be at least 1x1");
+  VCN_REQUIRE(upx >= 1 && upy >= 1 && downx >= 1 && downy >= 1, "upfirdn2d: up/down factors must be >= 1");
+  const int want_w = (in_w * upx + padx0 + padx1 - fw + downx) / downx;
+  const int want_h = (in_h * upy + pady0 + pady1 - fh + downy) / downy;
+  VCN_REQUIRE(want_w >= 1 && want_h >= 1, "upfirdn2d: output would be empty (%d x %d)", want_h, want_w);
+  VCN_REQUIRE(out_w == want_w && out_h == want_h, "upfirdn2d: output shape %dx%d does not match expected %dx%d", out_h,
+              out_w, want_h, want_w);
+  if (n == 0 || c == 0) return VCN_OK;
+  VCN_REQUIRE(x && f && y && xs && ys, "upfirdn2d: x, f, y and strides must not be NULL");
+  VCN_REQUIRE((int64_t)n * c * out_h * out_w <= 0x7fffffffLL && (int64_t)n * c * in_h * in_w <= 0x7fffffffLL,
+              "upfirdn2d: tensor too large");
+  UpfirdnArgs a{};
+  a.x = x; a.f = f; a.y = y;
+  a.n = n; a.c = c; a.in_h = in_h; a.in_w = in_w; a.out_h = out_h; a.out_w = out_w;
+  for (int i = 0; i < 4; ++i) { a.xs[i] = xs[i]; a.ys[i] = ys[i]; }
+  a.fh = fh; a.fw = fw; a.upx = upx; a.upy = upy; a.downx = downx; a.downy = downy;
+  a.padx0 = padx0; a.pady0 = pady0; a.flip = flip ? 1 : 0; a.gain = gain;
+  if (epi) {
+    a.scale = epi->scale; a.noise = epi->noise; a.noise_stride_n = epi->noise_stride_n; a.bias = epi->bias;
+    a.act = epi->act; a.alpha = epi->alpha; a.act_gain = epi->act_gain; a.clamp = epi->clamp;
+    VCN_REQUIRE(a.act == 0 || (a.act >= VCN_ACT_LINEAR && a.act <= VCN_ACT_SWISH), "upfirdn2d: bad epilogue act %d", a.act);
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype) {
+    case VCN_F32: return run<float>(a, dtype, st);
+    case VCN_F16: return run<__half>(a, dtype, st);
+    case VCN_BF16: return run<__nv_bfloat16>(a, dtype, st);
+    case VCN_F64: return run<double>(a, dtype, st);
+  }
+  return VCN_ERR_INVALID;
+}
