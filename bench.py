@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py - the measurement contract of this repo (see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload opsweep|synthesis] [--impl ours|reference]
+
+One "step" = one pass of the hot path over one batch of synthetic input.  Prints ONE JSON line (rank 0).
+  value     whole-job throughput with inputs resident in HBM (device-timed, CUDA events, max over ranks)
+  e2e       same metric through the public operator API with HOST (pinned) buffers: H2D + op + D2H timed
+  roofline  dominant kernel: algorithmic bytes per launch / CUDA-event duration vs MEASURED_PEAKS.json
+  cpu_baseline  the oracle (CPU restatement of the reference ref path) timed on a bounded sample, rank 0, N=1
+`--impl reference` times the reference's CPU implementation (the oracle port; /root/reference does not exist on
+the GPU box) on the same workload with all host threads.
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("VCN_BENCH_WORKLOAD", "auto"))
+    ap.add_argument("--batch", type=int, default=8, help="images per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            d = json.load(fh)
+        return dict(hbm=float(d["hbm_gbs"]), bf16=float(d["bf16_tflops"]), bf16_sus=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                    src="measured")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [s.strip() for s in ln.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx = float(p[2])
+            except ValueError:
+                continue
+            for nm, v in zip(names, p[5:9]):
+                if v.lower() == "active":
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        backend = "nccl" if torch.cuda.is_available() and args.impl == "ours" else "gloo"
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local)
+        dist.init_process_group(backend=backend)
+    return world, rank, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+def max_over_ranks(ms, world, device):
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    return ms
+
+
+# ----------------------------------------------------------------------------------------------------------
+# workloads
+# ----------------------------------------------------------------------------------------------------------
+
+GATE_SET = [(512, 64), (256, 128), (128, 256)]  # (channels, output resolution) of SURVEY 8(d) config 2: >> L2 at N=8
+
+
+class OpSweep:
+    """BASELINE.json configs[1]: upfirdn2d + bias_act over the memory-bound gate set (fp32, NCHW, N=batch).
+
+    Per step and per (C, H): pattern A FIR ([N,C,H+1,H+1] -> [N,C,H,H], 4x4, pad 1, gain 4: what follows every
+    transposed conv of the synthesis network) then bias_act(lrelu) on the result, forward; then
+    the bias_act grad-1 (+db) pass on the same tensor.  Algorithmic bytes: upfirdn2d (in+out)*4,
+    bias_act fwd 2*S*4, grad-1 3*S*4."""
+
+    name = "upfirdn2d+bias_act op sweep fp32 NCHW N=%d, C x H in {512x64, 256x128, 128x256}, fwd + bias_act grad1"
+    metric = "upfirdn2d+bias_act algorithmic HBM GB/s"
+    unit = "GB/s"
+    dtype = "f32"
+
+    def __init__(self, batch):
+        self.n = batch
+        self.name = self.name % batch
+
+    def alg_bytes(self, n=None):
+        n = self.n if n is None else n
+        tot = 0
+        for c, h in GATE_SET:
+            s_in, s_out = n * c * (h + 1) * (h + 1), n * c * h * h
+            tot += (s_in + s_out) * 4 + 2 * s_out * 4 + 3 * s_out * 4
+        return tot
+
+    def units_per_step(self):
+        return self.alg_bytes() / 1e9
+
+    def setup(self, device, seed):
+        import viscoin_next_b200 as V
+        self.V = V
+        g = torch.Generator(device=device).manual_seed(seed)
+        self.f = V.upfirdn2d.setup_filter([1, 3, 3, 1], device=device)
+        self.x = [torch.randn(self.n, c, h + 1, h + 1, device=device, generator=g) for c, h in GATE_SET]
+        self.b = [torch.randn(c, device=device, generator=g) for c, _ in GATE_SET]
+        self.dy = [torch.randn(self.n, c, h, h, device=device, generator=g) for c, h in GATE_SET]
+
+    def _one(self, x, b, dy):
+        V = self.V
+        y = V.upfirdn2d.upfirdn2d(x, self.f, padding=[1, 1, 1, 1], gain=4)
+        y = y.requires_grad_(True)
+        b = b.requires_grad_(True)
+        z = V.bias_act.bias_act(y, b, act="lrelu")
+        dx, db = torch.autograd.grad(z, [y, b], dy)
+        return dx, db
+
+    def step(self):
+        out = None
+        for x, b, dy in zip(self.x, self.b, self.dy):
+            out = self._one(x, b, dy)
+        return out
+
+    # --- end to end: host buffers in, host result out -------------------------------------------------
+    def e2e_setup(self, device):
+        self.hx = [x.cpu().pin_memory() for x in self.x]
+        self.hdy = [d.cpu().pin_memory() for d in self.dy]
+        self.hout = [torch.empty(d.shape, dtype=d.dtype).pin_memory() for d in self.dy]
+        self.h2d = sum(t.numel() * 4 for t in self.hx + self.hdy)
+        self.d2h = sum(t.numel() * 4 for t in self.hout)
+
+    def e2e_step(self, device):
+        for hx, hdy, b, ho in zip(self.hx, self.hdy, self.b, self.hout):
+            dx, _ = self._one(hx.to(device, non_blocking=True), b, hdy.to(device, non_blocking=True))
+            ho.copy_(dx, non_blocking=True)
+
+    # --- dominant kernel alone ----------------------------------------------------------------------
+    def roofline(self, device, peaks, iters=20):
+        """bias_act forward (rows kernel) on the largest tensor [N,128,256,256]: 2*S*4 algorithmic bytes."""
+        V = self.V
+        c, h = GATE_SET[-1]
+        x = torch.randn(self.n, c, h, h, device=device)
+        b = self.b[-1].detach()
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+        for _ in range(3):
+            V.bias_act.bias_act(x, b, act="lrelu")
+        times = []
+        for _ in range(iters):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            V.bias_act.bias_act(x, b, act="lrelu")
+            e1.record()
+            e1.synchronize()
+            times.append(e0.elapsed_time(e1))
+        ms = sum(times) / len(times)
+        alg = 2 * x.numel() * 4
+        ach = alg / (ms * 1e-3) / 1e9
+        return {"kernel": "bias_act_rows_kernel<float,lrelu> [%d,%d,%d,%d] fwd" % (self.n, c, h, h), "bound": "hbm",
+                "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s", "frac": round(ach / peaks["hbm"], 4),
+                "peak_source": peaks["src"] + " (burst copy)", "traffic": None, "alg_bytes_per_launch": alg,
+                "avg_launch_ms": round(ms, 5)}
+
+    # --- CPU (oracle) -------------------------------------------------------------------------------
+    def cpu_step(self, n_sample, seed=0):
+        """The oracle's restatement of the reference ref path on a sample of n_sample images per tensor."""
+        from oracle import ref_ops as R
+        g = torch.Generator().manual_seed(seed)
+        f = R.setup_filter([1, 3, 3, 1])
+        t0 = time.perf_counter()
+        for c, h in GATE_SET:
+            x = torch.randn(n_sample, c, h + 1, h + 1, generator=g)
+            b = torch.randn(c, generator=g).requires_grad_(True)
+            dy = torch.randn(n_sample, c, h, h, generator=g)
+            t0 -= 0  # generation is outside the op but cheap; keep the timer simple and conservative
+            y = R.upfirdn2d(x, f, padding=[1, 1, 1, 1], gain=4).requires_grad_(True)
+            z = R.bias_act(y, b, act="lrelu")
+            torch.autograd.grad(z, [y, b], dy)
+        return time.perf_counter() - t0
+
+
+WORKLOADS = {"opsweep": OpSweep}
+
+
+def pick_workload(args):
+    name = args.workload
+    if name == "auto":
+        name = DEFAULT_WORKLOAD
+    if name not in WORKLOADS:
+        raise SystemExit("unknown workload %r (have: %s)" % (name, ", ".join(WORKLOADS)))
+    return WORKLOADS[name](args.batch)
+
+
+DEFAULT_WORKLOAD = "opsweep"
+
+
+def run_reference(args, world, rank):
+    """The reference's own CPU implementation of the path (oracle port of its impl='ref' code) on host cores."""
+    if rank != 0:
+        return
+    wl = pick_workload(args)
+    cores = len(os.sched_getaffinity(0))
+    torch.set_num_threads(cores)
+    n_sample = 1
+    for _ in range(max(1, min(args.warmup, 1))):
+        wl.cpu_step(n_sample)
+    t = [wl.cpu_step(n_sample) for _ in range(max(1, min(args.steps, 5)))]
+    sec = sum(t) / len(t)
+    value = wl.units_per_step() * (n_sample / wl.n) / sec
+    line = {"impl": "reference", "metric": wl.metric, "value": round(value, 4), "unit": wl.unit, "n_gpus": args.gpus,
+            "steps": len(t), "warmup": 1, "ms_per_step": round(sec * 1e3 * wl.n / n_sample, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
+            "config": {"workload": wl.name, "device": "host CPU"},
+            "cpu_baseline": {"value": round(value, 4), "unit": wl.unit, "cores": cores, "kind": "port",
+                             "sample": "%d of %d images per tensor per step, oracle/ref_ops.py (torch CPU ref path)" % (n_sample, wl.n)},
+            "e2e": {"value": round(value, 4), "unit": wl.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    world, rank, local = dist_setup(args)
+    if args.impl == "reference":
+        run_reference(args, world, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    import viscoin_next_b200 as V
+    lib = V._lib.load()
+    V._lib.require_device(local)
+    peaks = measured_peaks()
+    wl = pick_workload(args)
+    wl.setup(device, seed=1000 * world + rank)
+
+    for _ in range(max(args.warmup, 3)):
+        wl.step()
+    torch.cuda.synchronize()
+    barrier(world)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.vcn_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        wl.step()
+    e1.record()
+    torch.cuda.synchronize()
+    barrier(world)
+    launches = lib.vcn_launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    ms = max_over_ranks(e0.elapsed_time(e1), world, device)
+    value = wl.units_per_step() * world * args.steps / (ms * 1e-3)
+
+    # end to end through the public API with host buffers
+    wl.e2e_setup(device)
+    for _ in range(2):
+        wl.e2e_step(device)
+    torch.cuda.synchronize()
+    barrier(world)
+    k_e2e = max(2, min(args.steps, 5))
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(k_e2e):
+        wl.e2e_step(device)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)
+    ms_e2e = max_over_ranks(ms_e2e, world, device)
+    e2e_value = wl.units_per_step() * world * k_e2e / (ms_e2e * 1e-3)
+
+    roof = cpu = None
+    if rank == 0:
+        roof = wl.roofline(device, peaks)
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(prof):  # dram bytes per launch from the committed ncu --set full capture
+            try:
+                roof["traffic"] = json.load(open(prof)).get(roof["kernel"].split("<")[0].split(" ")[0])
+            except Exception:
+                pass
+        if world == 1 and not args.no_cpu_baseline:
+            cores = len(os.sched_getaffinity(0))
+            torch.set_num_threads(cores)
+            wl.cpu_step(1)
+            sec = min(wl.cpu_step(1) for _ in range(2))
+            cpu = {"value": round(wl.units_per_step() / wl.n / sec, 4), "unit": wl.unit, "cores": cores, "kind": "port",
+                   "sample": "1 of %d images per tensor per step, oracle/ref_ops.py (torch CPU restatement of impl='ref')" % wl.n}
+    barrier(world)
+    if rank == 0:
+        line = {"metric": wl.metric, "value": round(value, 3), "unit": wl.unit, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
+                "config": {"workload": wl.name, "batch_per_gpu": wl.n, "l2": "inputs larger than L2 (every tensor >= 67 MB)",
+                           "parallelism": "dp%d (independent shards, no data-path collective)" % world},
+                "clocks": clocks,
+                "e2e": {"value": round(e2e_value, 3), "unit": wl.unit, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
+                        "steps": k_e2e},
+                "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

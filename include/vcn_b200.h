@@ -43,6 +43,8 @@ typedef enum {
 /* ---- library ---------------------------------------------------------------------------- */
 int vcn_abi_version(void);
 const char* vcn_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+uint64_t vcn_launch_count(void);
 /* 0 iff `device` exists and is compute capability 10.x; fills sm count / L2 bytes when non-NULL. */
 int vcn_device_info(int device, int* sm_count, int64_t* l2_bytes, int* cc_major, int* cc_minor);
 

@@ -1,0 +1,158 @@
+"""GPU parity: vcn_upfirdn2d (through the host mirror / C ABI) vs the oracle and the golden vectors recorded
+from the reference's impl='ref' path.  Tolerance: fp32 exact-FMA kernel, rel-L-inf <= 1e-5;
+bf16/fp16: <= 2 ulp of the storage type against the fp32 oracle on the rounded inputs.
+"""
+
+import pytest
+import torch
+
+from oracle import ref_ops as R
+from oracle.make_golden import UPFIRDN_CASES
+
+pytestmark = pytest.mark.gpu
+
+
+def _ops():
+    import viscoin_next_b200 as V
+    return V.upfirdn2d
+
+
+def _rel(a, b):
+    a = a.detach().double().cpu()
+    b = b.detach().double().cpu()
+    assert a.shape == b.shape, (a.shape, b.shape)
+    if a.numel() == 0:
+        return 0.0
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1.0)).item()
+
+
+@pytest.mark.parametrize("name", list(UPFIRDN_CASES))
+def test_golden(golden, name):
+    U = _ops()
+    g = golden("upfirdn2d")
+    _, _, kw = UPFIRDN_CASES[name]
+    x = g.t(name + ".x", device="cuda").requires_grad_(True)
+    f = g.t(name + ".f", device="cuda")
+    y = U.upfirdn2d(x, f, impl="cuda", **kw)
+    assert _rel(y, g.t(name + ".y")) <= 1e-5
+    (dx,) = torch.autograd.grad(y, [x], g.t(name + ".dy", device="cuda"))
+    assert _rel(dx, g.t(name + ".dx")) <= 1e-5
+
+
+def test_golden_wrappers(golden):
+    U = _ops()
+    g = golden("upfirdn2d")
+    x, f4 = g.t("wrap.x", device="cuda"), g.t("wrap.f", device="cuda")
+    assert _rel(U.filter2d(x, f4), g.t("wrap.filter2d")) <= 1e-5
+    assert _rel(U.upsample2d(x, f4), g.t("wrap.upsample2d")) <= 1e-5
+    assert _rel(U.downsample2d(x, f4), g.t("wrap.downsample2d")) <= 1e-5
+    assert _rel(U.upsample2d(x, f4, up=[2, 1], padding=[1, 0, 0, 2], gain=0.5), g.t("wrap.upsample2d_p")) <= 1e-5
+    assert _rel(U.setup_filter([1, 3, 3, 1]), g.t("setup.a")) <= 1e-7
+    assert _rel(U.setup_filter(list(range(1, 10)), gain=3), g.t("setup.c")) <= 1e-7
+
+
+# hot-path patterns of SURVEY 8(a6) at odd and even sizes (A: after transpose conv, B: RGB skip, primes: backward)
+PATTERNS = {
+    "A": dict(up=1, down=1, padding=[1, 1, 1, 1], gain=4),
+    "A_bwd": dict(up=1, down=1, padding=[2, 2, 2, 2], flip_filter=True, gain=4),
+    "B": dict(up=2, down=1, padding=[2, 1, 2, 1], gain=4),
+    "B_bwd": dict(up=1, down=2, padding=[1, 1, 1, 1], flip_filter=True, gain=4),
+    "down2": dict(up=1, down=2, padding=[1, 1, 1, 1]),
+    "up2_p0": dict(up=2, down=1, padding=[1, 2, 1, 2]),
+    "up2_mixed": dict(up=2, down=1, padding=[3, 0, 2, 1]),
+}
+
+
+@pytest.mark.parametrize("pat", list(PATTERNS))
+@pytest.mark.parametrize("shape", [(2, 3, 9, 9), (1, 5, 17, 17), (2, 4, 33, 33), (1, 2, 65, 65), (2, 3, 16, 16),
+                                   (1, 3, 64, 64), (1, 2, 129, 129), (1, 1, 6, 70), (3, 2, 40, 12), (1, 3, 128, 128)])
+def test_patterns_vs_oracle(pat, shape):
+    U = _ops()
+    kw = PATTERNS[pat]
+    g = torch.Generator().manual_seed(sum(shape) * 7 + len(pat))
+    x = torch.randn(shape, generator=g).requires_grad_(True)
+    f = R.setup_filter([1, 3, 3, 1])
+    y_ref = R.upfirdn2d(x, f, **kw)
+    dy = torch.randn(y_ref.shape, generator=g)
+    (dx_ref,) = torch.autograd.grad(y_ref, [x], dy)
+    xc = x.detach().cuda().requires_grad_(True)
+    y = U.upfirdn2d(xc, f.cuda(), impl="cuda", **kw)
+    (dx,) = torch.autograd.grad(y, [xc], dy.cuda())
+    assert _rel(y, y_ref) <= 1e-5
+    assert _rel(dx, dx_ref) <= 1e-5
+
+
+@pytest.mark.parametrize("fshape", [(1, 1), (2, 2), (3, 3), (4, 4), (5, 5), (8, 8), (3, 5), (1, 4)])
+@pytest.mark.parametrize("up,down,pad", [(1, 1, 0), (2, 1, [3, 2, 3, 2]), (1, 2, [2, 2, 1, 3]), (3, 2, [4, 3, 5, 2]),
+                                         ([2, 1], [1, 3], [4, 4, 4, 4]), (1, 1, [-1, 5, 6, -2])])
+@pytest.mark.parametrize("flip", [False, True])
+def test_generic_vs_oracle(fshape, up, down, pad, flip):
+    U = _ops()
+    g = torch.Generator().manual_seed(fshape[0] * 13 + fshape[1])
+    x = torch.randn(2, 3, 13, 11, generator=g)
+    f = torch.randn(fshape, generator=g)
+    y_ref = R.upfirdn2d(x, f, up=up, down=down, padding=pad, flip_filter=flip, gain=1.3)
+    y = U.upfirdn2d(x.cuda(), f.cuda(), up=up, down=down, padding=pad, flip_filter=flip, gain=1.3, impl="cuda")
+    assert _rel(y, y_ref) <= 1e-5
+
+
+def test_separable_and_channels_last():
+    U = _ops()
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 6, 20, 18, generator=g)
+    f12 = R.setup_filter([0.1, -0.3, 0.7, 1.1, 2.0, 3.1, 2.9, 1.9, 1.2, 0.6, -0.2, 0.05])
+    assert f12.ndim == 1
+    y_ref = R.upfirdn2d(x, f12, up=2, padding=[6, 5, 6, 5], gain=4)
+    y = U.upfirdn2d(x.cuda(), f12.cuda(), up=2, padding=[6, 5, 6, 5], gain=4, impl="cuda")
+    assert _rel(y, y_ref) <= 1e-5
+    f4 = R.setup_filter([1, 3, 3, 1])
+    xc = x.cuda().contiguous(memory_format=torch.channels_last)
+    y = U.upfirdn2d(xc, f4.cuda(), up=2, padding=[2, 1, 2, 1], gain=4, impl="cuda")
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, R.upfirdn2d(x, f4, up=2, padding=[2, 1, 2, 1], gain=4)) <= 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float64])
+def test_other_dtypes(dtype):
+    U = _ops()
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(2, 4, 32, 32, generator=g).to(dtype)
+    f4 = R.setup_filter([1, 3, 3, 1])
+    for kw in (PATTERNS["A"], PATTERNS["B"], PATTERNS["B_bwd"]):
+        y_ref = R.upfirdn2d(x.double(), f4, **kw) if dtype == torch.float64 else R.upfirdn2d(x.float(), f4, **kw)
+        y = U.upfirdn2d(x.cuda(), f4.cuda(), impl="cuda", **kw)
+        assert y.dtype == dtype
+        tol = 1e-6 if dtype == torch.float64 else 2 * torch.finfo(dtype).eps
+        assert _rel(y, y_ref) <= tol
+
+
+def test_errors_and_empty():
+    U = _ops()
+    from viscoin_next_b200 import _lib
+    f4 = R.setup_filter([1, 3, 3, 1])
+    with pytest.raises(_lib.VcnError):
+        U.upfirdn2d(torch.zeros(1, 1, 4, 4), f4, impl="cuda")
+    e = torch.zeros(0, 3, 8, 8, device="cuda")
+    assert U.upfirdn2d(e, f4.cuda(), up=2, padding=[2, 1, 2, 1], impl="cuda").shape == (0, 3, 16, 16)
+    with pytest.raises(AssertionError):
+        U.upfirdn2d(torch.zeros(1, 1, 2, 2, device="cuda"), f4.cuda(), impl="cuda")  # empty output
+
+
+def test_full_size_roundtrip_properties():
+    """Config-2 sizes: pattern A on [8,128,257,257] and B on [8,3,128,128]: adjoint identity <U x, y> = <x, U^T y>
+    (size-independent; U^T is the swapped-factor call, upfirdn2d.py:246-261) and a strided pointwise check."""
+    U = _ops()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    f4 = R.setup_filter([1, 3, 3, 1]).cuda()
+    for shape, kw in (((8, 128, 257, 257), PATTERNS["A"]), ((8, 3, 128, 128), PATTERNS["B"]),
+                      ((4, 64, 256, 256), PATTERNS["B_bwd"])):
+        x = torch.randn(shape, device="cuda", generator=g).requires_grad_(True)
+        y = U.upfirdn2d(x, f4, impl="cuda", **kw)
+        w = torch.randn(y.shape, device="cuda", generator=g)
+        (xt,) = torch.autograd.grad(y, [x], w)
+        lhs = (y.detach().double() * w.double()).sum()
+        rhs = (x.detach().double() * xt.double()).sum()
+        assert abs(lhs - rhs).item() <= 1e-6 * max(abs(lhs).item(), 1.0) + 1e-3
+        # one plane against the oracle
+        xs = x.detach()[1:2, 5:6].cpu()
+        assert _rel(y.detach()[1:2, 5:6], R.upfirdn2d(xs, f4.cpu(), **kw)) <= 1e-5

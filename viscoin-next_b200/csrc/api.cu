@@ -20,6 +20,9 @@ int cuda_fail(cudaError_t e, const char* what) {
   return VCN_ERR_CUDA;
 }
 
+static unsigned long long g_launches = 0;
+void count_launch() { __atomic_fetch_add(&g_launches, 1ULL, __ATOMIC_RELAXED); }
+
 int sm_count() {
   static thread_local int cached_dev = -1, cached = 0;
   int dev = 0;
@@ -93,6 +96,8 @@ extern "C" {
 int vcn_abi_version(void) { return VCN_ABI_VERSION; }
 
 const char* vcn_last_error(void) { return vcn::g_err; }
+
+uint64_t vcn_launch_count(void) { return __atomic_load_n(&vcn::g_launches, __ATOMIC_RELAXED); }
 
 int vcn_device_info(int device, int* sm_count, int64_t* l2_bytes, int* cc_major, int* cc_minor) {
   int n = 0;

@@ -15,6 +15,7 @@
 namespace vcn {
 void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
+void count_launch();  // bumps the process-wide kernel-launch counter read by vcn_launch_count()
 }  // namespace vcn
 
 #define VCN_REQUIRE(cond, ...)       \
@@ -35,6 +36,7 @@ int cuda_fail(cudaError_t e, const char* what);
   do {                                                           \
     cudaError_t e__ = cudaGetLastError();                        \
     if (e__ != cudaSuccess) return vcn::cuda_fail(e__, name);    \
+    vcn::count_launch();                                         \
   } while (0)
 
 namespace vcn {
