@@ -154,5 +154,5 @@ def test_full_size_roundtrip_properties():
         rhs = (x.detach().double() * xt.double()).sum()
         assert abs(lhs - rhs).item() <= 1e-6 * max(abs(lhs).item(), 1.0) + 1e-3
         # one plane against the oracle
-        xs = x.detach()[1:2, 5:6].cpu()
-        assert _rel(y.detach()[1:2, 5:6], R.upfirdn2d(xs, f4.cpu(), **kw)) <= 1e-5
+        xs = x.detach()[1:2, 1:2].cpu()
+        assert _rel(y.detach()[1:2, 1:2], R.upfirdn2d(xs, f4.cpu(), **kw)) <= 1e-5

@@ -55,6 +55,13 @@ static EncodeTiledFn encode_fn() {
 int make_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, const uint64_t* dims,
                     const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides,
                     int swizzle_128b) {
+  // Autograd worker threads may reach this point before the runtime has bound the primary context to the thread;
+  // the driver entry point needs one (CUDA_ERROR_INVALID_CONTEXT otherwise).
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(nullptr);
+    ctx_bound = true;
+  }
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("cuTensorMapEncodeTiled is not available from the driver");

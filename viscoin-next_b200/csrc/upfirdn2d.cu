@@ -291,7 +291,16 @@ int launch_tile(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st) {
   const int planes = a.n * a.c;
   CUtensorMap tmap;
   memset(&tmap, 0, sizeof(tmap));
-  g.use_tma = aligned16(a.x) && ((size_t)a.in_w * e) % 16 == 0 && g.iwp <= 256 && g.ih <= 256 && g.tp <= 256;
+  // TMA needs the innermost box coordinate to be a multiple of 16 bytes (measured on B200: an unaligned inner
+  // coordinate raises cudaErrorIllegalInstruction; negative / out-of-range coordinates are fine and zero-fill).
+  // ix0 of tile bx is ceil((bx*tw*DOWN - padx0) / UP); it is aligned for every bx iff it is for bx = 0 and 1.
+  constexpr int V = Vec16<T>::N;
+  auto ix0_of = [&](int bx) {
+    const int m = bx * g.tw * DOWN - a.padx0;
+    return m >= 0 ? (m + UP - 1) / UP : -((-m) / UP);
+  };
+  const bool coord_ok = (((ix0_of(0) % V) + V) % V == 0) && (((ix0_of(1) % V) + V) % V == 0);
+  g.use_tma = coord_ok && aligned16(a.x) && ((size_t)a.in_w * e) % 16 == 0 && g.iwp <= 256 && g.ih <= 256 && g.tp <= 256;
   if (g.use_tma) {
     const uint64_t dims[3] = {(uint64_t)a.in_w, (uint64_t)a.in_h, (uint64_t)planes};
     const uint64_t strides[2] = {(uint64_t)a.in_w * e, (uint64_t)a.in_w * a.in_h * e};

@@ -136,7 +136,11 @@ class _BiasAct(torch.autograd.Function):
         trivial = act_idx == 1 and gain == 1 and clamp < 0 and b is None
         y = x if trivial else _call(x, b, None, None, None, 0, dim, act_idx, alpha, gain, clamp, False)[0]
         keep_x = "x" in ref or has_2nd
-        ctx.save_for_backward(x if keep_x else None, b if keep_x else None, y if "y" in ref else None)
+        # The reference's CUDA wiring saves y only for ref='y' activations (bias_act.py:154-157), which leaves the
+        # clamp mask of `linear` without a yref; the impl='ref' path (the parity target) masks, so y is kept
+        # whenever a clamp is active.
+        keep_y = "y" in ref or (clamp >= 0 and "x" not in ref)
+        ctx.save_for_backward(x if keep_x else None, b if keep_x else None, y if keep_y else None)
         ctx.cfg = (dim, act_idx, alpha, gain, clamp, ref, has_2nd, trivial or (act_idx == 1 and gain == 1 and clamp < 0))
         ctx.has_b = b is not None
         return y
@@ -151,7 +155,8 @@ class _BiasAct(torch.autograd.Function):
             if passthrough:
                 dx = dy
                 if need_db:
-                    db = dy.sum([i for i in range(dy.ndim) if i != dim])
+                    other = [i for i in range(dy.ndim) if i != dim]
+                    db = dy.sum(other) if other else dy
             else:
                 dx, db = _BiasActGrad.apply(dy, x, b, y, dim, act_idx, alpha, gain, clamp, has_2nd, need_db)
                 if not need_db:
