@@ -93,7 +93,48 @@ int vcn_upfirdn2d(const void* x, const float* f, void* y, int dtype,
                   int padx0, int padx1, int pady0, int pady1, int flip, float gain,
                   const vcn_upfirdn2d_epilogue* epi, void* stream);
 
-/* @@MODCONV@@ */
+/* ---- modulated convolution -----------------------------------------------------------------
+ * Replaces the convolution under `modulated_conv2d` (training/networks.py:27-84), i.e. the ATen/cuDNN calls of
+ * conv2d_gradfix.py:38,43 reached through conv2d_resample.py:59-154, with a TMA-fed tcgen05/TMEM implicit GEMM.
+ * Formulation = the reference's non-fused branch (networks.py:63-72), proven equal to the fused one (SURVEY
+ * App. B):  xhat = x * s[n,ci]  ->  shared-weight convolution  ->  * d[n,co] + noise  ->  bias_act.
+ *
+ *   vcn_modulate_pack   x (any strides, f32/f16/bf16) * styles[n,ci] -> xhat, bf16 NHWC [n,h,w,cin_pad]
+ *                       (cin_pad = cin rounded up to 8; pad channels are written as 0)
+ *   vcn_pack_weights    W [cout,cin,kh,kw] (f32/bf16, dense) -> wt bf16 [kh*kw][rows][cols_pad] K-major per tap
+ *                       (rows,cols) = (cout,cin), or (cin,cout) with transpose_io (input-gradient GEMM); optional
+ *                       wsq[cout,cin] = sum_k W^2 (fp32) for the demodulation coefficients
+ *   vcn_demod_coefs     d[n,co] = rsqrt(sum_ci (s[n,ci])^2 * wsq[co,ci] + 1e-8)       (networks.py:55-58)
+ *   vcn_conv_igemm      the implicit GEMM; accumulates in fp32 (TMEM), operands bf16
+ */
+typedef enum {
+  VCN_CONV_FPROP = 0,   /* stride-1 correlation, padding (kh/2, kw/2): y[oy,ox] = sum x[oy+ky-ph, ox+kx-pw] W[ky,kx] */
+  VCN_CONV_TCONV2 = 1,  /* 3x3 stride-2 transposed conv, no padding: y[2i+ky, 2j+kx] += x[i,j] W[ky,kx]; out (2h+1, 2w+1)
+                           (conv2d_resample.py:125-138 with flip_weight=False) */
+  VCN_CONV_DGRAD = 2    /* stride-1 correlation with the spatially flipped taps (input gradient of FPROP when wt was
+                           packed with transpose_io) */
+} vcn_conv_kind;
+
+typedef struct {
+  int kind;                 /* vcn_conv_kind */
+  int n, h, w;              /* xhat is bf16 NHWC [n, h, w, cin_pad] */
+  int cin_pad;              /* multiple of 8 */
+  int cout;                 /* rows of wt per tap */
+  int kh, kw;               /* 1x1 or 3x3 (TCONV2: 3x3) */
+  int out_h, out_w;         /* must match the kind: (h, w) or (2h+1, 2w+1) */
+  int y_dtype;              /* VCN_F32 / VCN_BF16 / VCN_F16 */
+  int64_t ys[4];            /* element strides of y for (n, c, h, w): NCHW, channels_last or padded pitch */
+} vcn_conv_desc;
+
+int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat,
+                      int n, int cin, int cin_pad, int h, int w, void* stream);
+int vcn_pack_weights(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io,
+                     void* wt, int cols_pad, float* wsq, void* stream);
+int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int cin, int cout, void* stream);
+/* epi (may be NULL) reuses vcn_upfirdn2d_epilogue: acc * scale[n,co] + noise[n?,oy,ox], then bias_act. */
+int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_desc* desc,
+                   const vcn_upfirdn2d_epilogue* epi, void* stream);
+
 
 #ifdef __cplusplus
 }

@@ -28,6 +28,17 @@ class UpfirdnEpilogue(_c.Structure):
     ]
 
 
+class ConvDesc(_c.Structure):
+    """vcn_conv_desc"""
+
+    _fields_ = [
+        ("kind", _i), ("n", _i), ("h", _i), ("w", _i), ("cin_pad", _i), ("cout", _i), ("kh", _i), ("kw", _i),
+        ("out_h", _i), ("out_w", _i), ("y_dtype", _i), ("ys", _i64 * 4),
+    ]
+
+
+CONV_FPROP, CONV_TCONV2, CONV_DGRAD = 0, 1, 2
+
 # name -> (restype, argtypes); must list every symbol include/vcn_b200.h declares (tests check this).
 SIGNATURES = {
     "vcn_abi_version": (_i, []),
@@ -38,6 +49,10 @@ SIGNATURES = {
     "vcn_bias_act": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _f, _f, _i64, _i64, _i64, _vp]),
     "vcn_upfirdn2d": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _c.POINTER(_i64 * 4), _i, _i, _c.POINTER(_i64 * 4),
                            _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _c.POINTER(UpfirdnEpilogue), _vp]),
+    "vcn_modulate_pack": (_i, [_vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vcn_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
+    "vcn_demod_coefs": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "vcn_conv_igemm": (_i, [_vp, _vp, _vp, _c.POINTER(ConvDesc), _c.POINTER(UpfirdnEpilogue), _vp]),
 }
 
 _lock = threading.Lock()

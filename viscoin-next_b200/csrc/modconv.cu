@@ -1,0 +1,346 @@
+// modconv.cu - the convolution of modulated_conv2d as a TMA-fed tcgen05 / TMEM implicit GEMM (sm_100a).
+//
+// Replaces the ATen/cuDNN convolution under training/networks.py:27-84 (conv2d_resample.py:59-154 ->
+// conv2d_gradfix.py:38,43).  GEMM view, per CTA tile:
+//   D[128 pixels, N_TILE out-channels] (fp32, TMEM) = sum over taps t, channel blocks cb of
+//        A_t,cb[128 pixels, 64 ch] (bf16 smem, K-major, 128B swizzle)  x  B_t,cb[N_TILE, 64 ch]^T (bf16 smem, K-major)
+//   A = one TMA box (64ch, TW, TH, TN) of the NHWC activation at the tap's pixel shift: out-of-bounds zero fill IS the
+//       convolution's zero padding (negative coordinates included), TW*TH*TN = 128 rows.
+//   B = one TMA box (64ch, N_TILE, 1) of the packed weights [tap][cout][cin].
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, tcgen05.mma
+// cta_group::1 kind::f16, M=128), warps 2..5 = epilogue (tcgen05.ld of their TMEM lane quarter, then
+// demodulation * d[n,co] + noise, bias + activation + gain + clamp, store).  smem ring of S stages with
+// full/empty mbarriers; tcgen05.commit releases a stage and, after the last k-block, hands TMEM to the epilogue.
+// A "plan" lists the taps; taps are partitioned into up to 4 accumulator groups (TMEM column ranges): the plain
+// convolution has one group of kh*kw taps, the stride-2 transposed convolution has its 4 output phases as groups
+// (4+2+2+1 taps) so that it costs exactly the reference's FLOPs (2*9*Cin*Cout per INPUT pixel).
+#include <string.h>
+
+#include "act_math.cuh"
+#include "umma.cuh"
+
+namespace vcn {
+namespace {
+
+constexpr int kBlockM = 128;  // pixels per CTA tile = UMMA M
+constexpr int kBlockK = 64;   // bf16 channels per k-block = one 128-byte swizzle span
+constexpr int kUmmaK = 16;
+constexpr int kMaxTaps = 9;
+constexpr int kMaxGroups = 4;
+constexpr int kThreads = 192;
+constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
+
+struct ConvTap {
+  int dy, dx;  // pixel shift of the A tile in the M grid
+  int wtap;    // index of the tap in the packed weights
+  int group;   // accumulator group
+};
+
+struct IgemmArgs {
+  ConvTap taps[kMaxTaps];
+  int num_taps, num_groups;
+  int g_oy[kMaxGroups], g_ox[kMaxGroups];  // output pixel = (py * o_mul + g_oy, px * o_mul + g_ox)
+  int o_mul;
+  int grid_h, grid_w;  // extent of the M grid (pixels that own accumulator rows)
+  int n, cout, out_h, out_w;
+  int tw, th, tn, tiles_w, tiles_h;
+  int n_tile, kblocks_c, stages, tmem_cols;
+  void* y;
+  int y_dtype;
+  int64_t ys[4];
+  int vec_store;  // y is channels-fastest and 16-byte friendly
+  const float* scale;
+  const float* noise;
+  int64_t noise_stride_n;
+  const float* bias;
+  int act;
+  float alpha, act_gain, clamp;
+};
+
+template <typename T> __device__ __forceinline__ T cvt_out(float v);
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <typename T>
+__device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_t (&acc)[32], int n, int oy, int ox,
+                                               int co0, float noise) {
+  // 32 consecutive output channels co0.. of one pixel
+  T* ybase = static_cast<T*>(a.y) + (int64_t)n * a.ys[0] + (int64_t)oy * a.ys[2] + (int64_t)ox * a.ys[3];
+  const float* scale = a.scale ? a.scale + (int64_t)n * a.cout : nullptr;
+  float v[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int co = co0 + j;
+    float r = __uint_as_float(acc[j]);
+    if (co < a.cout) {
+      if (scale) r *= scale[co];
+      r += noise;
+      if (a.act) {
+        if (a.bias) r += a.bias[co];
+        r = act_eval<float, 0>(r, 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+      }
+    }
+    v[j] = r;
+  }
+  if (a.vec_store && co0 + 32 <= a.cout) {
+    constexpr int V = 16 / sizeof(T);
+#pragma unroll
+    for (int j = 0; j < 32; j += V) {
+      Vec16<T> o;
+#pragma unroll
+      for (int k = 0; k < V; ++k) o.v[k] = cvt_out<T>(v[j + k]);
+      *reinterpret_cast<Vec16<T>*>(ybase + (co0 + j)) = o;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int co = co0 + j;
+      if (co < a.cout) ybase[(int64_t)co * a.ys[1]] = cvt_out<T>(v[j]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ IgemmArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  // 1024-byte alignment: the 128B swizzle pattern repeats every 8 rows = 1024 bytes
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t b_bytes = (uint32_t)a.n_tile * kBlockK * 2;
+  const uint32_t stage_bytes = kABytes + b_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)a.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + a.stages;
+  uint64_t* tmem_full_bar = empty_bar + a.stages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int mt = blockIdx.x;
+  const int tile_wi = mt % a.tiles_w; mt /= a.tiles_w;
+  const int tile_hi = mt % a.tiles_h;
+  const int tile_ni = mt / a.tiles_h;
+  const int x0 = tile_wi * a.tw, y0 = tile_hi * a.th, n0 = tile_ni * a.tn;
+  const int co_tile0 = blockIdx.y * a.n_tile;
+  const int num_kb = a.num_taps * a.kblocks_c;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_ptr_smem, (uint32_t)a.tmem_cols);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int it = 0; it < num_kb; ++it) {
+        const int s = it % a.stages;
+        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+        mbar_wait(empty_bar + s, ph ^ 1u);
+        const int t = it / a.kblocks_c, cb = it - t * a.kblocks_c;
+        const ConvTap tap = a.taps[t];
+        unsigned char* sa = smem + (size_t)s * stage_bytes;
+        mbar_expect_tx(full_bar + s, stage_bytes);
+        tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, x0 + tap.dx, y0 + tap.dy, n0);
+        tma_load_3d(sa + kABytes, &tmap_b, full_bar + s, cb * kBlockK, co_tile0, tap.wtap);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16_f32(kBlockM, a.n_tile);
+      int cur_group = -1;
+      for (int it = 0; it < num_kb; ++it) {
+        const int s = it % a.stages;
+        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
+        const int t = it / a.kblocks_c;
+        const int g = a.taps[t].group;
+        mbar_wait(full_bar + s, ph);
+        tcgen05_fence_after();
+        const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+        const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + kABytes);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(g * a.n_tile);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
+          umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (g == cur_group || k > 0) ? 1u : 0u);
+        }
+        cur_group = g;
+        umma_commit(empty_bar + s);
+      }
+      umma_commit(tmem_full_bar);
+    }
+  } else {
+    // ===== epilogue: warps 2..5 own TMEM lane quarters (warp % 4) =====
+    const int q = warp & 3;
+    const int m = q * 32 + lane;
+    const int tw_i = m % a.tw;
+    const int th_i = (m / a.tw) % a.th;
+    const int tn_i = m / (a.tw * a.th);
+    const int px = x0 + tw_i, py = y0 + th_i, n = n0 + tn_i;
+    const bool row_ok = n < a.n && py < a.grid_h && px < a.grid_w;
+    mbar_wait(tmem_full_bar, 0);
+    tcgen05_fence_after();
+    for (int g = 0; g < a.num_groups; ++g) {
+      const int oy = py * a.o_mul + a.g_oy[g], ox = px * a.o_mul + a.g_ox[g];
+      const bool ok = row_ok && oy < a.out_h && ox < a.out_w;
+      float noise = 0.f;
+      if (ok && a.noise) noise = a.noise[(int64_t)n * a.noise_stride_n + (int64_t)oy * a.out_w + ox];
+      for (int c = 0; c < a.n_tile; c += 32) {
+        if (co_tile0 + c >= a.cout) break;  // warp-uniform
+        uint32_t acc[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * a.n_tile + c);
+        if (a.n_tile - c >= 32) {
+          tmem_ld_32x32(taddr, acc);
+        } else {  // n_tile is a multiple of 16: last half chunk
+          uint32_t h16[16];
+          tmem_ld_32x16(taddr, h16);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) { acc[j] = h16[j]; acc[16 + j] = 0u; }
+        }
+        tmem_ld_wait();
+        if (ok) {
+          if (a.y_dtype == VCN_F32) epilogue_store<float>(a, acc, n, oy, ox, co_tile0 + c, noise);
+          else if (a.y_dtype == VCN_BF16) epilogue_store<__nv_bfloat16>(a, acc, n, oy, ox, co_tile0 + c, noise);
+          else epilogue_store<__half>(a, acc, n, oy, ox, co_tile0 + c, noise);
+        }
+      }
+    }
+    tcgen05_fence_before();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+  }
+}
+
+inline int pow2_ceil(int v) {
+  int p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// (tw, th, tn) with tw*th*tn = 128 minimising the number of CTA tiles; ties -> wider rows
+void choose_tile(int gw, int gh, int n, int* tw, int* th, int* tn) {
+  int64_t best = -1;
+  for (int w = 128; w >= 1; w >>= 1) {
+    for (int h = 1; w * h <= 128; h <<= 1) {
+      const int nn = 128 / (w * h);
+      const int64_t tiles = (int64_t)((gw + w - 1) / w) * ((gh + h - 1) / h) * ((n + nn - 1) / nn);
+      if (best < 0 || tiles < best) { best = tiles; *tw = w; *th = h; *tn = nn; }
+    }
+  }
+}
+
+}  // namespace
+}  // namespace vcn
+
+extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_desc* d,
+                              const vcn_upfirdn2d_epilogue* epi, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(d != nullptr, "conv_igemm: desc must not be NULL");
+  VCN_REQUIRE(d->n >= 0 && d->h >= 1 && d->w >= 1 && d->cout >= 1, "conv_igemm: bad shape");
+  VCN_REQUIRE(d->cin_pad >= 8 && d->cin_pad % 8 == 0, "conv_igemm: cin_pad (%d) must be a positive multiple of 8", d->cin_pad);
+  VCN_REQUIRE((d->kh == 1 && d->kw == 1) || (d->kh == 3 && d->kw == 3), "conv_igemm: only 1x1 and 3x3 kernels (got %dx%d)",
+              d->kh, d->kw);
+  VCN_REQUIRE(d->y_dtype == VCN_F32 || d->y_dtype == VCN_BF16 || d->y_dtype == VCN_F16, "conv_igemm: bad output dtype %d",
+              d->y_dtype);
+  IgemmArgs a;
+  memset(&a, 0, sizeof(a));
+  const int kh = d->kh, kw = d->kw;
+  if (d->kind == VCN_CONV_FPROP || d->kind == VCN_CONV_DGRAD) {
+    VCN_REQUIRE(d->out_h == d->h && d->out_w == d->w, "conv_igemm: stride-1 output must be %dx%d", d->h, d->w);
+    for (int ky = 0; ky < kh; ++ky)
+      for (int kx = 0; kx < kw; ++kx) {
+        ConvTap& t = a.taps[a.num_taps++];
+        if (d->kind == VCN_CONV_FPROP) { t.dy = ky - kh / 2; t.dx = kx - kw / 2; }
+        else { t.dy = kh / 2 - ky; t.dx = kw / 2 - kx; }
+        t.wtap = ky * kw + kx;
+        t.group = 0;
+      }
+    a.num_groups = 1; a.o_mul = 1; a.grid_h = d->h; a.grid_w = d->w;
+  } else if (d->kind == VCN_CONV_TCONV2) {
+    VCN_REQUIRE(kh == 3 && kw == 3, "conv_igemm: transposed conv needs a 3x3 kernel");
+    VCN_REQUIRE(d->out_h == 2 * d->h + 1 && d->out_w == 2 * d->w + 1, "conv_igemm: transposed output must be %dx%d",
+                2 * d->h + 1, 2 * d->w + 1);
+    for (int g = 0; g < 4; ++g) {
+      const int pa = g >> 1, pb = g & 1;
+      a.g_oy[g] = pa; a.g_ox[g] = pb;
+      for (int ky = pa; ky < 3; ky += 2)
+        for (int kx = pb; kx < 3; kx += 2) {
+          ConvTap& t = a.taps[a.num_taps++];
+          t.dy = -(ky >> 1); t.dx = -(kx >> 1); t.wtap = ky * 3 + kx; t.group = g;
+        }
+    }
+    a.num_groups = 4; a.o_mul = 2; a.grid_h = d->h + 1; a.grid_w = d->w + 1;
+  } else {
+    set_error("conv_igemm: unknown kind %d", d->kind);
+    return VCN_ERR_INVALID;
+  }
+  if (d->n == 0) return VCN_OK;
+  VCN_REQUIRE(xhat && wt && y, "conv_igemm: xhat, wt and y must not be NULL");
+  VCN_REQUIRE(aligned16(xhat) && aligned16(wt), "conv_igemm: xhat and wt must be 16-byte aligned");
+
+  a.n = d->n; a.cout = d->cout; a.out_h = d->out_h; a.out_w = d->out_w;
+  choose_tile(a.grid_w, a.grid_h, d->n, &a.tw, &a.th, &a.tn);
+  a.tiles_w = (a.grid_w + a.tw - 1) / a.tw;
+  a.tiles_h = (a.grid_h + a.th - 1) / a.th;
+  const int tiles_n = (d->n + a.tn - 1) / a.tn;
+  const int max_tile = 512 / a.num_groups > 256 ? 256 : 512 / a.num_groups;
+  a.n_tile = (d->cout + 15) / 16 * 16;
+  if (a.n_tile > max_tile) a.n_tile = max_tile;
+  a.kblocks_c = (d->cin_pad + kBlockK - 1) / kBlockK;
+  a.tmem_cols = pow2_ceil(a.num_groups * a.n_tile);
+  if (a.tmem_cols < 32) a.tmem_cols = 32;
+  const size_t stage_bytes = kABytes + (size_t)a.n_tile * kBlockK * 2;
+  a.stages = (int)((200 * 1024) / stage_bytes);
+  if (a.stages > 8) a.stages = 8;
+  if (a.stages > a.num_taps * a.kblocks_c) a.stages = a.num_taps * a.kblocks_c;
+  if (a.stages < 1) a.stages = 1;
+  // more than 256 TMEM columns must never share an SM with a second CTA of this kernel (allocation would spin)
+  size_t smem = 1024 + (size_t)a.stages * stage_bytes + (2 * (size_t)a.stages + 1) * 8 + 16;
+  if (a.tmem_cols > 256 && smem < 120 * 1024) smem = 120 * 1024;
+
+  a.y = y; a.y_dtype = d->y_dtype;
+  for (int i = 0; i < 4; ++i) a.ys[i] = d->ys[i];
+  const size_t oe = dtype_size(d->y_dtype);
+  const int64_t vq = 16 / (int64_t)oe;
+  a.vec_store = d->ys[1] == 1 && aligned16(y) && d->ys[0] % vq == 0 && d->ys[2] % vq == 0 && d->ys[3] % vq == 0;
+  if (epi) {
+    a.scale = epi->scale; a.noise = epi->noise; a.noise_stride_n = epi->noise_stride_n; a.bias = epi->bias;
+    a.act = epi->act; a.alpha = epi->alpha; a.act_gain = epi->act_gain; a.clamp = epi->clamp;
+    VCN_REQUIRE(a.act == 0 || (a.act >= VCN_ACT_LINEAR && a.act <= VCN_ACT_SWISH), "conv_igemm: bad epilogue act %d", a.act);
+  }
+
+  CUtensorMap tmap_a, tmap_b;
+  {
+    const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
+    const uint64_t strides[3] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->w * d->cin_pad * 2,
+                                 (uint64_t)d->h * d->w * d->cin_pad * 2};
+    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)a.tw, (uint32_t)a.th, (uint32_t)a.tn};
+    const int rc = make_tensor_map(&tmap_a, VCN_BF16, 4, xhat, dims, strides, box, nullptr, 1);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)d->cin_pad, (uint64_t)d->cout, (uint64_t)(kh * kw)};
+    const uint64_t strides[2] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->cout * d->cin_pad * 2};
+    const uint32_t box[3] = {(uint32_t)kBlockK, (uint32_t)a.n_tile, 1u};
+    const int rc = make_tensor_map(&tmap_b, VCN_BF16, 3, wt, dims, strides, box, nullptr, 1);
+    if (rc) return rc;
+  }
+  VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)((int64_t)a.tiles_w * a.tiles_h * tiles_n), (unsigned)((d->cout + a.n_tile - 1) / a.n_tile));
+  conv_igemm_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, a);
+  VCN_LAUNCH_CHECK("conv_igemm_kernel");
+  return VCN_OK;
+}

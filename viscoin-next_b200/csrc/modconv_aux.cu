@@ -1,0 +1,212 @@
+// modconv_aux.cu - operand preparation for the tcgen05 implicit GEMM of modconv.cu (all memory-bound).
+//   modulate_pack : x[n,ci,h,w] (any strides, f32/f16/bf16) * styles[n,ci] -> xhat bf16 NHWC [n,h,w,cin_pad]
+//                   (networks.py:64 `x = x * styles.reshape(N,-1,1,1)` fused with the layout/dtype change the tensor
+//                   cores need; a 64-channel x 32-pixel tile is transposed through shared memory so that both the
+//                   NCHW reads and the NHWC writes are full 128-byte lines)
+//   pack_weights  : W[cout,cin,kh,kw] -> wt bf16 [tap][rows][cols_pad] (+ wsq[cout,cin] = sum_k W^2)
+//   demod_coefs   : d[n,co] = rsqrt(sum_ci s^2 wsq + 1e-8)  (networks.py:55-58 without materialising w*s)
+#include "common.cuh"
+
+namespace vcn {
+namespace {
+
+template <typename T>
+__global__ void __launch_bounds__(256) modulate_pack_kernel(const T* __restrict__ x, int64_t xs_n, int64_t xs_c,
+                                                            int64_t xs_h, int64_t xs_w, const float* __restrict__ styles,
+                                                            __nv_bfloat16* __restrict__ xhat, int cin, int cin_pad, int h,
+                                                            int w) {
+  // grid: (ceil(h*w/32), ceil(cin_pad/64), n); tile = 64 channels x 32 pixels
+  __shared__ float tile[64][33];
+  const int n = blockIdx.z, c0 = blockIdx.y * 64, p0 = blockIdx.x * 32;
+  const int hw = h * w;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* xn = x + (int64_t)n * xs_n;
+  const int p = p0 + lane;
+  const int py = p / w, px = p - py * w;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = c0 + warp * 8 + i;
+    float v = 0.f;
+    if (c < cin && p < hw) {
+      v = to_acc<T>(xn[(int64_t)c * xs_c + (int64_t)py * xs_h + (int64_t)px * xs_w]);
+      if (styles) v *= styles[(int64_t)n * cin + c];
+    }
+    tile[warp * 8 + i][lane] = v;
+  }
+  __syncthreads();
+  // each warp writes 4 pixels; a lane owns channels (2*lane, 2*lane+1): 128 contiguous bytes per pixel
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int pp = warp * 4 + i;
+    const int gp = p0 + pp;
+    const int c = c0 + 2 * lane;
+    if (gp < hw && c < cin_pad) {
+      const __nv_bfloat162 v = __floats2bfloat162_rn(tile[2 * lane][pp], tile[2 * lane + 1][pp]);
+      *reinterpret_cast<__nv_bfloat162*>(xhat + ((int64_t)n * hw + gp) * cin_pad + c) = v;
+    }
+  }
+}
+
+// channels-fastest input (xs_c == 1): plain vectorisable elementwise pass, 2 channels per thread
+template <typename T>
+__global__ void __launch_bounds__(256) modulate_pack_cl_kernel(const T* __restrict__ x, int64_t xs_n, int64_t xs_h,
+                                                               int64_t xs_w, const float* __restrict__ styles,
+                                                               __nv_bfloat16* __restrict__ xhat, int n_img, int cin,
+                                                               int cin_pad, int h, int w) {
+  const int64_t pairs = (int64_t)cin_pad / 2;
+  const int64_t total = (int64_t)n_img * h * w * pairs;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % pairs) * 2;
+    int64_t r = i / pairs;
+    const int px = (int)(r % w); r /= w;
+    const int py = (int)(r % h);
+    const int n = (int)(r / h);
+    const T* src = x + n * xs_n + py * xs_h + px * xs_w + c;
+    float v0 = 0.f, v1 = 0.f;
+    if (c < cin) v0 = to_acc<T>(src[0]) * (styles ? styles[(int64_t)n * cin + c] : 1.f);
+    if (c + 1 < cin) v1 = to_acc<T>(src[1]) * (styles ? styles[(int64_t)n * cin + c + 1] : 1.f);
+    *reinterpret_cast<__nv_bfloat162*>(xhat + (((int64_t)n * h + py) * w + px) * cin_pad + c) = __floats2bfloat162_rn(v0, v1);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) pack_weights_kernel(const T* __restrict__ w, int cout, int cin, int taps,
+                                                           int transpose_io, __nv_bfloat16* __restrict__ wt, int rows,
+                                                           int cols, int cols_pad) {
+  // one thread per (tap, row, col_pad) element of wt
+  const int64_t total = (int64_t)taps * rows * cols_pad;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int col = (int)(i % cols_pad);
+    int64_t r = i / cols_pad;
+    const int row = (int)(r % rows);
+    const int tap = (int)(r / rows);
+    float v = 0.f;
+    if (col < cols) {
+      const int co = transpose_io ? col : row, ci = transpose_io ? row : col;
+      v = to_acc<T>(w[((int64_t)co * cin + ci) * taps + tap]);
+    }
+    wt[i] = __float2bfloat16_rn(v);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) weight_sq_kernel(const T* __restrict__ w, int64_t pairs, int taps,
+                                                        float* __restrict__ wsq) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= pairs) return;
+  float acc = 0.f;
+  for (int t = 0; t < taps; ++t) {
+    const float v = to_acc<T>(w[i * taps + t]);
+    acc = fmaf(v, v, acc);
+  }
+  wsq[i] = acc;
+}
+
+// one warp per (n, co): d = rsqrt(sum_ci s[n,ci]^2 * wsq[co,ci] + 1e-8)
+__global__ void __launch_bounds__(256) demod_coefs_kernel(const float* __restrict__ styles, const float* __restrict__ wsq,
+                                                          float* __restrict__ d, int n, int cin, int cout) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (gw >= n * cout) return;
+  const int in = gw / cout, co = gw - in * cout;
+  const float* s = styles + (int64_t)in * cin;
+  const float* q = wsq + (int64_t)co * cin;
+  float acc = 0.f;
+  for (int c = lane; c < cin; c += 32) acc = fmaf(s[c] * s[c], q[c], acc);
+  acc = warp_sum(acc);
+  if (lane == 0) d[gw] = rsqrtf(acc + 1e-8f);
+}
+
+template <typename T>
+int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* xhat, int n, int cin, int cin_pad, int h,
+                 int w, cudaStream_t st) {
+  const T* px = static_cast<const T*>(x);
+  __nv_bfloat16* po = static_cast<__nv_bfloat16*>(xhat);
+  if (xs[1] == 1 && cin > 1 && cin % 2 == 0) {
+    const int64_t total = (int64_t)n * h * w * (cin_pad / 2);
+    int64_t grid = (total + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (grid > cap) grid = cap;
+    modulate_pack_cl_kernel<T><<<(unsigned)grid, 256, 0, st>>>(px, xs[0], xs[2], xs[3], styles, po, n, cin, cin_pad, h, w);
+    VCN_LAUNCH_CHECK("modulate_pack_cl_kernel");
+    return VCN_OK;
+  }
+  dim3 grid((unsigned)((h * w + 31) / 32), (unsigned)((cin_pad + 63) / 64), (unsigned)n);
+  modulate_pack_kernel<T><<<grid, 256, 0, st>>>(px, xs[0], xs[1], xs[2], xs[3], styles, po, cin, cin_pad, h, w);
+  VCN_LAUNCH_CHECK("modulate_pack_kernel");
+  return VCN_OK;
+}
+
+template <typename T>
+int run_pack(const void* w, int cout, int cin, int taps, int transpose_io, void* wt, int cols_pad, float* wsq,
+             cudaStream_t st) {
+  const int rows = transpose_io ? cin : cout, cols = transpose_io ? cout : cin;
+  if (wt) {
+    const int64_t total = (int64_t)taps * rows * cols_pad;
+    int64_t grid = (total + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (grid > cap) grid = cap;
+    pack_weights_kernel<T><<<(unsigned)grid, 256, 0, st>>>(static_cast<const T*>(w), cout, cin, taps, transpose_io,
+                                                          static_cast<__nv_bfloat16*>(wt), rows, cols, cols_pad);
+    VCN_LAUNCH_CHECK("pack_weights_kernel");
+  }
+  if (wsq) {
+    const int64_t pairs = (int64_t)cout * cin;
+    weight_sq_kernel<T><<<(unsigned)((pairs + 255) / 256), 256, 0, st>>>(static_cast<const T*>(w), pairs, taps, wsq);
+    VCN_LAUNCH_CHECK("weight_sq_kernel");
+  }
+  return VCN_OK;
+}
+
+}  // namespace
+}  // namespace vcn
+
+extern "C" {
+
+int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat, int n, int cin,
+                      int cin_pad, int h, int w, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && cin >= 1 && h >= 1 && w >= 1, "modulate_pack: bad shape [%d,%d,%d,%d]", n, cin, h, w);
+  VCN_REQUIRE(cin_pad >= cin && cin_pad % 8 == 0, "modulate_pack: cin_pad (%d) must be a multiple of 8 and >= cin (%d)",
+              cin_pad, cin);
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(x && xhat && xs, "modulate_pack: x, xs and xhat must not be NULL");
+  VCN_REQUIRE((int64_t)n * h * w * cin_pad <= 0x7fffffffLL * 4, "modulate_pack: tensor too large");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (x_dtype) {
+    case VCN_F32: return run_modulate<float>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+    case VCN_F16: return run_modulate<__half>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+    case VCN_BF16: return run_modulate<__nv_bfloat16>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+  }
+  set_error("modulate_pack: unsupported dtype %d", x_dtype);
+  return VCN_ERR_INVALID;
+}
+
+int vcn_pack_weights(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io, void* wt,
+                     int cols_pad, float* wsq, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(w != nullptr, "pack_weights: w must not be NULL");
+  VCN_REQUIRE(cout >= 1 && cin >= 1 && kh >= 1 && kw >= 1, "pack_weights: bad shape [%d,%d,%d,%d]", cout, cin, kh, kw);
+  const int cols = transpose_io ? cout : cin;
+  if (wt) VCN_REQUIRE(cols_pad >= cols && cols_pad % 8 == 0, "pack_weights: cols_pad (%d) must be a multiple of 8 >= %d", cols_pad, cols);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (w_dtype) {
+    case VCN_F32: return run_pack<float>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+    case VCN_F16: return run_pack<__half>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+    case VCN_BF16: return run_pack<__nv_bfloat16>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+  }
+  set_error("pack_weights: unsupported dtype %d", w_dtype);
+  return VCN_ERR_INVALID;
+}
+
+int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int cin, int cout, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && cin >= 1 && cout >= 1, "demod_coefs: bad shape");
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(styles && wsq && d, "demod_coefs: NULL pointer");
+  const int64_t threads = (int64_t)n * cout * 32;
+  demod_coefs_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(styles, wsq, d, n, cin, cout);
+  VCN_LAUNCH_CHECK("demod_coefs_kernel");
+  return VCN_OK;
+}
+
+}  // extern "C"
