@@ -111,8 +111,10 @@ typedef enum {
   VCN_CONV_FPROP = 0,   /* stride-1 correlation, padding (kh/2, kw/2): y[oy,ox] = sum x[oy+ky-ph, ox+kx-pw] W[ky,kx] */
   VCN_CONV_TCONV2 = 1,  /* 3x3 stride-2 transposed conv, no padding: y[2i+ky, 2j+kx] += x[i,j] W[ky,kx]; out (2h+1, 2w+1)
                            (conv2d_resample.py:125-138 with flip_weight=False) */
-  VCN_CONV_DGRAD = 2    /* stride-1 correlation with the spatially flipped taps (input gradient of FPROP when wt was
+  VCN_CONV_DGRAD = 2,   /* stride-1 correlation with the spatially flipped taps (input gradient of FPROP when wt was
                            packed with transpose_io) */
+  VCN_CONV_SCONV2 = 3   /* 3x3 stride-2 correlation, no padding: y[i,j] = sum x[2i+ky, 2j+kx] W[ky,kx]; (2h+1, 2w+1) -> (h, w)
+                           (input gradient of TCONV2 when wt was packed with transpose_io) */
 } vcn_conv_kind;
 
 typedef struct {
@@ -121,7 +123,7 @@ typedef struct {
   int cin_pad;              /* multiple of 8 */
   int cout;                 /* rows of wt per tap */
   int kh, kw;               /* 1x1 or 3x3 (TCONV2: 3x3) */
-  int out_h, out_w;         /* must match the kind: (h, w) or (2h+1, 2w+1) */
+  int out_h, out_w;         /* must match the kind: (h, w), (2h+1, 2w+1) or ((h-1)/2, (w-1)/2) */
   int y_dtype;              /* VCN_F32 / VCN_BF16 / VCN_F16 */
   int64_t ys[4];            /* element strides of y for (n, c, h, w): NCHW, channels_last or padded pitch */
 } vcn_conv_desc;
@@ -134,6 +136,23 @@ int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int 
 /* epi (may be NULL) reuses vcn_upfirdn2d_epilogue: acc * scale[n,co] + noise[n?,oy,ox], then bias_act. */
 int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_desc* desc,
                    const vcn_upfirdn2d_epilogue* epi, void* stream);
+
+/* Backward of the (fused) layer  y = bias_act(conv(x*s, W) * d + noise, b)  w.r.t. x and s (the reference gets these
+ * from autograd over networks.py:63-72 + bias_act.py:160-175; closed form verified in SURVEY App. B):
+ *   vcn_modconv_bwd_pack    dz = bias_act'(dy; y) (epi->act: 0 none, linear, or lrelu), gsum[n,c] += sum_p dz*(y0*d),
+ *                           db[c] += sum_p dz, dy0 = dz * d[n,c] -> bf16 NHWC [n,h,w,c_pad] (operand of the DGRAD /
+ *                           SCONV2 GEMM).  epi->scale = d (NULL: no demodulation), epi->noise/bias as in forward.
+ *                           gsum and db accumulate with atomics: zero them first.
+ *   vcn_modconv_bwd_finish  dx = dxhat * s[n,c] in place (fp32), dsum[n,c] += sum_p dxhat * x
+ *   vcn_demod_grad          ds[n,i] += s[n,i] * sum_o (-gsum[n,o] d[n,o]^2) wsq[o,i]
+ */
+int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
+                         const vcn_upfirdn2d_epilogue* epi, void* dy0, float* gsum, float* db,
+                         int n, int c, int c_pad, int h, int w, void* stream);
+int vcn_modconv_bwd_finish(float* dxhat, const int64_t ds[4], const void* x, int x_dtype, const int64_t xs[4],
+                           const float* styles, float* dsum, int n, int c, int h, int w, void* stream);
+int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const float* dcoef, const float* wsq,
+                   int n, int cin, int cout, void* stream);
 
 
 #ifdef __cplusplus

@@ -37,7 +37,7 @@ class ConvDesc(_c.Structure):
     ]
 
 
-CONV_FPROP, CONV_TCONV2, CONV_DGRAD = 0, 1, 2
+CONV_FPROP, CONV_TCONV2, CONV_DGRAD, CONV_SCONV2 = 0, 1, 2, 3
 
 # name -> (restype, argtypes); must list every symbol include/vcn_b200.h declares (tests check this).
 SIGNATURES = {
@@ -53,6 +53,10 @@ SIGNATURES = {
     "vcn_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
     "vcn_demod_coefs": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "vcn_conv_igemm": (_i, [_vp, _vp, _vp, _c.POINTER(ConvDesc), _c.POINTER(UpfirdnEpilogue), _vp]),
+    "vcn_modconv_bwd_pack": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _c.POINTER(UpfirdnEpilogue),
+                                  _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vcn_modconv_bwd_finish": (_i, [_vp, _c.POINTER(_i64 * 4), _vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _vp]),
+    "vcn_demod_grad": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
 }
 
 _lock = threading.Lock()

@@ -41,6 +41,7 @@ struct IgemmArgs {
   int num_taps, num_groups;
   int g_oy[kMaxGroups], g_ox[kMaxGroups];  // output pixel = (py * o_mul + g_oy, px * o_mul + g_ox)
   int o_mul;
+  int a_mul;           // A-tile origin = tile origin * a_mul + tap shift (2 for the stride-2 convolution)
   int grid_h, grid_w;  // extent of the M grid (pixels that own accumulator rows)
   int n, cout, out_h, out_w;
   int tw, th, tn, tiles_w, tiles_h;
@@ -150,7 +151,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const ConvTap tap = a.taps[t];
         unsigned char* sa = smem + (size_t)s * stage_bytes;
         mbar_expect_tx(full_bar + s, stage_bytes);
-        tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, x0 + tap.dx, y0 + tap.dy, n0);
+        tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, x0 * a.a_mul + tap.dx, y0 * a.a_mul + tap.dy, n0);
         tma_load_3d(sa + kABytes, &tmap_b, full_bar + s, cb * kBlockK, co_tile0, tap.wtap);
       }
     }
@@ -269,6 +270,16 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
         t.group = 0;
       }
     a.num_groups = 1; a.o_mul = 1; a.grid_h = d->h; a.grid_w = d->w;
+  } else if (d->kind == VCN_CONV_SCONV2) {
+    VCN_REQUIRE(kh == 3 && kw == 3, "conv_igemm: stride-2 conv needs a 3x3 kernel");
+    VCN_REQUIRE(d->h >= 3 && d->w >= 3 && d->h % 2 == 1 && d->w % 2 == 1 && d->out_h == (d->h - 1) / 2 && d->out_w == (d->w - 1) / 2,
+                "conv_igemm: stride-2 conv maps (2h+1, 2w+1) to (h, w); got %dx%d -> %dx%d", d->h, d->w, d->out_h, d->out_w);
+    for (int ky = 0; ky < 3; ++ky)
+      for (int kx = 0; kx < 3; ++kx) {
+        ConvTap& t = a.taps[a.num_taps++];
+        t.dy = ky; t.dx = kx; t.wtap = ky * 3 + kx; t.group = 0;
+      }
+    a.num_groups = 1; a.o_mul = 1; a.grid_h = d->out_h; a.grid_w = d->out_w;
   } else if (d->kind == VCN_CONV_TCONV2) {
     VCN_REQUIRE(kh == 3 && kw == 3, "conv_igemm: transposed conv needs a 3x3 kernel");
     VCN_REQUIRE(d->out_h == 2 * d->h + 1 && d->out_w == 2 * d->w + 1, "conv_igemm: transposed output must be %dx%d",
@@ -291,6 +302,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   VCN_REQUIRE(xhat && wt && y, "conv_igemm: xhat, wt and y must not be NULL");
   VCN_REQUIRE(aligned16(xhat) && aligned16(wt), "conv_igemm: xhat and wt must be 16-byte aligned");
 
+  a.a_mul = d->kind == VCN_CONV_SCONV2 ? 2 : 1;
   a.n = d->n; a.cout = d->cout; a.out_h = d->out_h; a.out_w = d->out_w;
   choose_tile(a.grid_w, a.grid_h, d->n, &a.tw, &a.th, &a.tn);
   a.tiles_w = (a.grid_w + a.tw - 1) / a.tw;
@@ -327,8 +339,11 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
     const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
     const uint64_t strides[3] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->w * d->cin_pad * 2,
                                  (uint64_t)d->h * d->w * d->cin_pad * 2};
-    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)a.tw, (uint32_t)a.th, (uint32_t)a.tn};
-    const int rc = make_tensor_map(&tmap_a, VCN_BF16, 4, xhat, dims, strides, box, nullptr, 1);
+    // stride-2 gather: traversal strides (1,2,2,1); the box spans 2*TW x 2*TH input pixels and delivers TW x TH
+    const uint32_t m = (uint32_t)a.a_mul;
+    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)a.tw * m, (uint32_t)a.th * m, (uint32_t)a.tn};
+    const uint32_t estr[4] = {1u, m, m, 1u};
+    const int rc = make_tensor_map(&tmap_a, VCN_BF16, 4, xhat, dims, strides, box, estr, 1);
     if (rc) return rc;
   }
   {

@@ -5,6 +5,8 @@
 //                   NCHW reads and the NHWC writes are full 128-byte lines)
 //   pack_weights  : W[cout,cin,kh,kw] -> wt bf16 [tap][rows][cols_pad] (+ wsq[cout,cin] = sum_k W^2)
 //   demod_coefs   : d[n,co] = rsqrt(sum_ci s^2 wsq + 1e-8)  (networks.py:55-58 without materialising w*s)
+#include <string.h>
+
 #include "common.cuh"
 
 namespace vcn {
@@ -116,6 +118,138 @@ __global__ void __launch_bounds__(256) demod_coefs_kernel(const float* __restric
   if (lane == 0) d[gw] = rsqrtf(acc + 1e-8f);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// backward helpers
+// ---------------------------------------------------------------------------------------------------------
+struct BwdPackArgs {
+  const void* dy; const void* y;
+  int64_t dys[4], ys[4];
+  const float* noise; int64_t noise_stride_n;
+  const float* bias; const float* dcoef;
+  __nv_bfloat16* dy0; float* gsum; float* db;
+  int n, c, c_pad, h, w;
+  int act; float alpha, gain, clamp;
+};
+
+// dz = bias_act'(dy; y), r = act^-1(y) - bias - noise (= y0 * d), gsum[n,c] += sum_p dz*r, db[c] += sum_p dz,
+// dy0 = dz * d[n,c] -> bf16 NHWC.  Tile = 64 channels x 128 pixels; lanes run along pixels for the NCHW reads and
+// along channels for the NHWC writes (transposed through shared memory).
+template <typename T>
+__global__ void __launch_bounds__(256) modconv_bwd_pack_kernel(const BwdPackArgs a) {
+  __shared__ float tile[64][33];
+  const int n = blockIdx.z, c0 = blockIdx.y * 64;
+  const int hw = a.h * a.w;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* dyn = static_cast<const T*>(a.dy) + (int64_t)n * a.dys[0];
+  const T* yn = a.y ? static_cast<const T*>(a.y) + (int64_t)n * a.ys[0] : nullptr;
+  float gacc[8], bacc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) gacc[i] = bacc[i] = 0.f;
+  for (int sub = 0; sub < 4; ++sub) {
+    const int p0 = (blockIdx.x * 4 + sub) * 32;
+    if (p0 >= hw) break;  // block-uniform
+    const int p = p0 + lane;
+    const int py = p / a.w, px = p - py * a.w;
+    float nz = 0.f;
+    if (a.noise && p < hw) nz = a.noise[(int64_t)n * a.noise_stride_n + p];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = c0 + warp * 8 + i;
+      float out = 0.f;
+      if (c < a.c && p < hw) {
+        const float dyv = to_acc<T>(dyn[(int64_t)c * a.dys[1] + (int64_t)py * a.dys[2] + (int64_t)px * a.dys[3]]);
+        const float yv = yn ? to_acc<T>(yn[(int64_t)c * a.ys[1] + (int64_t)py * a.ys[2] + (int64_t)px * a.ys[3]]) : 0.f;
+        float dz = dyv, r = yv;
+        if (a.act) {
+          // first derivative of bias_act keyed on the stored output (bias_act.cu:48,72,141)
+          const float yy = yv / a.gain;
+          dz = (a.act == VCN_ACT_LRELU && !(yy > 0.f)) ? dyv * a.alpha : dyv;
+          dz *= a.gain;
+          if (a.clamp >= 0.f && !(yv > -a.clamp && yv < a.clamp)) dz = 0.f;
+          r = (a.act == VCN_ACT_LRELU && !(yy > 0.f)) ? yy / a.alpha : yy;
+          if (a.bias) r -= a.bias[c];
+        }
+        r -= nz;
+        gacc[i] = fmaf(dz, r, gacc[i]);
+        bacc[i] += dz;
+        out = a.dcoef ? dz * a.dcoef[(int64_t)n * a.c + c] : dz;
+      }
+      tile[warp * 8 + i][lane] = out;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int pp = warp * 4 + i;
+      const int gp = p0 + pp;
+      const int c = c0 + 2 * lane;
+      if (gp < hw && c < a.c_pad)
+        *reinterpret_cast<__nv_bfloat162*>(a.dy0 + ((int64_t)n * hw + gp) * a.c_pad + c) =
+            __floats2bfloat162_rn(tile[2 * lane][pp], tile[2 * lane + 1][pp]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = c0 + warp * 8 + i;
+    const float g = warp_sum(gacc[i]), b = warp_sum(bacc[i]);
+    if (lane == 0 && c < a.c) {
+      if (a.gsum) atomicAdd(a.gsum + (int64_t)n * a.c + c, g);
+      if (a.db) atomicAdd(a.db + c, b);
+    }
+  }
+}
+
+// dx = dxhat * s[n,c] (in place), ds1[n,c] += sum_p dxhat * x.  grid (chunks, c, n); dxhat fp32, any strides.
+template <typename T>
+__global__ void __launch_bounds__(256) modconv_bwd_finish_kernel(float* __restrict__ dxhat, const int64_t ds0, const int64_t ds1_,
+                                                                 const int64_t ds2, const int64_t ds3,
+                                                                 const T* __restrict__ x, const int64_t xs0, const int64_t xs1,
+                                                                 const int64_t xs2, const int64_t xs3,
+                                                                 const float* __restrict__ styles, float* __restrict__ dsum,
+                                                                 int c_total, int h, int w, int chunk) {
+  const int n = blockIdx.z, c = blockIdx.y;
+  const int hw = h * w;
+  const int p_begin = blockIdx.x * chunk;
+  const int p_end = min(hw, p_begin + chunk);
+  const float s = styles ? styles[(int64_t)n * c_total + c] : 1.f;
+  float* dp = dxhat + n * ds0 + c * ds1_;
+  const T* xp = x ? x + n * xs0 + c * xs1 : nullptr;
+  float acc = 0.f;
+  for (int p = p_begin + threadIdx.x; p < p_end; p += blockDim.x) {
+    const int py = p / w, px = p - py * w;
+    float* d = dp + py * ds2 + px * ds3;
+    const float v = *d;
+    if (xp) acc = fmaf(v, to_acc<T>(xp[py * xs2 + px * xs3]), acc);
+    *d = v * s;
+  }
+  if (dsum) {
+    __shared__ float red[8];
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 8; ++i) t += red[i];
+      atomicAdd(dsum + (int64_t)n * c_total + c, t);
+    }
+  }
+}
+
+// ds[n,i] += s[n,i] * sum_o (-gsum[n,o] * d[n,o]^2) * wsq[o,i]
+__global__ void __launch_bounds__(128) demod_grad_kernel(float* __restrict__ ds, const float* __restrict__ styles,
+                                                         const float* __restrict__ gsum, const float* __restrict__ dcoef,
+                                                         const float* __restrict__ wsq, int n, int cin, int cout) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, in = blockIdx.y;
+  if (i >= cin) return;
+  float acc = 0.f;
+  for (int o = 0; o < cout; ++o) {
+    const float d = dcoef[(int64_t)in * cout + o];
+    acc = fmaf(-gsum[(int64_t)in * cout + o] * d * d, wsq[(int64_t)o * cin + i], acc);
+  }
+  ds[(int64_t)in * cin + i] += styles[(int64_t)in * cin + i] * acc;
+}
+
 template <typename T>
 int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* xhat, int n, int cin, int cin_pad, int h,
                  int w, cudaStream_t st) {
@@ -206,6 +340,78 @@ int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int 
   const int64_t threads = (int64_t)n * cout * 32;
   demod_coefs_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(styles, wsq, d, n, cin, cout);
   VCN_LAUNCH_CHECK("demod_coefs_kernel");
+  return VCN_OK;
+}
+
+
+int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
+                         const vcn_upfirdn2d_epilogue* epi, void* dy0, float* gsum, float* db, int n, int c, int c_pad,
+                         int h, int w, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && c >= 1 && h >= 1 && w >= 1, "modconv_bwd_pack: bad shape");
+  VCN_REQUIRE(c_pad >= c && c_pad % 8 == 0, "modconv_bwd_pack: c_pad must be a multiple of 8 >= c");
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(dy && dy0 && dys, "modconv_bwd_pack: dy, dys, dy0 must not be NULL");
+  BwdPackArgs a;
+  memset(&a, 0, sizeof(a));
+  a.dy = dy; a.y = y; a.dy0 = static_cast<__nv_bfloat16*>(dy0); a.gsum = gsum; a.db = db;
+  for (int i = 0; i < 4; ++i) { a.dys[i] = dys[i]; a.ys[i] = ys ? ys[i] : dys[i]; }
+  a.n = n; a.c = c; a.c_pad = c_pad; a.h = h; a.w = w;
+  a.gain = 1.f; a.clamp = -1.f;
+  if (epi) {
+    a.noise = epi->noise; a.noise_stride_n = epi->noise_stride_n; a.bias = epi->bias; a.dcoef = epi->scale;
+    a.act = epi->act; a.alpha = epi->alpha; a.gain = epi->act_gain; a.clamp = epi->clamp;
+  }
+  VCN_REQUIRE(a.act == 0 || a.act == VCN_ACT_LINEAR || (a.act == VCN_ACT_LRELU && a.alpha != 0.f),
+              "modconv_bwd_pack: fused backward supports no activation, linear, or lrelu with alpha != 0 (got act %d)", a.act);
+  VCN_REQUIRE(a.act == 0 || a.gain != 0.f, "modconv_bwd_pack: gain must be non-zero");
+  VCN_REQUIRE((a.act == 0 && !gsum) || y, "modconv_bwd_pack: y is required with an activation or when gsum is requested");
+  dim3 grid((unsigned)((h * w + 127) / 128), (unsigned)((c_pad + 63) / 64), (unsigned)n);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (dtype) {
+    case VCN_F32: modconv_bwd_pack_kernel<float><<<grid, 256, 0, st>>>(a); break;
+    case VCN_F16: modconv_bwd_pack_kernel<__half><<<grid, 256, 0, st>>>(a); break;
+    case VCN_BF16: modconv_bwd_pack_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(a); break;
+    default: set_error("modconv_bwd_pack: unsupported dtype %d", dtype); return VCN_ERR_INVALID;
+  }
+  VCN_LAUNCH_CHECK("modconv_bwd_pack_kernel");
+  return VCN_OK;
+}
+
+int vcn_modconv_bwd_finish(float* dxhat, const int64_t ds[4], const void* x, int x_dtype, const int64_t xs[4],
+                           const float* styles, float* dsum, int n, int c, int h, int w, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && c >= 1 && h >= 1 && w >= 1, "modconv_bwd_finish: bad shape");
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(dxhat && ds, "modconv_bwd_finish: dxhat must not be NULL");
+  VCN_REQUIRE(!dsum || (x && xs), "modconv_bwd_finish: dsum needs x");
+  const int hw = h * w;
+  int chunk = hw;
+  // enough CTAs to fill the machine, at least 2048 pixels each
+  while (chunk > 4096 && (int64_t)n * c * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 8) chunk = (chunk + 1) / 2;
+  dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)c, (unsigned)n);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t z[4] = {0, 0, 0, 0};
+  if (!xs) xs = z;
+  switch (x ? x_dtype : VCN_F32) {
+    case VCN_F32: modconv_bwd_finish_kernel<float><<<grid, 256, 0, st>>>(dxhat, ds[0], ds[1], ds[2], ds[3], static_cast<const float*>(x), xs[0], xs[1], xs[2], xs[3], styles, dsum, c, h, w, chunk); break;
+    case VCN_F16: modconv_bwd_finish_kernel<__half><<<grid, 256, 0, st>>>(dxhat, ds[0], ds[1], ds[2], ds[3], static_cast<const __half*>(x), xs[0], xs[1], xs[2], xs[3], styles, dsum, c, h, w, chunk); break;
+    case VCN_BF16: modconv_bwd_finish_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(dxhat, ds[0], ds[1], ds[2], ds[3], static_cast<const __nv_bfloat16*>(x), xs[0], xs[1], xs[2], xs[3], styles, dsum, c, h, w, chunk); break;
+    default: set_error("modconv_bwd_finish: unsupported dtype %d", x_dtype); return VCN_ERR_INVALID;
+  }
+  VCN_LAUNCH_CHECK("modconv_bwd_finish_kernel");
+  return VCN_OK;
+}
+
+int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const float* dcoef, const float* wsq, int n, int cin,
+                   int cout, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && cin >= 1 && cout >= 1, "demod_grad: bad shape");
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(ds && styles && gsum && dcoef && wsq, "demod_grad: NULL pointer");
+  dim3 grid((unsigned)((cin + 127) / 128), (unsigned)n);
+  demod_grad_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(ds, styles, gsum, dcoef, wsq, n, cin, cout);
+  VCN_LAUNCH_CHECK("demod_grad_kernel");
   return VCN_OK;
 }
 

@@ -119,7 +119,7 @@ def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_l
     n, h, w, cin_pad = xhat.shape
     assert xhat.dtype == torch.bfloat16 and wt.dtype == torch.bfloat16 and xhat.is_contiguous() and wt.is_contiguous()
     assert wt.shape == (kh * kw, cout, cin_pad), (wt.shape, (kh * kw, cout, cin_pad))
-    oh, ow = (2 * h + 1, 2 * w + 1) if kind == _lib.CONV_TCONV2 else (h, w)
+    oh, ow = (2 * h + 1, 2 * w + 1) if kind == _lib.CONV_TCONV2 else ((h - 1) // 2, (w - 1) // 2) if kind == _lib.CONV_SCONV2 else (h, w)
     if out is None:
         fmt = torch.channels_last if channels_last else torch.contiguous_format
         out = torch.empty([n, cout, oh, ow], dtype=out_dtype, device=xhat.device, memory_format=fmt)
@@ -134,3 +134,244 @@ def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_l
                                 _lib.current_stream(xhat.device))
     _lib.check(st, "vcn_conv_igemm")
     return out
+
+
+def bwd_pack(dy, y, epilogue, want_gsum, want_db):
+    """vcn_modconv_bwd_pack: (dy0 bf16 NHWC [N,H,W,C_pad], gsum [N,C] or None, db [C] or None)."""
+    lib = _lib.load()
+    n, c, h, w = dy.shape
+    c_pad = _round_up(c, 8)
+    dy0 = torch.empty([n, h, w, c_pad], dtype=torch.bfloat16, device=dy.device)
+    gsum = torch.zeros([n, c], dtype=torch.float32, device=dy.device) if want_gsum else None
+    db = torch.zeros([c], dtype=torch.float32, device=dy.device) if want_db else None
+    if n == 0:
+        return dy0, gsum, db
+    if y is not None:
+        assert y.shape == dy.shape and y.dtype == dy.dtype
+    with torch.cuda.device(dy.device):
+        st = lib.vcn_modconv_bwd_pack(_lib.ptr(dy), _lib.ptr(y), _lib.dtype_code(dy.dtype), ctypes.byref(_strides4(dy)),
+                                      ctypes.byref(_strides4(y)) if y is not None else None, ctypes.byref(epilogue),
+                                      _lib.ptr(dy0), _lib.ptr(gsum), _lib.ptr(db), n, c, c_pad, h, w,
+                                      _lib.current_stream(dy.device))
+    _lib.check(st, "vcn_modconv_bwd_pack")
+    return dy0, gsum, db
+
+
+def bwd_finish(dxhat, x, styles, want_dsum):
+    """vcn_modconv_bwd_finish: dxhat (fp32) *= s in place; returns dsum [N,C] = sum_p dxhat*x (or None)."""
+    lib = _lib.load()
+    n, c, h, w = dxhat.shape
+    assert dxhat.dtype == torch.float32
+    dsum = torch.zeros([n, c], dtype=torch.float32, device=dxhat.device) if want_dsum else None
+    if n == 0:
+        return dsum
+    with torch.cuda.device(dxhat.device):
+        st = lib.vcn_modconv_bwd_finish(_lib.ptr(dxhat), ctypes.byref(_strides4(dxhat)), _lib.ptr(x) if want_dsum else None,
+                                        _lib.dtype_code(x.dtype), ctypes.byref(_strides4(x)), _lib.ptr(styles), _lib.ptr(dsum),
+                                        n, c, h, w, _lib.current_stream(dxhat.device))
+    _lib.check(st, "vcn_modconv_bwd_finish")
+    return dsum
+
+
+def demod_grad(ds, styles, gsum, dcoef, wsq):
+    lib = _lib.load()
+    n, cin = ds.shape
+    cout = dcoef.shape[1]
+    if n == 0:
+        return ds
+    with torch.cuda.device(ds.device):
+        st = lib.vcn_demod_grad(_lib.ptr(ds), _lib.ptr(styles), _lib.ptr(gsum), _lib.ptr(dcoef), _lib.ptr(wsq), n, cin, cout,
+                                _lib.current_stream(ds.device))
+    _lib.check(st, "vcn_demod_grad")
+    return ds
+
+
+# ---- packed-weight cache (synthesis weights are frozen in VisCoIN: pack once per weight version) -------------------
+
+_wcache = {}
+
+
+def _packed(weight, transpose_io, flip, want_wsq):
+    """Packed bf16 taps (+ wsq) of `weight`, cached per tensor object and version.  The entry holds a weak reference to
+    the tensor so that a recycled address or id can never alias a dead tensor's entry."""
+    import weakref
+    key = (id(weight), transpose_io, flip)
+    hit = _wcache.get(key)
+    if hit is not None:
+        ref, version, ptr, wt, wsq = hit
+        if ref() is weight and version == weight._version and ptr == weight.data_ptr():
+            return wt, wsq
+    src = weight.detach()
+    if flip:
+        src = src.flip([2, 3])
+    wt, wsq = pack_weights(src, transpose_io=transpose_io, want_wsq=True)
+    if len(_wcache) > 512:
+        for k in [k for k, v in _wcache.items() if v[0]() is None]:
+            del _wcache[k]
+    _wcache[key] = (weakref.ref(weight), weight._version, weight.data_ptr(), wt, wsq)
+    return wt, wsq
+
+
+_FUSABLE_ACTS = (None, "linear", "lrelu")
+
+
+class _ModConvLayer(torch.autograd.Function):
+    """y = bias_act(modulated_conv2d(x, W, s, noise), b)  (act None = plain modulated_conv2d)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, styles, noise, bias, resample_filter, cfg):
+        up, demodulate, flip_weight, act, alpha, gain, clamp = cfg
+        _lib.require_device(x.device.index)
+        n, cin, h, w = x.shape
+        cout, cin_w, kh, kw = weight.shape
+        assert cin_w == cin and kh == kw and kh in (1, 3), "modulated_conv2d(impl='cuda'): 1x1 and 3x3 kernels only"
+        assert styles is None or tuple(styles.shape) == (n, cin)
+        styles32 = styles.to(torch.float32).contiguous() if styles is not None else None
+        hold = []
+        if up == 1:
+            wt, wsq = _packed(weight, False, False, demodulate)
+        else:
+            assert up == 2 and kh == 3, "modulated_conv2d(impl='cuda'): up=2 needs a 3x3 kernel"
+            assert resample_filter is not None and tuple(resample_filter.shape) == (4, 4), "up=2 needs a 4x4 resample filter"
+            # reference: flip_weight=False -> conv_transpose2d with the weight as is (conv2d_resample.py:127-138)
+            wt, wsq = _packed(weight, False, bool(flip_weight), demodulate)
+        d = demod_coefs(styles32, wsq) if demodulate else None
+        xhat = modulate_pack(x, styles32)
+        epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
+        if up == 1:
+            kind = _lib.CONV_FPROP if flip_weight else _lib.CONV_DGRAD
+            y = conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=x.dtype, epilogue=epi)
+        else:
+            z = conv_igemm(xhat, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=torch.float32)
+            f = resample_filter.to(device=x.device, dtype=torch.float32)
+            y = _upfirdn2d.launch(z, f, 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi,
+                                  out=torch.empty([n, cout, 2 * h, 2 * w], dtype=x.dtype, device=x.device))
+        ctx.cfg = cfg
+        ctx.has = (styles is not None, noise is not None, bias is not None)
+        ctx.save_for_backward(x, weight, styles32, noise, bias, resample_filter, d, wsq, y)
+        del hold
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, styles32, noise, bias, resample_filter, d, wsq, y = ctx.saved_tensors
+        up, demodulate, flip_weight, act, alpha, gain, clamp = ctx.cfg
+        need_x, need_w, need_s, need_noise, need_b = ctx.needs_input_grad[:5]
+        if need_w:
+            raise _lib.VcnError("modulated_conv2d(impl='cuda'): the weight gradient is not implemented yet (VisCoIN "
+                                "freezes the synthesis weights, viscoin/training/viscoin.py:116)")
+        n, cin, h, w = x.shape
+        cout, _, kh, kw = weight.shape
+        dy = dy.contiguous() if not dy.is_contiguous() else dy
+        if dy.dtype != y.dtype:
+            dy = dy.to(y.dtype)
+        epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
+        want_g = demodulate and need_s
+        dy0, gsum, db = bwd_pack(dy, y if (act is not None or want_g) else None, epi, want_g, need_b and bias is not None)
+        dx = ds = dnoise = None
+        if need_x or need_s:
+            if up == 1:
+                wt_t, _ = _packed(weight, True, False, False)
+                kind = _lib.CONV_DGRAD if flip_weight else _lib.CONV_FPROP
+                dxhat = conv_igemm(dy0, wt_t, kind, cin, kh, kw, out_dtype=torch.float32)
+            else:
+                wt_t, _ = _packed(weight, True, bool(flip_weight), False)
+                f = resample_filter.to(device=x.device, dtype=torch.float32)
+                # FIR^T: same op, flipped filter, padding fw-1-p = 2 (upfirdn2d.py:246-261); channels_last view of dy0
+                dz = _upfirdn2d.launch(dy0.permute(0, 3, 1, 2), f, 1, 1, 1, 1, 2, 2, 2, 2, True, 4.0)
+                dz = dz.permute(0, 2, 3, 1)
+                assert dz.is_contiguous()
+                dxhat = conv_igemm(dz, wt_t, _lib.CONV_SCONV2, cin, 3, 3, out_dtype=torch.float32)
+            ds1 = bwd_finish(dxhat, x, styles32, need_s and styles32 is not None)
+            if need_x:
+                dx = dxhat if x.dtype == torch.float32 else dxhat.to(x.dtype)
+            if need_s and styles32 is not None:
+                ds = ds1
+                if demodulate:
+                    ds = demod_grad(ds, styles32, gsum, d, wsq)
+        if need_noise and noise is not None:
+            # rare path (noise buffers are constants / fresh randn in the reference): dz summed over channels
+            if act is not None:
+                dzf = _bias_act._call(dy, None, None, y, None, 1, 1, _bias_act.activation_funcs[act].cuda_idx,
+                                      epi.alpha, epi.act_gain, epi.clamp, False)[0]
+            else:
+                dzf = dy
+            dnoise = dzf.sum(dim=1, keepdim=True)
+            if noise.ndim == 2 or noise.shape[0] == 1:
+                dnoise = dnoise.sum(dim=0).reshape(noise.shape)
+            dnoise = dnoise.to(noise.dtype)
+        del hold
+        return dx, None, ds, dnoise, (db.to(bias.dtype) if db is not None else None), None, None
+
+
+def _check_cuda(x, what):
+    if x.device.type != "cuda":
+        raise _lib.VcnError("%s(impl='cuda') needs a CUDA tensor; this build has no CPU fallback (use impl='ref')" % what)
+
+
+def modconv_layer(x, weight, styles, noise=None, bias=None, up=1, padding=None, resample_filter=None, demodulate=True,
+                  flip_weight=True, act="lrelu", alpha=None, gain=None, clamp=None):
+    """Fused SynthesisLayer / ToRGBLayer body: bias_act(modulated_conv2d(...), bias, act, gain, clamp)
+    (networks.py:299-304, 322-323) in one GEMM epilogue.  Activations other than linear / lrelu run bias_act
+    as a second kernel."""
+    _check_cuda(x, "modconv_layer")
+    k = int(weight.shape[-1])
+    assert padding is None or padding == k // 2, "modulated_conv2d(impl='cuda'): padding must be k//2"
+    assert up in (1, 2)
+    fuse = act in _FUSABLE_ACTS and not (act == "lrelu" and alpha == 0)
+    cfg = (up, bool(demodulate), bool(flip_weight), act if fuse else None, alpha, gain, clamp)
+    if styles is None:
+        demodulate = False
+        cfg = (up, False, bool(flip_weight), cfg[3], alpha, gain, clamp)
+    y = _ModConvLayer.apply(x, weight, styles, noise, bias if fuse else None, resample_filter, cfg)
+    if not fuse:
+        y = _bias_act.bias_act(y, bias.to(y.dtype) if bias is not None else None, act=act, alpha=alpha, gain=gain, clamp=clamp)
+    return y
+
+
+def modulated_conv2d(x, weight, styles, noise=None, up=1, down=1, padding=0, resample_filter=None, demodulate=True,
+                     flip_weight=True, fused_modconv=True, impl="cuda"):
+    """Signature of training/networks.py:27-40 (+ impl).  x [N,Cin,H,W], weight [Cout,Cin,k,k], styles [N,Cin],
+    noise broadcastable to [N,1,Hout,Wout] or None."""
+    assert impl in ["ref", "cuda"]
+    if impl == "ref":
+        return _modulated_conv2d_ref(x, weight, styles, noise, up, down, padding, resample_filter, demodulate, flip_weight,
+                                     fused_modconv)
+    _check_cuda(x, "modulated_conv2d")
+    if down != 1:
+        raise _lib.VcnError("modulated_conv2d(impl='cuda'): down != 1 is not on the synthesis path and is not implemented")
+    return modconv_layer(x, weight, styles, noise=noise, bias=None, up=up, padding=padding, resample_filter=resample_filter,
+                         demodulate=demodulate, flip_weight=flip_weight, act=None)
+
+
+def _modulated_conv2d_ref(x, weight, styles, noise, up, down, padding, resample_filter, demodulate, flip_weight,
+                          fused_modconv):
+    """Plain torch formulation (non-fused branch of networks.py:63-72; the grouped branch is the same function)."""
+    n = x.shape[0]
+    cout, cin, kh, kw = weight.shape
+    dcoefs = None
+    if demodulate:
+        w = weight.unsqueeze(0) * styles.reshape(n, 1, -1, 1, 1)
+        dcoefs = (w.square().sum(dim=[2, 3, 4]) + 1e-8).rsqrt()
+    x = x * styles.to(x.dtype).reshape(n, -1, 1, 1)
+    px0, px1, py0, py1 = _upfirdn2d._parse_padding(padding)
+    wgt = weight.to(x.dtype)
+    if up == 1 and down == 1:
+        if not flip_weight:
+            wgt = wgt.flip([2, 3])
+        x = torch.nn.functional.conv2d(x, wgt, padding=[py0, px0])
+    elif up == 2 and down == 1:
+        wt = wgt.transpose(0, 1)
+        if flip_weight:
+            wt = wt.flip([2, 3])
+        x = torch.nn.functional.conv_transpose2d(x, wt, stride=2)
+        fw, fh = _upfirdn2d._get_filter_size(resample_filter)
+        p = [px0 + (fw + 1) // 2 - (kw - 1), px1 + (fw - 2) // 2 - (kw - 2), py0 + (fh + 1) // 2 - (kh - 1), py1 + (fh - 2) // 2 - (kh - 2)]
+        x = _upfirdn2d._upfirdn2d_ref(x, resample_filter, padding=p, gain=4)
+    else:
+        raise NotImplementedError("ref path covers the synthesis configurations (up in {1,2}, down=1)")
+    if dcoefs is not None:
+        x = x * dcoefs.to(x.dtype).reshape(n, -1, 1, 1)
+    if noise is not None:
+        x = x + noise.to(x.dtype)
+    return x
