@@ -7,6 +7,6 @@ installer).  Import as ``viscoin_next_b200`` (the hyphenated directory is not an
 """
 
 from . import _lib  # noqa: F401
-from .host import bias_act, modconv, upfirdn2d  # noqa: F401
+from .host import bias_act, modconv, networks, upfirdn2d  # noqa: F401
 
-__all__ = ["_lib", "bias_act", "modconv", "upfirdn2d"]
+__all__ = ["_lib", "bias_act", "modconv", "networks", "upfirdn2d"]

@@ -1,0 +1,306 @@
+"""networks - the consumers of the hot path, mirrored from the reference with identical parameter / buffer names so
+that reference ``state_dict``s load unchanged:
+
+  FullyConnectedLayer   stylegan2_ada/training/networks.py:89-118
+  SynthesisLayer        :254-305     ToRGBLayer :310-324     SynthesisBlock :329-419     SynthesisNetwork :424-472
+  MappingNetwork        :174-249 (c_dim = 0)                 Generator :477-500
+  MappingNetworkAdapted / GeneratorAdapted                   viscoin/models/gan.py:35-234
+
+Every layer body is ONE fused call into the sm_100a library (``modconv.modconv_layer``: modulation -> tcgen05
+implicit GEMM -> demodulation + noise + bias + activation + clamp in the epilogue); the RGB skip uses
+``upfirdn2d.upsample2d``; mapping FCs use ``bias_act``.  The small dense FCs (affine 512->C, mapping) are plain
+library GEMMs (torch.addmm / matmul).  All blocks run in fp32 storage (``force_fp32`` semantics of :382-383); the
+convolution operands are bf16 on the tensor cores (tolerances in tests/).
+"""
+
+import math
+
+import numpy as np
+import torch
+
+from . import bias_act as _bias_act
+from . import modconv as _modconv
+from . import upfirdn2d as _upfirdn2d
+
+
+def normalize_2nd_moment(x, dim=1, eps=1e-8):
+    return x * (x.square().mean(dim=dim, keepdim=True) + eps).rsqrt()
+
+
+class FullyConnectedLayer(torch.nn.Module):
+    def __init__(self, in_features, out_features, bias=True, activation="linear", lr_multiplier=1, bias_init=0):
+        super().__init__()
+        self.activation = activation
+        self.weight = torch.nn.Parameter(torch.randn([out_features, in_features]) / lr_multiplier)
+        self.bias = torch.nn.Parameter(torch.full([out_features], np.float32(bias_init))) if bias else None
+        self.weight_gain = lr_multiplier / math.sqrt(in_features)
+        self.bias_gain = lr_multiplier
+
+    def forward(self, x):
+        w = self.weight.to(x.dtype) * self.weight_gain
+        b = self.bias
+        if b is not None:
+            b = b.to(x.dtype)
+            if self.bias_gain != 1:
+                b = b * self.bias_gain
+        if self.activation == "linear" and b is not None:
+            return torch.addmm(b.unsqueeze(0), x, w.t())
+        x = x.matmul(w.t())
+        return _bias_act.bias_act(x, b, act=self.activation)
+
+
+class SynthesisLayer(torch.nn.Module):
+    def __init__(self, in_channels, out_channels, w_dim, resolution, kernel_size=3, up=1, use_noise=True,
+                 activation="lrelu", resample_filter=[1, 3, 3, 1], conv_clamp=None, channels_last=False):
+        super().__init__()
+        self.resolution, self.up, self.use_noise, self.activation, self.conv_clamp = resolution, up, use_noise, activation, conv_clamp
+        self.register_buffer("resample_filter", _upfirdn2d.setup_filter(resample_filter))
+        self.padding = kernel_size // 2
+        self.act_gain = _bias_act.activation_funcs[activation].def_gain
+        self.affine = FullyConnectedLayer(w_dim, in_channels, bias_init=1)
+        self.weight = torch.nn.Parameter(torch.randn([out_channels, in_channels, kernel_size, kernel_size]))
+        if use_noise:
+            self.register_buffer("noise_const", torch.randn([resolution, resolution]))
+            self.noise_strength = torch.nn.Parameter(torch.zeros([]))
+        self.bias = torch.nn.Parameter(torch.zeros([out_channels]))
+
+    def forward(self, x, w, noise_mode="random", fused_modconv=True, gain=1):
+        assert noise_mode in ["random", "const", "none"]
+        in_res = self.resolution // self.up
+        assert tuple(x.shape[1:]) == (self.weight.shape[1], in_res, in_res)
+        styles = self.affine(w)
+        noise = None
+        if self.use_noise and noise_mode == "random":
+            noise = torch.randn([x.shape[0], 1, self.resolution, self.resolution], device=x.device) * self.noise_strength
+        if self.use_noise and noise_mode == "const":
+            noise = self.noise_const * self.noise_strength
+        act_clamp = self.conv_clamp * gain if self.conv_clamp is not None else None
+        return _modconv.modconv_layer(x, self.weight, styles, noise=noise, bias=self.bias, up=self.up, padding=self.padding,
+                                      resample_filter=self.resample_filter, flip_weight=(self.up == 1),
+                                      act=self.activation, gain=self.act_gain * gain, clamp=act_clamp)
+
+
+class ToRGBLayer(torch.nn.Module):
+    def __init__(self, in_channels, out_channels, w_dim, kernel_size=1, conv_clamp=None, channels_last=False):
+        super().__init__()
+        self.conv_clamp = conv_clamp
+        self.affine = FullyConnectedLayer(w_dim, in_channels, bias_init=1)
+        self.weight = torch.nn.Parameter(torch.randn([out_channels, in_channels, kernel_size, kernel_size]))
+        self.bias = torch.nn.Parameter(torch.zeros([out_channels]))
+        self.weight_gain = 1 / math.sqrt(in_channels * (kernel_size ** 2))
+
+    def forward(self, x, w, fused_modconv=True):
+        styles = self.affine(w) * self.weight_gain
+        return _modconv.modconv_layer(x, self.weight, styles, bias=self.bias, demodulate=False, act="linear",
+                                      clamp=self.conv_clamp)
+
+
+class Conv2dLayer(torch.nn.Module):
+    """networks.py:123-169, the configurations the synthesis side uses (the 'resnet' skip: 1x1, up=2, no bias)."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, bias=True, activation="linear", up=1, down=1,
+                 resample_filter=[1, 3, 3, 1], conv_clamp=None, channels_last=False, trainable=True):
+        super().__init__()
+        assert down == 1 and kernel_size in (1, 3), "only the synthesis-side configurations are implemented"
+        self.activation, self.up, self.conv_clamp = activation, up, conv_clamp
+        self.register_buffer("resample_filter", _upfirdn2d.setup_filter(resample_filter))
+        self.padding = kernel_size // 2
+        self.weight_gain = 1 / math.sqrt(in_channels * (kernel_size ** 2))
+        self.act_gain = _bias_act.activation_funcs[activation].def_gain
+        self.weight = torch.nn.Parameter(torch.randn([out_channels, in_channels, kernel_size, kernel_size]))
+        self.bias = torch.nn.Parameter(torch.zeros([out_channels])) if bias else None
+
+    def forward(self, x, gain=1):
+        w = self.weight * self.weight_gain
+        act_clamp = self.conv_clamp * gain if self.conv_clamp is not None else None
+        if self.up == 1 or self.weight.shape[-1] == 3:
+            return _modconv.modconv_layer(x, w, None, bias=self.bias, up=self.up, resample_filter=self.resample_filter,
+                                          demodulate=False, flip_weight=(self.up == 1), act=self.activation,
+                                          gain=self.act_gain * gain, clamp=act_clamp)
+        # 1x1 with up=2: convolve at low resolution, then FIR-upsample (conv2d_resample.py:107-110)
+        x = _modconv.modconv_layer(x, w, None, demodulate=False, act=None)
+        x = _upfirdn2d.upsample2d(x, self.resample_filter)
+        return _bias_act.bias_act(x, self.bias, act=self.activation, gain=self.act_gain * gain, clamp=act_clamp)
+
+
+class SynthesisBlock(torch.nn.Module):
+    def __init__(self, in_channels, out_channels, w_dim, resolution, img_channels, is_last, architecture="skip",
+                 resample_filter=[1, 3, 3, 1], conv_clamp=None, use_fp16=False, fp16_channels_last=False, **layer_kwargs):
+        assert architecture in ["orig", "skip", "resnet"]
+        super().__init__()
+        self.in_channels, self.w_dim, self.resolution, self.img_channels = in_channels, w_dim, resolution, img_channels
+        self.is_last, self.architecture = is_last, architecture
+        self.register_buffer("resample_filter", _upfirdn2d.setup_filter(resample_filter))
+        self.num_conv = self.num_torgb = 0
+        if in_channels == 0:
+            self.const = torch.nn.Parameter(torch.randn([out_channels, resolution, resolution]))
+        if in_channels != 0:
+            self.conv0 = SynthesisLayer(in_channels, out_channels, w_dim=w_dim, resolution=resolution, up=2,
+                                        resample_filter=resample_filter, conv_clamp=conv_clamp, **layer_kwargs)
+            self.num_conv += 1
+        self.conv1 = SynthesisLayer(out_channels, out_channels, w_dim=w_dim, resolution=resolution, conv_clamp=conv_clamp,
+                                    **layer_kwargs)
+        self.num_conv += 1
+        if is_last or architecture == "skip":
+            self.torgb = ToRGBLayer(out_channels, img_channels, w_dim=w_dim, conv_clamp=conv_clamp)
+            self.num_torgb += 1
+        if in_channels != 0 and architecture == "resnet":
+            self.skip = Conv2dLayer(in_channels, out_channels, kernel_size=1, bias=False, up=2, resample_filter=resample_filter)
+
+    def forward(self, x, img, ws, force_fp32=False, fused_modconv=None, **layer_kwargs):
+        assert tuple(ws.shape[1:]) == (self.num_conv + self.num_torgb, self.w_dim)
+        w_iter = iter(ws.unbind(dim=1))
+        if self.in_channels == 0:
+            x = self.const.to(torch.float32).unsqueeze(0).repeat([ws.shape[0], 1, 1, 1])
+        else:
+            x = x.to(torch.float32)
+        if self.in_channels == 0:
+            x = self.conv1(x, next(w_iter), **layer_kwargs)
+        elif self.architecture == "resnet":
+            y = self.skip(x, gain=math.sqrt(0.5))
+            x = self.conv0(x, next(w_iter), **layer_kwargs)
+            x = self.conv1(x, next(w_iter), gain=math.sqrt(0.5), **layer_kwargs)
+            x = y + x
+        else:
+            x = self.conv0(x, next(w_iter), **layer_kwargs)
+            x = self.conv1(x, next(w_iter), **layer_kwargs)
+        if img is not None:
+            img = _upfirdn2d.upsample2d(img, self.resample_filter)
+        if self.is_last or self.architecture == "skip":
+            y = self.torgb(x, next(w_iter)).to(torch.float32)
+            img = img.add_(y) if img is not None else y
+        return x, img
+
+
+class SynthesisNetwork(torch.nn.Module):
+    def __init__(self, w_dim, img_resolution, img_channels, channel_base=32768, channel_max=512, num_fp16_res=0,
+                 **block_kwargs):
+        assert img_resolution >= 4 and img_resolution & (img_resolution - 1) == 0
+        super().__init__()
+        self.w_dim, self.img_resolution, self.img_channels = w_dim, img_resolution, img_channels
+        self.img_resolution_log2 = int(np.log2(img_resolution))
+        self.block_resolutions = [2 ** i for i in range(2, self.img_resolution_log2 + 1)]
+        channels_dict = {res: min(channel_base // res, channel_max) for res in self.block_resolutions}
+        self.num_ws = 0
+        for res in self.block_resolutions:
+            in_channels = channels_dict[res // 2] if res > 4 else 0
+            block = SynthesisBlock(in_channels, channels_dict[res], w_dim=w_dim, resolution=res, img_channels=img_channels,
+                                   is_last=(res == img_resolution), **block_kwargs)
+            self.num_ws += block.num_conv
+            if res == img_resolution:
+                self.num_ws += block.num_torgb
+            setattr(self, f"b{res}", block)
+
+    def forward(self, ws, **block_kwargs):
+        assert tuple(ws.shape[1:]) == (self.num_ws, self.w_dim)
+        ws = ws.to(torch.float32)
+        block_ws, w_idx = [], 0
+        for res in self.block_resolutions:
+            block = getattr(self, f"b{res}")
+            block_ws.append(ws.narrow(1, w_idx, block.num_conv + block.num_torgb))
+            w_idx += block.num_conv
+        x = img = None
+        for res, cur_ws in zip(self.block_resolutions, block_ws):
+            x, img = getattr(self, f"b{res}")(x, img, cur_ws, **block_kwargs)
+        return img
+
+
+class MappingNetwork(torch.nn.Module):
+    def __init__(self, z_dim, c_dim, w_dim, num_ws, num_layers=8, embed_features=None, layer_features=None,
+                 activation="lrelu", lr_multiplier=0.01, w_avg_beta=0.995):
+        super().__init__()
+        assert c_dim == 0, "conditional mapping is not on the VisCoIN path"
+        self.z_dim, self.c_dim, self.w_dim, self.num_ws, self.num_layers, self.w_avg_beta = z_dim, c_dim, w_dim, num_ws, num_layers, w_avg_beta
+        if layer_features is None:
+            layer_features = w_dim
+        features = [z_dim] + [layer_features] * (num_layers - 1) + [w_dim]
+        for idx in range(num_layers):
+            setattr(self, f"fc{idx}", FullyConnectedLayer(features[idx], features[idx + 1], activation=activation,
+                                                         lr_multiplier=lr_multiplier))
+        if num_ws is not None and w_avg_beta is not None:
+            self.register_buffer("w_avg", torch.zeros([w_dim]))
+
+    def forward(self, z, c=None, truncation_psi=1, truncation_cutoff=None, skip_w_avg_update=False):
+        x = normalize_2nd_moment(z.to(torch.float32))
+        for idx in range(self.num_layers):
+            x = getattr(self, f"fc{idx}")(x)
+        if self.w_avg_beta is not None and self.training and not skip_w_avg_update:
+            self.w_avg.copy_(x.detach().mean(dim=0).lerp(self.w_avg, self.w_avg_beta))
+        if self.num_ws is not None:
+            x = x.unsqueeze(1).repeat([1, self.num_ws, 1])
+        if truncation_psi != 1:
+            if self.num_ws is None or truncation_cutoff is None:
+                x = self.w_avg.lerp(x, truncation_psi)
+            else:
+                x[:, :truncation_cutoff] = self.w_avg.lerp(x[:, :truncation_cutoff], truncation_psi)
+        return x
+
+
+class Generator(torch.nn.Module):
+    def __init__(self, z_dim, c_dim, w_dim, img_resolution, img_channels, mapping_kwargs={}, synthesis_kwargs={}):
+        super().__init__()
+        self.z_dim, self.c_dim, self.w_dim, self.img_resolution, self.img_channels = z_dim, c_dim, w_dim, img_resolution, img_channels
+        self.synthesis = SynthesisNetwork(w_dim=w_dim, img_resolution=img_resolution, img_channels=img_channels, **synthesis_kwargs)
+        self.num_ws = self.synthesis.num_ws
+        self.mapping = MappingNetwork(z_dim=z_dim, c_dim=c_dim, w_dim=w_dim, num_ws=self.num_ws, **mapping_kwargs)
+
+    def forward(self, z, c=None, truncation_psi=1, truncation_cutoff=None, **synthesis_kwargs):
+        ws = self.mapping(z, c, truncation_psi=truncation_psi, truncation_cutoff=truncation_cutoff)
+        return self.synthesis(ws, **synthesis_kwargs)
+
+
+class MappingNetworkAdapted(torch.nn.Module):
+    """viscoin/models/gan.py:147-234: one FC stack per w; stacks coarse..mid read z1, the others z2."""
+
+    def __init__(self, z1_dim, z2_dim, w_dim, num_ws, num_layers=1, coarse_layer=2, mid_layer=10, activation="lrelu",
+                 lr_multiplier=0.01):
+        super().__init__()
+        self.z1_dim, self.z2_dim, self.w_dim, self.num_ws, self.num_layers = z1_dim, z2_dim, w_dim, num_ws, num_layers
+        self.coarse_layer, self.mid_layer = coarse_layer, mid_layer
+        self.fixed_w_avg = torch.nn.Parameter(torch.zeros([w_dim]))
+        for i in range(num_ws):
+            z_dim = z2_dim if (i < coarse_layer or i > mid_layer) else z1_dim
+            feats = [z_dim] + [w_dim] * num_layers
+            stack = torch.nn.ModuleList([FullyConnectedLayer(feats[j], feats[j + 1], activation=activation,
+                                                             lr_multiplier=lr_multiplier) for j in range(num_layers)])
+            setattr(self, f"s{i}", stack)
+
+    def forward(self, z1, z2):
+        if z1.ndim > 3:
+            z1 = z1.reshape(-1, self.z1_dim)
+        x1 = normalize_2nd_moment(z1.to(torch.float32))
+        x2 = normalize_2nd_moment(z2.to(torch.float32))
+        outs = []
+        for i in range(self.num_ws):
+            x = x2 if (i < self.coarse_layer or i > self.mid_layer) else x1
+            for layer in getattr(self, f"s{i}"):
+                x = layer(x)
+            outs.append(x)
+        return torch.stack(outs, dim=1) + self.fixed_w_avg
+
+
+class GeneratorAdapted(torch.nn.Module):
+    """viscoin/models/gan.py:35-144 (low_res256 False)."""
+
+    def __init__(self, z_dim=256, w_dim=512, img_resolution=256, img_channels=3, mapping_kwargs={}, synthesis_kwargs={}):
+        super().__init__()
+        self.z_dim, self.w_dim, self.img_resolution, self.img_channels = z_dim, w_dim, img_resolution, img_channels
+        self.synthesis = SynthesisNetwork(w_dim=w_dim, img_resolution=img_resolution, img_channels=img_channels, **synthesis_kwargs)
+        self.num_ws = self.synthesis.num_ws
+        self.mapping = MappingNetworkAdapted(9 * z_dim, 9 * z_dim, w_dim, self.num_ws, **mapping_kwargs)
+
+    @classmethod
+    def from_gan(cls, gan, z_dim=256, w_dim=512, mapping_kwargs={}):
+        assert gan.synthesis is not None, "The provided GAN is not a valid StyleGAN model"
+        model = cls(z_dim=z_dim, w_dim=w_dim, mapping_kwargs=mapping_kwargs)
+        model.synthesis = gan.synthesis  # the SAME module object is shared by both generators (gan.py:142)
+        model.num_ws, model.img_resolution, model.img_channels = gan.synthesis.num_ws, gan.synthesis.img_resolution, gan.synthesis.img_channels
+        return model
+
+    def forward(self, z1, z2, return_latents=False, truncation_psi=1, truncation_cutoff=None, **synthesis_kwargs):
+        ws = self.mapping(z1, z2)
+        img = self.synthesis(ws, **synthesis_kwargs)
+        return (img, ws) if return_latents else img
+
+    def gen_from_w(self, w, **synthesis_kwargs):
+        return self.synthesis(w, **synthesis_kwargs)
