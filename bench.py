@@ -245,7 +245,98 @@ class OpSweep:
         return time.perf_counter() - t0
 
 
-WORKLOADS = {"opsweep": OpSweep}
+class Synthesis:
+    """BASELINE.json configs[0] on the GPU: StyleGAN2-ADA SynthesisNetwork forward, 256x256, batch N, random-init,
+    fp32 storage (bf16 tensor-core operands), noise_mode='const' with noise_strength 0.1.
+    One step = ws[N,14,512] -> img[N,3,256,256] through this package's modules (every layer one fused sm_100a call)."""
+
+    metric = "G-synthesis images/s @256^2"
+    unit = "images/s"
+    dtype = "bf16"
+    RES = 256
+
+    def __init__(self, batch):
+        self.n = batch
+        self.name = "SynthesisNetwork forward %dx%d batch %d/GPU, random-init, noise const 0.1, fp32 I/O + bf16 MMA operands" % (self.RES, self.RES, batch)
+
+    def units_per_step(self):
+        return float(self.n)
+
+    def _build(self, device, N):
+        torch.manual_seed(0)
+        S = N.SynthesisNetwork(w_dim=512, img_resolution=self.RES, img_channels=3)
+        with torch.no_grad():
+            for name, p in S.named_parameters():
+                if name.endswith("noise_strength"):
+                    p.fill_(0.1)
+        return S.to(device).eval().requires_grad_(False)
+
+    def setup(self, device, seed):
+        import viscoin_next_b200 as V
+        self.V = V
+        self.S = self._build(device, V.networks)
+        g = torch.Generator(device=device).manual_seed(seed)
+        self.ws = torch.randn(self.n, self.S.num_ws, 512, device=device, generator=g)
+
+    def step(self):
+        with torch.no_grad():
+            return self.S(self.ws, noise_mode="const")
+
+    def e2e_setup(self, device):
+        self.hws = self.ws.cpu().pin_memory()
+        self.himg = torch.empty(self.n, 3, self.RES, self.RES).pin_memory()
+        self.h2d = self.hws.numel() * 4
+        self.d2h = self.himg.numel() * 4
+
+    def e2e_step(self, device):
+        with torch.no_grad():
+            img = self.S(self.hws.to(device, non_blocking=True), noise_mode="const")
+            self.himg.copy_(img, non_blocking=True)
+
+    def roofline(self, device, peaks, iters=20):
+        """conv_igemm on the heaviest layer shape b256.conv1: [N,128,256,256] x [128,128,3,3], 2*N*Cout*Cin*9*H*W FLOP."""
+        M = self.V.modconv
+        n, c, r = self.n, 128, self.RES
+        x = torch.randn(n, c, r, r, device=device)
+        w = torch.randn(c, c, 3, 3, device=device)
+        xh = M.modulate_pack(x, None)
+        wt, _ = M.pack_weights(w)
+        out = torch.empty(n, c, r, r, device=device)
+        from viscoin_next_b200 import _lib
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+        for _ in range(3):
+            M.conv_igemm(xh, wt, _lib.CONV_FPROP, c, 3, 3, out=out)
+        times = []
+        for _ in range(iters):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            M.conv_igemm(xh, wt, _lib.CONV_FPROP, c, 3, 3, out=out)
+            e1.record()
+            e1.synchronize()
+            times.append(e0.elapsed_time(e1))
+        ms = sum(times) / len(times)
+        flop = 2.0 * n * c * c * 9 * r * r
+        ach = flop / (ms * 1e-3) / 1e12
+        return {"kernel": "conv_igemm_kernel FPROP [%d,128,256,256]x[128,128,3,3] bf16->f32" % n, "bound": "tensor",
+                "achieved": round(ach, 1), "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": round(ach / peaks["bf16"], 4),
+                "peak_source": peaks["src"] + " (burst cuBLAS bf16)", "traffic": None, "alg_flop_per_launch": flop,
+                "avg_launch_ms": round(ms, 5)}
+
+    def cpu_step(self, n_sample, seed=0):
+        from oracle import ref_net as RN
+        if not hasattr(self, "_cpu_sd"):
+            import viscoin_next_b200 as V
+            self._cpu_sd = {k: v.detach().cpu() for k, v in self._build(torch.device("cpu"), V.networks).state_dict().items()}
+        g = torch.Generator().manual_seed(seed)
+        ws = torch.randn(n_sample, 14, 512, generator=g)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            RN.synthesis_network(ws, self._cpu_sd, self.RES, noise_mode="const")
+        return time.perf_counter() - t0
+
+
+WORKLOADS = {"opsweep": OpSweep, "synthesis": Synthesis}
 
 
 def pick_workload(args):
@@ -257,7 +348,7 @@ def pick_workload(args):
     return WORKLOADS[name](args.batch)
 
 
-DEFAULT_WORKLOAD = "opsweep"
+DEFAULT_WORKLOAD = "synthesis"
 
 
 def run_reference(args, world, rank):
@@ -275,10 +366,10 @@ def run_reference(args, world, rank):
     value = wl.units_per_step() * (n_sample / wl.n) / sec
     line = {"impl": "reference", "metric": wl.metric, "value": round(value, 4), "unit": wl.unit, "n_gpus": args.gpus,
             "steps": len(t), "warmup": 1, "ms_per_step": round(sec * 1e3 * wl.n / n_sample, 3), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl.name, "device": "host CPU"},
             "cpu_baseline": {"value": round(value, 4), "unit": wl.unit, "cores": cores, "kind": "port",
-                             "sample": "%d of %d images per tensor per step, oracle/ref_ops.py (torch CPU ref path)" % (n_sample, wl.n)},
+                             "sample": "%d of the %d images of a step, oracle/ (torch CPU restatement of the reference impl='ref' path)" % (n_sample, wl.n)},
             "e2e": {"value": round(value, 4), "unit": wl.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -353,13 +444,13 @@ def main():
             wl.cpu_step(1)
             sec = min(wl.cpu_step(1) for _ in range(2))
             cpu = {"value": round(wl.units_per_step() / wl.n / sec, 4), "unit": wl.unit, "cores": cores, "kind": "port",
-                   "sample": "1 of %d images per tensor per step, oracle/ref_ops.py (torch CPU restatement of impl='ref')" % wl.n}
+                   "sample": "1 of the %d images of a step, oracle/ (torch CPU restatement of the reference impl='ref' path)" % wl.n}
     barrier(world)
     if rank == 0:
         line = {"metric": wl.metric, "value": round(value, 3), "unit": wl.unit, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
-                "config": {"workload": wl.name, "batch_per_gpu": wl.n, "l2": "inputs larger than L2 (every tensor >= 67 MB)",
+                "config": {"workload": wl.name, "batch_per_gpu": wl.n, "l2": getattr(wl, "l2_note", "working set per step larger than L2 (activations >= 67 MB per layer at 64^2 and above)"),
                            "parallelism": "dp%d (independent shards, no data-path collective)" % world},
                 "clocks": clocks,
                 "e2e": {"value": round(e2e_value, 3), "unit": wl.unit, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
