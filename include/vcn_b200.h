@@ -126,6 +126,7 @@ typedef struct {
   int out_h, out_w;         /* must match the kind: (h, w), (2h+1, 2w+1) or ((h-1)/2, (w-1)/2) */
   int y_dtype;              /* VCN_F32 / VCN_BF16 / VCN_F16 */
   int64_t ys[4];            /* element strides of y for (n, c, h, w): NCHW, channels_last or padded pitch */
+  int w_per_sample;         /* wt has a leading sample dimension [n][tap][cout][cin_pad] (per-sample modulated weights) */
 } vcn_conv_desc;
 
 int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat,

@@ -33,7 +33,7 @@ class ConvDesc(_c.Structure):
 
     _fields_ = [
         ("kind", _i), ("n", _i), ("h", _i), ("w", _i), ("cin_pad", _i), ("cout", _i), ("kh", _i), ("kw", _i),
-        ("out_h", _i), ("out_w", _i), ("y_dtype", _i), ("ys", _i64 * 4),
+        ("out_h", _i), ("out_w", _i), ("y_dtype", _i), ("ys", _i64 * 4), ("w_per_sample", _i),
     ]
 
 

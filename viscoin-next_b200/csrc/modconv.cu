@@ -26,26 +26,28 @@ constexpr int kBlockM = 128;  // pixels per CTA tile = UMMA M
 constexpr int kBlockK = 64;   // bf16 channels per k-block = one 128-byte swizzle span
 constexpr int kUmmaK = 16;
 constexpr int kMaxTaps = 9;
-constexpr int kMaxGroups = 4;
+constexpr int kMaxPhases = 4;
+constexpr int kEpilogueWarps = 4;
 constexpr int kThreads = 192;
 constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
 
 struct ConvTap {
   int dy, dx;  // pixel shift of the A tile in the M grid
   int wtap;    // index of the tap in the packed weights
-  int group;   // accumulator group
 };
 
 struct IgemmArgs {
-  ConvTap taps[kMaxTaps];
-  int num_taps, num_groups;
-  int g_oy[kMaxGroups], g_ox[kMaxGroups];  // output pixel = (py * o_mul + g_oy, px * o_mul + g_ox)
+  ConvTap taps[kMaxTaps];               // sorted by output phase
+  int phase_first[kMaxPhases + 1];      // taps of phase p: [phase_first[p], phase_first[p+1])
+  int num_phases;
+  int g_oy[kMaxPhases], g_ox[kMaxPhases];  // output pixel = (py * o_mul + g_oy, px * o_mul + g_ox)
   int o_mul;
   int a_mul;           // A-tile origin = tile origin * a_mul + tap shift (2 for the stride-2 convolution)
   int grid_h, grid_w;  // extent of the M grid (pixels that own accumulator rows)
   int n, cout, out_h, out_w;
-  int tw, th, tn, tiles_w, tiles_h;
+  int tw, th, tn, tiles_w, tiles_h, tiles_m, tiles_total;
   int n_tile, kblocks_c, stages, tmem_cols;
+  int w_per_sample;
   void* y;
   int y_dtype;
   int64_t ys[4];
@@ -63,24 +65,21 @@ template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v;
 template <> __device__ __forceinline__ __half cvt_out<__half>(float v) { return __float2half_rn(v); }
 template <> __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
 
-template <typename T>
-__device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_t (&acc)[32], int n, int oy, int ox,
-                                               int co0, float noise) {
-  // 32 consecutive output channels co0.. of one pixel
-  T* ybase = static_cast<T*>(a.y) + (int64_t)n * a.ys[0] + (int64_t)oy * a.ys[2] + (int64_t)ox * a.ys[3];
-  const float* scale = a.scale ? a.scale + (int64_t)n * a.cout : nullptr;
+// 32 consecutive output channels (co0..) of one pixel: demodulate, add noise, bias + activation, store.
+// s_scale / s_bias point at the shared-memory copies for channel co0 (scale may be NULL = 1, bias NULL = 0).
+template <typename T, int ACT>
+__device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_t (&acc)[32], T* __restrict__ ybase,
+                                               int co0, float noise, const float* __restrict__ s_scale,
+                                               const float* __restrict__ s_bias, bool has_scale) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
-    const int co = co0 + j;
     float r = __uint_as_float(acc[j]);
-    if (co < a.cout) {
-      if (scale) r *= scale[co];
-      r += noise;
-      if (a.act) {
-        if (a.bias) r += a.bias[co];
-        r = act_eval<float, 0>(r, 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
-      }
+    if (has_scale) r *= s_scale[j];
+    r += noise;
+    if (ACT != -1) {
+      r += s_bias[j];
+      r = act_eval<float, (ACT > 0 ? ACT : 0)>(r, 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
     }
     v[j] = r;
   }
@@ -94,12 +93,41 @@ __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_
       *reinterpret_cast<Vec16<T>*>(ybase + (co0 + j)) = o;
     }
   } else {
+    const int64_t cs = a.ys[1];
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const int co = co0 + j;
-      if (co < a.cout) ybase[(int64_t)co * a.ys[1]] = cvt_out<T>(v[j]);
-    }
+    for (int j = 0; j < 32; ++j)
+      if (co0 + j < a.cout) ybase[(int64_t)(co0 + j) * cs] = cvt_out<T>(v[j]);
   }
+}
+
+template <typename T>
+__device__ __forceinline__ void epilogue_dispatch(const IgemmArgs& a, const uint32_t (&acc)[32], T* ybase, int co0,
+                                                  float noise, const float* s_scale, const float* s_bias, bool has_scale) {
+  if (a.act == 0) epilogue_store<T, -1>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
+  else if (a.act == VCN_ACT_LRELU) epilogue_store<T, VCN_ACT_LRELU>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
+  else if (a.act == VCN_ACT_LINEAR) epilogue_store<T, VCN_ACT_LINEAR>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
+  else epilogue_store<T, 0>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
+}
+
+struct TileCoord {
+  int x0, y0, n0, co0, phase;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const IgemmArgs& a, int tile) {
+  // m-tiles fastest: consecutive CTAs share the weight tile (L2 reuse of B), then phases, then out-channel tiles
+  int mt = tile % a.tiles_m;
+  int r = tile / a.tiles_m;
+  TileCoord t;
+  t.phase = r % a.num_phases;
+  t.co0 = (r / a.num_phases) * a.n_tile;
+  const int wi = mt % a.tiles_w; mt /= a.tiles_w;
+  const int hi = mt % a.tiles_h;
+  t.x0 = wi * a.tw; t.y0 = hi * a.th; t.n0 = (mt / a.tiles_h) * a.tn;
+  return t;
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -112,17 +140,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t stage_bytes = kABytes + b_bytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)a.stages * stage_bytes);
   uint64_t* empty_bar = full_bar + a.stages;
-  uint64_t* tmem_full_bar = empty_bar + a.stages;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint64_t* tmem_full_bar = empty_bar + a.stages;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;     // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  float* s_par = reinterpret_cast<float*>(tmem_ptr_smem + 4);  // [2 acc stages][scale n_tile | bias n_tile]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int mt = blockIdx.x;
-  const int tile_wi = mt % a.tiles_w; mt /= a.tiles_w;
-  const int tile_hi = mt % a.tiles_h;
-  const int tile_ni = mt / a.tiles_h;
-  const int x0 = tile_wi * a.tw, y0 = tile_hi * a.th, n0 = tile_ni * a.tn;
-  const int co_tile0 = blockIdx.y * a.n_tile;
-  const int num_kb = a.num_taps * a.kblocks_c;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -131,7 +154,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       mbar_init(full_bar + s, 1);
       mbar_init(empty_bar + s, 1);
     }
-    mbar_init(tmem_full_bar, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tmem_full_bar + s, 1);
+      mbar_init(tmem_empty_bar + s, kEpilogueWarps);
+    }
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc(tmem_ptr_smem, (uint32_t)a.tmem_cols);
@@ -143,63 +169,96 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int it = 0; it < num_kb; ++it) {
-        const int s = it % a.stages;
-        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
-        mbar_wait(empty_bar + s, ph ^ 1u);
-        const int t = it / a.kblocks_c, cb = it - t * a.kblocks_c;
-        const ConvTap tap = a.taps[t];
-        unsigned char* sa = smem + (size_t)s * stage_bytes;
-        mbar_expect_tx(full_bar + s, stage_bytes);
-        tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, x0 * a.a_mul + tap.dx, y0 * a.a_mul + tap.dy, n0);
-        tma_load_3d(sa + kABytes, &tmap_b, full_bar + s, cb * kBlockK, co_tile0, tap.wtap);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(a, tile);
+        const int nw = a.w_per_sample ? tc.n0 : 0;
+        for (int t = a.phase_first[tc.phase]; t < a.phase_first[tc.phase + 1]; ++t) {
+          const ConvTap tap = a.taps[t];
+          const int ax = tc.x0 * a.a_mul + tap.dx, ay = tc.y0 * a.a_mul + tap.dy;
+          for (int cb = 0; cb < a.kblocks_c; ++cb) {
+            mbar_wait(empty_bar + s, ph ^ 1u);
+            unsigned char* sa = smem + (size_t)s * stage_bytes;
+            mbar_expect_tx(full_bar + s, stage_bytes);
+            tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, ax, ay, tc.n0);
+            tma_load_4d(sa + kABytes, &tmap_b, full_bar + s, cb * kBlockK, tc.co0, tap.wtap, nw);
+            if (++s == a.stages) { s = 0; ph ^= 1u; }
+          }
+        }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16_f32(kBlockM, a.n_tile);
-      int cur_group = -1;
-      for (int it = 0; it < num_kb; ++it) {
-        const int s = it % a.stages;
-        const uint32_t ph = (uint32_t)(it / a.stages) & 1u;
-        const int t = it / a.kblocks_c;
-        const int g = a.taps[t].group;
-        mbar_wait(full_bar + s, ph);
+      int s = 0;
+      uint32_t ph = 0;
+      int tile_iter = 0;
+      for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
+        const TileCoord tc = decode_tile(a, tile);
+        const int num_kb = (a.phase_first[tc.phase + 1] - a.phase_first[tc.phase]) * a.kblocks_c;
+        const int as = tile_iter & 1;
+        const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
+        mbar_wait(tmem_empty_bar + as, aph ^ 1u);  // epilogue has drained this accumulator stage
         tcgen05_fence_after();
-        const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
-        const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + kABytes);
-        const uint32_t d_tmem = tmem_base + (uint32_t)(g * a.n_tile);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * a.n_tile);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar + s, ph);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+          const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + kABytes);
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
-          umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (g == cur_group || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
+            umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + s);
+          if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
-        cur_group = g;
-        umma_commit(empty_bar + s);
+        umma_commit(tmem_full_bar + as);
       }
-      umma_commit(tmem_full_bar);
     }
   } else {
     // ===== epilogue: warps 2..5 own TMEM lane quarters (warp % 4) =====
     const int q = warp & 3;
+    const int et = threadIdx.x - 64;  // 0..127
     const int m = q * 32 + lane;
     const int tw_i = m % a.tw;
     const int th_i = (m / a.tw) % a.th;
     const int tn_i = m / (a.tw * a.th);
-    const int px = x0 + tw_i, py = y0 + th_i, n = n0 + tn_i;
-    const bool row_ok = n < a.n && py < a.grid_h && px < a.grid_w;
-    mbar_wait(tmem_full_bar, 0);
-    tcgen05_fence_after();
-    for (int g = 0; g < a.num_groups; ++g) {
-      const int oy = py * a.o_mul + a.g_oy[g], ox = px * a.o_mul + a.g_ox[g];
-      const bool ok = row_ok && oy < a.out_h && ox < a.out_w;
+    const bool stage_scale = a.scale != nullptr && a.tn == 1;
+    int tile_iter = 0;
+    for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
+      const TileCoord tc = decode_tile(a, tile);
+      const int as = tile_iter & 1;
+      const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
+      float* sp = s_par + as * 2 * a.n_tile;
+      // per-tile channel parameters -> shared memory (read while the MMAs of this tile are still running)
+      for (int j = et; j < a.n_tile; j += kEpilogueWarps * 32) {
+        const int co = tc.co0 + j;
+        float sc = 1.f, bi = 0.f;
+        if (co < a.cout) {
+          if (stage_scale) sc = a.scale[(int64_t)tc.n0 * a.cout + co];
+          if (a.bias) bi = a.bias[co];
+        }
+        sp[j] = sc;
+        sp[a.n_tile + j] = bi;
+      }
+      const int px = tc.x0 + tw_i, py = tc.y0 + th_i, n = tc.n0 + tn_i;
+      const int oy = py * a.o_mul + a.g_oy[tc.phase], ox = px * a.o_mul + a.g_ox[tc.phase];
+      const bool ok = n < a.n && py < a.grid_h && px < a.grid_w && oy < a.out_h && ox < a.out_w;
       float noise = 0.f;
       if (ok && a.noise) noise = a.noise[(int64_t)n * a.noise_stride_n + (int64_t)oy * a.out_w + ox];
+      const int64_t yoff = ok ? (int64_t)n * a.ys[0] + (int64_t)oy * a.ys[2] + (int64_t)ox * a.ys[3] : 0;
+      const float* gscale = (a.scale && !stage_scale && ok) ? a.scale + (int64_t)n * a.cout : nullptr;
+      named_bar_sync(1, kEpilogueWarps * 32);
+      mbar_wait(tmem_full_bar + as, aph);
+      tcgen05_fence_after();
       for (int c = 0; c < a.n_tile; c += 32) {
-        if (co_tile0 + c >= a.cout) break;  // warp-uniform
+        if (tc.co0 + c >= a.cout) break;  // warp-uniform
         uint32_t acc[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(g * a.n_tile + c);
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * a.n_tile + c);
         if (a.n_tile - c >= 32) {
           tmem_ld_32x32(taddr, acc);
         } else {  // n_tile is a multiple of 16: last half chunk
@@ -210,14 +269,28 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         tmem_ld_wait();
         if (ok) {
-          if (a.y_dtype == VCN_F32) epilogue_store<float>(a, acc, n, oy, ox, co_tile0 + c, noise);
-          else if (a.y_dtype == VCN_BF16) epilogue_store<__nv_bfloat16>(a, acc, n, oy, ox, co_tile0 + c, noise);
-          else epilogue_store<__half>(a, acc, n, oy, ox, co_tile0 + c, noise);
+          float lsc[32];
+          const float* scp = sp + c;
+          bool has_scale = stage_scale;
+          if (gscale) {  // several samples in one tile (tiny resolutions): per-row scale from global memory
+#pragma unroll
+            for (int j = 0; j < 32; ++j) lsc[j] = (tc.co0 + c + j < a.cout) ? gscale[tc.co0 + c + j] : 1.f;
+            scp = lsc;
+            has_scale = true;
+          }
+          const float* bip = sp + a.n_tile + c;
+          if (a.y_dtype == VCN_F32) epilogue_dispatch<float>(a, acc, static_cast<float*>(a.y) + yoff, tc.co0 + c, noise, scp, bip, has_scale);
+          else if (a.y_dtype == VCN_BF16) epilogue_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + yoff, tc.co0 + c, noise, scp, bip, has_scale);
+          else epilogue_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, tc.co0 + c, noise, scp, bip, has_scale);
         }
       }
+      // hand the accumulator stage back to the MMA warp
+      tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty_bar + as);
     }
-    tcgen05_fence_before();
   }
+  tcgen05_fence_before();
   __syncthreads();
   if (warp == 2) {
     tcgen05_fence_after();
@@ -232,11 +305,12 @@ inline int pow2_ceil(int v) {
 }
 
 // (tw, th, tn) with tw*th*tn = 128 minimising the number of CTA tiles; ties -> wider rows
-void choose_tile(int gw, int gh, int n, int* tw, int* th, int* tn) {
+void choose_tile(int gw, int gh, int n, int one_sample, int* tw, int* th, int* tn) {
   int64_t best = -1;
   for (int w = 128; w >= 1; w >>= 1) {
     for (int h = 1; w * h <= 128; h <<= 1) {
       const int nn = 128 / (w * h);
+      if (one_sample && nn != 1) continue;  // per-sample weights: a tile must not straddle samples
       const int64_t tiles = (int64_t)((gw + w - 1) / w) * ((gh + h - 1) / h) * ((n + nn - 1) / nn);
       if (best < 0 || tiles < best) { best = tiles; *tw = w; *th = h; *tn = nn; }
     }
@@ -259,41 +333,44 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   IgemmArgs a;
   memset(&a, 0, sizeof(a));
   const int kh = d->kh, kw = d->kw;
+  int num_taps = 0;
   if (d->kind == VCN_CONV_FPROP || d->kind == VCN_CONV_DGRAD) {
     VCN_REQUIRE(d->out_h == d->h && d->out_w == d->w, "conv_igemm: stride-1 output must be %dx%d", d->h, d->w);
     for (int ky = 0; ky < kh; ++ky)
       for (int kx = 0; kx < kw; ++kx) {
-        ConvTap& t = a.taps[a.num_taps++];
+        ConvTap& t = a.taps[num_taps++];
         if (d->kind == VCN_CONV_FPROP) { t.dy = ky - kh / 2; t.dx = kx - kw / 2; }
         else { t.dy = kh / 2 - ky; t.dx = kw / 2 - kx; }
         t.wtap = ky * kw + kx;
-        t.group = 0;
       }
-    a.num_groups = 1; a.o_mul = 1; a.grid_h = d->h; a.grid_w = d->w;
+    a.num_phases = 1; a.phase_first[1] = num_taps; a.o_mul = 1; a.grid_h = d->h; a.grid_w = d->w;
   } else if (d->kind == VCN_CONV_SCONV2) {
     VCN_REQUIRE(kh == 3 && kw == 3, "conv_igemm: stride-2 conv needs a 3x3 kernel");
     VCN_REQUIRE(d->h >= 3 && d->w >= 3 && d->h % 2 == 1 && d->w % 2 == 1 && d->out_h == (d->h - 1) / 2 && d->out_w == (d->w - 1) / 2,
                 "conv_igemm: stride-2 conv maps (2h+1, 2w+1) to (h, w); got %dx%d -> %dx%d", d->h, d->w, d->out_h, d->out_w);
     for (int ky = 0; ky < 3; ++ky)
       for (int kx = 0; kx < 3; ++kx) {
-        ConvTap& t = a.taps[a.num_taps++];
-        t.dy = ky; t.dx = kx; t.wtap = ky * 3 + kx; t.group = 0;
+        ConvTap& t = a.taps[num_taps++];
+        t.dy = ky; t.dx = kx; t.wtap = ky * 3 + kx;
       }
-    a.num_groups = 1; a.o_mul = 1; a.grid_h = d->out_h; a.grid_w = d->out_w;
+    a.num_phases = 1; a.phase_first[1] = num_taps; a.o_mul = 1; a.grid_h = d->out_h; a.grid_w = d->out_w;
   } else if (d->kind == VCN_CONV_TCONV2) {
     VCN_REQUIRE(kh == 3 && kw == 3, "conv_igemm: transposed conv needs a 3x3 kernel");
     VCN_REQUIRE(d->out_h == 2 * d->h + 1 && d->out_w == 2 * d->w + 1, "conv_igemm: transposed output must be %dx%d",
                 2 * d->h + 1, 2 * d->w + 1);
+    // output phase (a,b) = (oy&1, ox&1) collects the taps with ky%2==a, kx%2==b; input shift -(k>>1)
     for (int g = 0; g < 4; ++g) {
       const int pa = g >> 1, pb = g & 1;
       a.g_oy[g] = pa; a.g_ox[g] = pb;
+      a.phase_first[g] = num_taps;
       for (int ky = pa; ky < 3; ky += 2)
         for (int kx = pb; kx < 3; kx += 2) {
-          ConvTap& t = a.taps[a.num_taps++];
-          t.dy = -(ky >> 1); t.dx = -(kx >> 1); t.wtap = ky * 3 + kx; t.group = g;
+          ConvTap& t = a.taps[num_taps++];
+          t.dy = -(ky >> 1); t.dx = -(kx >> 1); t.wtap = ky * 3 + kx;
         }
     }
-    a.num_groups = 4; a.o_mul = 2; a.grid_h = d->h + 1; a.grid_w = d->w + 1;
+    a.phase_first[4] = num_taps;
+    a.num_phases = 4; a.o_mul = 2; a.grid_h = d->h + 1; a.grid_w = d->w + 1;
   } else {
     set_error("conv_igemm: unknown kind %d", d->kind);
     return VCN_ERR_INVALID;
@@ -303,25 +380,31 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   VCN_REQUIRE(aligned16(xhat) && aligned16(wt), "conv_igemm: xhat and wt must be 16-byte aligned");
 
   a.a_mul = d->kind == VCN_CONV_SCONV2 ? 2 : 1;
+  a.w_per_sample = d->w_per_sample ? 1 : 0;
   a.n = d->n; a.cout = d->cout; a.out_h = d->out_h; a.out_w = d->out_w;
-  choose_tile(a.grid_w, a.grid_h, d->n, &a.tw, &a.th, &a.tn);
+  choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample, &a.tw, &a.th, &a.tn);
   a.tiles_w = (a.grid_w + a.tw - 1) / a.tw;
   a.tiles_h = (a.grid_h + a.th - 1) / a.th;
   const int tiles_n = (d->n + a.tn - 1) / a.tn;
-  const int max_tile = 512 / a.num_groups > 256 ? 256 : 512 / a.num_groups;
+  a.tiles_m = a.tiles_w * a.tiles_h * tiles_n;
+  // two accumulator stages of n_tile fp32 columns each must fit the 512 TMEM columns
   a.n_tile = (d->cout + 15) / 16 * 16;
-  if (a.n_tile > max_tile) a.n_tile = max_tile;
+  if (a.n_tile > 256) a.n_tile = 256;
+  const int tiles_co = (d->cout + a.n_tile - 1) / a.n_tile;
+  const int64_t total = (int64_t)a.tiles_m * a.num_phases * tiles_co;
+  VCN_REQUIRE(total <= 0x7fffffffLL, "conv_igemm: too many tiles");
+  a.tiles_total = (int)total;
   a.kblocks_c = (d->cin_pad + kBlockK - 1) / kBlockK;
-  a.tmem_cols = pow2_ceil(a.num_groups * a.n_tile);
+  a.tmem_cols = pow2_ceil(2 * a.n_tile);
   if (a.tmem_cols < 32) a.tmem_cols = 32;
   const size_t stage_bytes = kABytes + (size_t)a.n_tile * kBlockK * 2;
-  a.stages = (int)((200 * 1024) / stage_bytes);
+  const size_t tail_bytes = (2 * (size_t)8 + 4) * 8 + 16 + 4 * (size_t)a.n_tile * sizeof(float) + 64;
+  a.stages = (int)((220 * 1024 - 1024 - tail_bytes) / stage_bytes);
   if (a.stages > 8) a.stages = 8;
-  if (a.stages > a.num_taps * a.kblocks_c) a.stages = a.num_taps * a.kblocks_c;
   if (a.stages < 1) a.stages = 1;
-  // more than 256 TMEM columns must never share an SM with a second CTA of this kernel (allocation would spin)
-  size_t smem = 1024 + (size_t)a.stages * stage_bytes + (2 * (size_t)a.stages + 1) * 8 + 16;
-  if (a.tmem_cols > 256 && smem < 120 * 1024) smem = 120 * 1024;
+  // one CTA per SM (launch bounds); TMEM allocations above 256 columns additionally rely on it
+  size_t smem = 1024 + (size_t)a.stages * stage_bytes + tail_bytes;
+  if (smem < 120 * 1024) smem = 120 * 1024;
 
   a.y = y; a.y_dtype = d->y_dtype;
   for (int i = 0; i < 4; ++i) a.ys[i] = d->ys[i];
@@ -347,15 +430,18 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
     if (rc) return rc;
   }
   {
-    const uint64_t dims[3] = {(uint64_t)d->cin_pad, (uint64_t)d->cout, (uint64_t)(kh * kw)};
-    const uint64_t strides[2] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->cout * d->cin_pad * 2};
-    const uint32_t box[3] = {(uint32_t)kBlockK, (uint32_t)a.n_tile, 1u};
-    const int rc = make_tensor_map(&tmap_b, VCN_BF16, 3, wt, dims, strides, box, nullptr, 1);
+    const uint64_t taps = (uint64_t)(kh * kw);
+    const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->cout, taps, (uint64_t)(a.w_per_sample ? d->n : 1)};
+    const uint64_t strides[3] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->cout * d->cin_pad * 2,
+                                 taps * d->cout * d->cin_pad * 2};
+    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)a.n_tile, 1u, 1u};
+    const int rc = make_tensor_map(&tmap_b, VCN_BF16, 4, wt, dims, strides, box, nullptr, 1);
     if (rc) return rc;
   }
   VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((unsigned)((int64_t)a.tiles_w * a.tiles_h * tiles_n), (unsigned)((d->cout + a.n_tile - 1) / a.n_tile));
-  conv_igemm_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, a);
+  int grid = sm_count();
+  if (grid > a.tiles_total) grid = a.tiles_total;
+  conv_igemm_kernel<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, a);
   VCN_LAUNCH_CHECK("conv_igemm_kernel");
   return VCN_OK;
 }
