@@ -156,3 +156,21 @@ def test_full_size_roundtrip_properties():
         # one plane against the oracle
         xs = x.detach()[1:2, 1:2].cpu()
         assert _rel(y.detach()[1:2, 1:2], R.upfirdn2d(xs, f4.cpu(), **kw)) <= 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(2, 64, 17, 17), (1, 72, 33, 40), (2, 8, 9, 9), (1, 128, 65, 65), (3, 16, 5, 70)])
+@pytest.mark.parametrize("pat", ["A", "A_bwd"])
+def test_channels_last_16bit_fast_path(dtype, shape, pat):
+    """The TMA-staged channels-last kernel (16-bit storage, up = down = 1): the FIR after the transposed convolution
+    and its adjoint.  Oracle in fp32 on the rounded inputs; <= 2 ulp of the storage type."""
+    U = _ops()
+    kw = PATTERNS[pat]
+    g = torch.Generator().manual_seed(sum(shape))
+    x = torch.randn(shape, generator=g).to(dtype)
+    f4 = R.setup_filter([1, 3, 3, 1])
+    y_ref = R.upfirdn2d(x.float(), f4, **kw)
+    xc = x.cuda().contiguous(memory_format=torch.channels_last)
+    y = U.upfirdn2d(xc, f4.cuda(), impl="cuda", **kw)
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, y_ref) <= 2 * torch.finfo(dtype).eps

@@ -248,6 +248,165 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// channels-last kernel: 16-bit storage, up = down = 1, filter <= 4x4 (the FIR after the transposed convolution and its
+// adjoint).  x is NHWC-strided (xs[1] == 1).  One CTA = 16 x 32 output pixels x 64 channels; the (16+3) x (32+3) x 64ch
+// halo tile is ONE TMA 4-D box load (inner coordinate = channel offset, always 16-byte aligned; out-of-bounds pixels
+// zero-fill = the op's padding).  Thread = 8 channels (one 16-byte vector) x four 2x2 pixel blocks: each staged vector
+// is read once from shared memory per 2x2 block (25 LDS.128 for 4 outputs) - the 8 threads of a quarter warp read the
+// 128 contiguous bytes of one pixel, so the reads are bank-conflict free.
+// ---------------------------------------------------------------------------------------------
+constexpr int kClTx = 32, kClTy = 16, kClCb = 64;
+
+template <typename T, typename TO>
+__global__ void __launch_bounds__(256, 2)
+upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int HX = kClTx + kF - 1, HY = kClTy + kF - 1;
+  T* tile = reinterpret_cast<T*>(smem_raw);                                   // [HY][HX][64]
+  float* s_par = reinterpret_cast<float*>(smem_raw + (size_t)HY * HX * kClCb * sizeof(T));  // scale[64] | bias[64] | flt[16]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_par + 2 * kClCb + kF * kF);
+
+  const int tid = threadIdx.x;
+  int bid = blockIdx.x;
+  const int bx = bid % tiles_x; bid /= tiles_x;
+  const int by = bid % tiles_y;
+  const int n = bid / tiles_y;
+  const int c0 = blockIdx.y * kClCb;
+  const int ox0 = bx * kClTx, oy0 = by * kClTy;
+
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    mbar_expect_tx(bar, (uint32_t)(HY * HX * kClCb * sizeof(T)));
+    tma_load_4d(tile, &tmap, bar, c0, ox0 - a.padx0, oy0 - a.pady0, n);
+  }
+  if (tid < kF * kF) {
+    const int fy = tid / kF, fx = tid % kF;
+    float w = 0.f;
+    if (fy < a.fh && fx < a.fw) w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
+    s_par[2 * kClCb + tid] = w * a.gain;
+  } else if (tid >= 64 && tid < 64 + kClCb) {
+    const int c = c0 + tid - 64;
+    s_par[tid - 64] = (a.scale && c < a.c) ? a.scale[(int64_t)n * a.c + c] : 1.f;
+  } else if (tid >= 128 && tid < 128 + kClCb) {
+    const int c = c0 + tid - 128;
+    s_par[kClCb + tid - 128] = (a.bias && a.act && c < a.c) ? a.bias[c] : 0.f;
+  }
+  __syncthreads();
+  mbar_wait(bar, 0);
+
+  float flt[kF][kF];
+#pragma unroll
+  for (int i = 0; i < kF; ++i)
+#pragma unroll
+    for (int j = 0; j < kF; ++j) flt[i][j] = s_par[2 * kClCb + i * kF + j];
+
+  const int cg = tid & 7;          // channel group: channels c0 + cg*8 .. +7
+  const int pb = tid >> 3;         // 0..31
+  const int c = c0 + cg * 8;
+  if (c >= a.c) return;
+  float sc[8], bi[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { sc[k] = s_par[cg * 8 + k]; bi[k] = s_par[kClCb + cg * 8 + k]; }
+
+#pragma unroll 1
+  for (int it = 0; it < 4; ++it) {
+    const int blk = pb + it * 32;               // 128 blocks of 2x2 pixels: 16 wide x 8 high
+    const int bxx = blk % (kClTx / 2), byy = blk / (kClTx / 2);
+    const int oy = oy0 + 2 * byy, ox = ox0 + 2 * bxx;
+    if (oy >= a.out_h || ox >= a.out_w) continue;
+    float acc[2][2][8];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[i][j][k] = 0.f;
+#pragma unroll
+    for (int wy = 0; wy < kF + 1; ++wy) {
+#pragma unroll
+      for (int wx = 0; wx < kF + 1; ++wx) {
+        const Vec16<T> v = *reinterpret_cast<const Vec16<T>*>(tile + ((size_t)(2 * byy + wy) * HX + (2 * bxx + wx)) * kClCb + cg * 8);
+        float f[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f[k] = to_acc<T>(v.v[k]);
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy) {
+          const int fy = wy - dy;
+          if (fy < 0 || fy >= kF) continue;
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) {
+            const int fx = wx - dx;
+            if (fx < 0 || fx >= kF) continue;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[dy][dx][k] = fmaf(f[k], flt[fy][fx], acc[dy][dx][k]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int yy = oy + dy, xx = ox + dx;
+        if (yy >= a.out_h || xx >= a.out_w) continue;
+        float nz = 0.f;
+        if (a.noise) nz = a.noise[(int64_t)n * a.noise_stride_n + (int64_t)yy * a.out_w + xx];
+        TO* dst = static_cast<TO*>(a.y) + n * a.ys[0] + yy * a.ys[2] + xx * a.ys[3] + c;
+        constexpr int VO = 16 / sizeof(TO);
+#pragma unroll
+        for (int h = 0; h < 8 / VO; ++h) {
+          Vec16<TO> o;
+#pragma unroll
+          for (int k = 0; k < VO; ++k) {
+            float r = acc[dy][dx][h * VO + k] * sc[h * VO + k] + nz;
+            if (a.act) r = act_eval<float, 0>(r + bi[h * VO + k], 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+            o.v[k] = from_acc<TO>(r);
+          }
+          *reinterpret_cast<Vec16<TO>*>(dst + h * VO) = o;
+        }
+      }
+    }
+  }
+}
+
+// Eligibility + launch of the channels-last kernel.  Returns -1 when the configuration is not covered.
+template <typename T>
+int try_launch_cl(const UpfirdnArgs& a, int dtype, int y_dtype, cudaStream_t st) {
+  if (sizeof(T) != 2) return -1;
+  if (!(a.upx == 1 && a.upy == 1 && a.downx == 1 && a.downy == 1 && a.fw <= kF && a.fh <= kF)) return -1;
+  if (!(a.xs[1] == 1 && a.ys[1] == 1 && a.c % 8 == 0)) return -1;
+  if (!(a.xs[0] % 8 == 0 && a.xs[2] % 8 == 0 && a.xs[3] % 8 == 0 && aligned16(a.x) && aligned16(a.y))) return -1;
+  const int64_t vo = y_dtype == VCN_F32 ? 4 : 8;
+  if (!(a.ys[0] % vo == 0 && a.ys[2] % vo == 0 && a.ys[3] % vo == 0)) return -1;
+  CUtensorMap tmap;
+  memset(&tmap, 0, sizeof(tmap));
+  const uint64_t dims[4] = {(uint64_t)a.c, (uint64_t)a.in_w, (uint64_t)a.in_h, (uint64_t)a.n};
+  const uint64_t strides[3] = {(uint64_t)a.xs[3] * 2, (uint64_t)a.xs[2] * 2, (uint64_t)a.xs[0] * 2};
+  const uint32_t box[4] = {(uint32_t)kClCb, (uint32_t)(kClTx + kF - 1), (uint32_t)(kClTy + kF - 1), 1u};
+  const int rc = make_tensor_map(&tmap, dtype, 4, a.x, dims, strides, box, nullptr, 0);
+  if (rc) return rc;
+  const int tiles_x = (a.out_w + kClTx - 1) / kClTx, tiles_y = (a.out_h + kClTy - 1) / kClTy;
+  const size_t smem = (size_t)(kClTy + kF - 1) * (kClTx + kF - 1) * kClCb * 2 + (2 * kClCb + kF * kF) * sizeof(float) + 16;
+  dim3 grid((unsigned)((int64_t)tiles_x * tiles_y * a.n), (unsigned)((a.c + kClCb - 1) / kClCb));
+  if (y_dtype == VCN_F32) {
+    auto kern = upfirdn2d_cl_kernel<T, float>;
+    VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
+  } else {
+    auto kern = upfirdn2d_cl_kernel<T, T>;
+    VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
+  }
+  VCN_LAUNCH_CHECK("upfirdn2d_cl_kernel");
+  return VCN_OK;
+}
+
 inline int pow2_ceil(int v) {
   int p = 1;
   while (p < v) p <<= 1;
@@ -329,6 +488,10 @@ int run(const UpfirdnArgs& a, int dtype, cudaStream_t st) {
   const bool sq = a.upx == a.upy && a.downx == a.downy;
   const int up = a.upx, down = a.downx;
   const bool combo = (up == 1 && down == 1) || (up == 2 && down == 1) || (up == 1 && down == 2);
+  if constexpr (sizeof(T) == 2) {
+    const int rc = try_launch_cl<T>(a, dtype, dtype, st);
+    if (rc >= 0) return rc;
+  }
   if constexpr (sizeof(T) != 8)
   if (dense_in && dense_out && small_f && sq && combo && a.out_w >= 4 && a.out_h >= 4) {
     const TileGeom g = make_geom<T>(a, up, down);
