@@ -134,6 +134,10 @@ int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const flo
 int vcn_pack_weights(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io,
                      void* wt, int cols_pad, float* wsq, void* stream);
 int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int cin, int cout, void* stream);
+/* Per-sample modulated (and, with dcoef, demodulated) weights of the reference's fused branch (networks.py:54-60):
+ * wn bf16 [n][kh*kw][cout][cin_pad] = W[co,ci,tap] * styles[n,ci] * dcoef[n,co]; consumed with desc.w_per_sample = 1. */
+int vcn_pack_weights_mod(const void* w, int w_dtype, const float* styles, const float* dcoef, void* wn,
+                         int n, int cout, int cin, int cin_pad, int kh, int kw, void* stream);
 /* epi (may be NULL) reuses vcn_upfirdn2d_epilogue: acc * scale[n,co] + noise[n?,oy,ox], then bias_act. */
 int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_desc* desc,
                    const vcn_upfirdn2d_epilogue* epi, void* stream);

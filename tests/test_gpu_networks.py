@@ -46,6 +46,9 @@ def test_generator_golden(golden):
     G.eval()
     z = g.t("G.z", device="cuda")
     assert _rel(G(z, None, noise_mode="const"), g.t("G.full.img")) <= 2e-2
+    with torch.no_grad():  # resident bf16-NHWC inference pipeline (per-sample weights / channels-last FIR)
+        assert _rel(G(z, None, noise_mode="const"), g.t("G.full.img")) <= 3e-2
+        assert _rel(G.synthesis(g.t("G.eval.ws", device="cuda"), noise_mode="const"), g.t("G.eval.img")) <= 3e-2
     assert _rel(G(z, None, truncation_psi=0.7, noise_mode="none"), g.t("G.trunc.img")) <= 2e-2
     # noise_mode='random' consumes torch.randn exactly like the reference (same shapes, same order)
     torch.manual_seed(5)
@@ -98,6 +101,9 @@ def test_full_size_synthesis_runs():
     ws = torch.randn(8, S.num_ws, 512, device="cuda")
     img = S(ws, noise_mode="const")
     assert img.shape == (8, 3, 256, 256) and torch.isfinite(img).all()
+    with torch.no_grad():  # the resident-activation pipeline agrees with the per-op path (both bf16 operands)
+        fast = S(ws, noise_mode="const")
+    assert _rel(fast, img) <= 3e-2
     one = S(ws[5:6], noise_mode="const")
     # the style FCs are library GEMMs whose batch-8 and batch-1 algorithms differ in the last fp32 bit; the bf16 rounding
     # of x*s turns some of those into 2^-9 operand differences, hence the operand-rounding tolerance, not 1e-5

@@ -250,6 +250,35 @@ __global__ void __launch_bounds__(128) demod_grad_kernel(float* __restrict__ ds,
   ds[(int64_t)in * cin + i] += styles[(int64_t)in * cin + i] * acc;
 }
 
+
+// Per-sample modulated weights (the reference's fused branch, networks.py:54-60): wn[n][tap][co][ci_pad] =
+// bf16( W[co,ci,tap] * s[n,ci] * d[n,co] ).  One CTA = one output channel x 128 input channels: the fp32 taps are read
+// once (coalesced) into shared memory and reused for every sample.
+template <typename T>
+__global__ void __launch_bounds__(128) pack_weights_mod_kernel(const T* __restrict__ w, const float* __restrict__ styles,
+                                                               const float* __restrict__ dcoef, __nv_bfloat16* __restrict__ wn,
+                                                               int n, int cout, int cin, int cin_pad, int taps) {
+  extern __shared__ float sw[];  // [128][taps]
+  const int co = blockIdx.y, ci0 = blockIdx.x * 128;
+  const int cnt = min(128, cin - ci0);
+  const T* src = w + ((int64_t)co * cin + ci0) * taps;
+  for (int i = threadIdx.x; i < cnt * taps; i += 128) sw[i] = to_acc<T>(src[i]);
+  __syncthreads();
+  const int ci = ci0 + threadIdx.x;
+  if (ci >= cin_pad) return;
+  for (int in = 0; in < n; ++in) {
+    float m = 0.f;
+    if (ci < cin) {
+      m = styles[(int64_t)in * cin + ci];
+      if (dcoef) m *= dcoef[(int64_t)in * cout + co];
+    }
+    for (int t = 0; t < taps; ++t) {
+      const float v = ci < cin ? sw[threadIdx.x * taps + t] * m : 0.f;
+      wn[(((int64_t)in * taps + t) * cout + co) * cin_pad + ci] = __float2bfloat16_rn(v);
+    }
+  }
+}
+
 template <typename T>
 int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* xhat, int n, int cin, int cin_pad, int h,
                  int w, cudaStream_t st) {
@@ -412,6 +441,28 @@ int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const floa
   dim3 grid((unsigned)((cin + 127) / 128), (unsigned)n);
   demod_grad_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(ds, styles, gsum, dcoef, wsq, n, cin, cout);
   VCN_LAUNCH_CHECK("demod_grad_kernel");
+  return VCN_OK;
+}
+
+
+int vcn_pack_weights_mod(const void* w, int w_dtype, const float* styles, const float* dcoef, void* wn, int n, int cout,
+                         int cin, int cin_pad, int kh, int kw, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && cout >= 1 && cin >= 1 && kh >= 1 && kw >= 1, "pack_weights_mod: bad shape");
+  VCN_REQUIRE(cin_pad >= cin && cin_pad % 8 == 0, "pack_weights_mod: cin_pad must be a multiple of 8 >= cin");
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(w && styles && wn, "pack_weights_mod: NULL pointer");
+  const int taps = kh * kw;
+  dim3 grid((unsigned)((cin_pad + 127) / 128), (unsigned)cout);
+  const size_t smem = (size_t)128 * taps * sizeof(float);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (w_dtype) {
+    case VCN_F32: pack_weights_mod_kernel<float><<<grid, 128, smem, st>>>(static_cast<const float*>(w), styles, dcoef, static_cast<__nv_bfloat16*>(wn), n, cout, cin, cin_pad, taps); break;
+    case VCN_F16: pack_weights_mod_kernel<__half><<<grid, 128, smem, st>>>(static_cast<const __half*>(w), styles, dcoef, static_cast<__nv_bfloat16*>(wn), n, cout, cin, cin_pad, taps); break;
+    case VCN_BF16: pack_weights_mod_kernel<__nv_bfloat16><<<grid, 128, smem, st>>>(static_cast<const __nv_bfloat16*>(w), styles, dcoef, static_cast<__nv_bfloat16*>(wn), n, cout, cin, cin_pad, taps); break;
+    default: set_error("pack_weights_mod: unsupported dtype %d", w_dtype); return VCN_ERR_INVALID;
+  }
+  VCN_LAUNCH_CHECK("pack_weights_mod_kernel");
   return VCN_OK;
 }
 

@@ -111,14 +111,16 @@ def make_epilogue(scale=None, noise=None, bias=None, act=None, alpha=None, gain=
     return e, hold
 
 
-def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_last=False, epilogue=None, out=None):
+def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_last=False, epilogue=None, out=None,
+               w_per_sample=False):
     """One vcn_conv_igemm launch.  xhat bf16 [N,H,W,Cin_pad]; wt bf16 [kh*kw, cout, Cin_pad].  Returns y as a
     logical [N,cout,OH,OW] tensor (NCHW memory, or channels_last memory when requested)."""
     lib = _lib.load()
     _lib.require_device(xhat.device.index)
     n, h, w, cin_pad = xhat.shape
     assert xhat.dtype == torch.bfloat16 and wt.dtype == torch.bfloat16 and xhat.is_contiguous() and wt.is_contiguous()
-    assert wt.shape == (kh * kw, cout, cin_pad), (wt.shape, (kh * kw, cout, cin_pad))
+    want = (n, kh * kw, cout, cin_pad) if w_per_sample else (kh * kw, cout, cin_pad)
+    assert tuple(wt.shape) == want, (tuple(wt.shape), want)
     oh, ow = (2 * h + 1, 2 * w + 1) if kind == _lib.CONV_TCONV2 else ((h - 1) // 2, (w - 1) // 2) if kind == _lib.CONV_SCONV2 else (h, w)
     if out is None:
         fmt = torch.channels_last if channels_last else torch.contiguous_format
@@ -127,13 +129,31 @@ def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_l
     if n == 0:
         return out
     d = _lib.ConvDesc(kind=kind, n=n, h=h, w=w, cin_pad=cin_pad, cout=cout, kh=kh, kw=kw, out_h=oh, out_w=ow,
-                      y_dtype=_lib.dtype_code(out.dtype), ys=_strides4(out))
+                      y_dtype=_lib.dtype_code(out.dtype), ys=_strides4(out), w_per_sample=int(w_per_sample))
     epi = ctypes.byref(epilogue) if epilogue is not None else None
     with torch.cuda.device(xhat.device):
         st = lib.vcn_conv_igemm(_lib.ptr(xhat), _lib.ptr(wt), _lib.ptr(out), ctypes.byref(d), epi,
                                 _lib.current_stream(xhat.device))
     _lib.check(st, "vcn_conv_igemm")
     return out
+
+
+def pack_weights_mod(weight, styles, dcoef=None):
+    """Per-sample weights of the fused branch (networks.py:54-60): bf16 [N, kh*kw, Cout, Cin_pad] = W * s[n,ci] * d[n,co]."""
+    lib = _lib.load()
+    weight = weight.detach().contiguous()
+    cout, cin, kh, kw = weight.shape
+    styles = styles.to(torch.float32).contiguous()
+    n = styles.shape[0]
+    cin_pad = _round_up(cin, 8)
+    wn = torch.empty([n, kh * kw, cout, cin_pad], dtype=torch.bfloat16, device=weight.device)
+    if n == 0:
+        return wn
+    with torch.cuda.device(weight.device):
+        st = lib.vcn_pack_weights_mod(_lib.ptr(weight), _lib.dtype_code(weight.dtype), _lib.ptr(styles), _lib.ptr(dcoef),
+                                      _lib.ptr(wn), n, cout, cin, cin_pad, kh, kw, _lib.current_stream(weight.device))
+    _lib.check(st, "vcn_pack_weights_mod")
+    return wn
 
 
 def bwd_pack(dy, y, epilogue, want_gsum, want_db):
@@ -375,3 +395,46 @@ def _modulated_conv2d_ref(x, weight, styles, noise, up, down, padding, resample_
     if noise is not None:
         x = x + noise.to(x.dtype)
     return x
+
+
+# ---- resident-activation pipeline (inference): activations stay bf16 NHWC between layers -------------------------------
+
+
+def layer_nhwc(act, weight, styles, noise=None, bias=None, up=1, resample_filter=None, demodulate=True, act_name="lrelu",
+               alpha=None, gain=None, clamp=None, per_sample=None, out_nchw_f32=False):
+    """One synthesis layer on a resident activation: act bf16 [N,H,W,Cin_pad] (NHWC, unmodulated) -> bf16 [N,H',W',Cout]
+    (or fp32 NCHW [N,Cout,H',W'] with out_nchw_f32, used by ToRGB).  No autograd (inference path).
+
+    per_sample=True  : the reference's fused branch - weights W*s[n]*d[n] per sample (vcn_pack_weights_mod), the GEMM
+                       reads the activation as is: no pass over the activation at all (large resolutions).
+    per_sample=False : the non-fused branch - xhat = act*s (one channels-last pass), shared weights, d in the epilogue
+                       (small resolutions, where N copies of the weights would outweigh the activation)."""
+    n, h, w, cin_pad = act.shape
+    cout, cin, kh, kw = weight.shape
+    assert act.dtype == torch.bfloat16 and act.is_contiguous() and cin_pad == _round_up(cin, 8)
+    if per_sample is None:
+        per_sample = (kh == 1) or h * w >= 128 * 128
+    styles32 = styles.to(torch.float32).contiguous()
+    d = None
+    if demodulate:
+        _, wsq = _packed(weight, False, False, True)
+        d = demod_coefs(styles32, wsq)
+    if per_sample:
+        wt = pack_weights_mod(weight, styles32, d)
+        xin, scale = act, None
+    else:
+        wt, _ = _packed(weight, False, False, demodulate)
+        xin, scale = modulate_pack(act.permute(0, 3, 1, 2)[:, :cin], styles32), d
+    if up == 1:
+        epi, hold = make_epilogue(scale=scale, noise=noise, bias=bias, act=act_name, alpha=alpha, gain=gain, clamp=clamp)
+        y = conv_igemm(xin, wt, _lib.CONV_FPROP, cout, kh, kw, out_dtype=torch.float32 if out_nchw_f32 else torch.bfloat16,
+                       channels_last=not out_nchw_f32, epilogue=epi, w_per_sample=per_sample)
+        del hold
+        return y if out_nchw_f32 else y.permute(0, 2, 3, 1)
+    assert up == 2 and kh == 3 and not out_nchw_f32
+    z = conv_igemm(xin, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=torch.bfloat16, channels_last=True, w_per_sample=per_sample)
+    epi, hold = make_epilogue(scale=scale, noise=noise, bias=bias, act=act_name, alpha=alpha, gain=gain, clamp=clamp)
+    f = resample_filter.to(device=act.device, dtype=torch.float32)
+    y = _upfirdn2d.launch(z, f, 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi)
+    del hold
+    return y.permute(0, 2, 3, 1)

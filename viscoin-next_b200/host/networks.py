@@ -79,6 +79,19 @@ class SynthesisLayer(torch.nn.Module):
                                       resample_filter=self.resample_filter, flip_weight=(self.up == 1),
                                       act=self.activation, gain=self.act_gain * gain, clamp=act_clamp)
 
+    def forward_nhwc(self, act, w, noise_mode="random", gain=1):
+        """Resident-activation (bf16 NHWC) variant of forward(); inference only."""
+        styles = self.affine(w)
+        noise = None
+        if self.use_noise and noise_mode == "random":
+            noise = torch.randn([act.shape[0], 1, self.resolution, self.resolution], device=act.device) * self.noise_strength
+        if self.use_noise and noise_mode == "const":
+            noise = self.noise_const * self.noise_strength
+        act_clamp = self.conv_clamp * gain if self.conv_clamp is not None else None
+        return _modconv.layer_nhwc(act, self.weight, styles, noise=noise, bias=self.bias, up=self.up,
+                                   resample_filter=self.resample_filter, act_name=self.activation,
+                                   gain=self.act_gain * gain, clamp=act_clamp)
+
 
 class ToRGBLayer(torch.nn.Module):
     def __init__(self, in_channels, out_channels, w_dim, kernel_size=1, conv_clamp=None, channels_last=False):
@@ -93,6 +106,12 @@ class ToRGBLayer(torch.nn.Module):
         styles = self.affine(w) * self.weight_gain
         return _modconv.modconv_layer(x, self.weight, styles, bias=self.bias, demodulate=False, act="linear",
                                       clamp=self.conv_clamp)
+
+    def forward_nhwc(self, act, w):
+        """bf16 NHWC activation -> fp32 NCHW RGB: per-sample 1x1 weights, no pass over the activation besides the GEMM."""
+        styles = self.affine(w) * self.weight_gain
+        return _modconv.layer_nhwc(act, self.weight, styles, bias=self.bias, demodulate=False, act_name="linear",
+                                   clamp=self.conv_clamp, per_sample=True, out_nchw_f32=True)
 
 
 class Conv2dLayer(torch.nn.Module):
@@ -147,6 +166,22 @@ class SynthesisBlock(torch.nn.Module):
         if in_channels != 0 and architecture == "resnet":
             self.skip = Conv2dLayer(in_channels, out_channels, kernel_size=1, bias=False, up=2, resample_filter=resample_filter)
 
+    def forward_nhwc(self, act, img, ws, noise_mode="random"):
+        """Resident-activation block ('skip' / 'orig' architectures): act stays bf16 NHWC, img fp32 NCHW."""
+        w_iter = iter(ws.unbind(dim=1))
+        if self.in_channels == 0:
+            act = self.const.to(torch.bfloat16).permute(1, 2, 0).unsqueeze(0).repeat([ws.shape[0], 1, 1, 1]).contiguous()
+            act = self.conv1.forward_nhwc(act, next(w_iter), noise_mode=noise_mode)
+        else:
+            act = self.conv0.forward_nhwc(act, next(w_iter), noise_mode=noise_mode)
+            act = self.conv1.forward_nhwc(act, next(w_iter), noise_mode=noise_mode)
+        if img is not None:
+            img = _upfirdn2d.upsample2d(img, self.resample_filter)
+        if self.is_last or self.architecture == "skip":
+            y = self.torgb.forward_nhwc(act, next(w_iter))
+            img = img.add_(y) if img is not None else y
+        return act, img
+
     def forward(self, x, img, ws, force_fp32=False, fused_modconv=None, **layer_kwargs):
         assert tuple(ws.shape[1:]) == (self.num_conv + self.num_torgb, self.w_dim)
         w_iter = iter(ws.unbind(dim=1))
@@ -200,8 +235,13 @@ class SynthesisNetwork(torch.nn.Module):
             block_ws.append(ws.narrow(1, w_idx, block.num_conv + block.num_torgb))
             w_idx += block.num_conv
         x = img = None
+        fast = (not torch.is_grad_enabled()) and ws.is_cuda and set(block_kwargs) <= {"noise_mode"} \
+            and all(getattr(self, f"b{res}").architecture in ("skip", "orig") for res in self.block_resolutions)
         for res, cur_ws in zip(self.block_resolutions, block_ws):
-            x, img = getattr(self, f"b{res}")(x, img, cur_ws, **block_kwargs)
+            if fast:  # inference: activations stay resident as bf16 NHWC, no per-layer layout / modulation passes
+                x, img = getattr(self, f"b{res}").forward_nhwc(x, img, cur_ws, **block_kwargs)
+            else:
+                x, img = getattr(self, f"b{res}")(x, img, cur_ws, **block_kwargs)
         return img
 
 
