@@ -277,8 +277,13 @@ class Synthesis:
         self.S = self._build(device, V.networks)
         g = torch.Generator(device=device).manual_seed(seed)
         self.ws = torch.randn(self.n, self.S.num_ws, 512, device=device, generator=g)
+        self.graphed = None
+        if os.environ.get("VCN_BENCH_GRAPH", "1") == "1":
+            self.graphed = V.networks.GraphedSynthesis(self.S, self.n, noise_mode="const")
 
     def step(self):
+        if self.graphed is not None:
+            return self.graphed(self.ws)
         with torch.no_grad():
             return self.S(self.ws, noise_mode="const")
 
@@ -290,7 +295,8 @@ class Synthesis:
 
     def e2e_step(self, device):
         with torch.no_grad():
-            img = self.S(self.hws.to(device, non_blocking=True), noise_mode="const")
+            ws = self.hws.to(device, non_blocking=True)
+            img = self.graphed(ws) if self.graphed is not None else self.S(ws, noise_mode="const")
             self.himg.copy_(img, non_blocking=True)
 
     def roofline(self, device, peaks, iters=20):

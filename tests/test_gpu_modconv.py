@@ -66,6 +66,7 @@ CASES = [
     (2, 256, 128, 32, 3, 2, True, "rand", "lrelu"),
     (2, 128, 3, 16, 1, 1, False, None, "linear"),
     (2, 64, 64, 8, 3, 1, True, None, "sigmoid"),      # not fusable: second kernel
+    (1, 192, 160, 8, 3, 1, True, "rand", "lrelu"),    # few M tiles: several narrow out-channel tiles per pixel tile
 ]
 
 

@@ -108,3 +108,20 @@ def test_full_size_synthesis_runs():
     # the style FCs are library GEMMs whose batch-8 and batch-1 algorithms differ in the last fp32 bit; the bf16 rounding
     # of x*s turns some of those into 2^-9 operand differences, hence the operand-rounding tolerance, not 1e-5
     assert _rel(img[5:6], one) <= 1e-2
+
+
+def test_cuda_graph_replay_equals_eager():
+    """GraphedSynthesis (one captured graph of the whole forward) reproduces the eager inference path bit for bit on
+    new latents, and keeps doing so across replays."""
+    from viscoin_next_b200 import networks as N
+    torch.manual_seed(1)
+    S = N.SynthesisNetwork(w_dim=64, img_resolution=64, img_channels=3, channel_base=2048, channel_max=64).cuda().eval().requires_grad_(False)
+    for name, p in S.named_parameters():
+        if name.endswith("noise_strength"):
+            p.fill_(0.2)
+    gs = N.GraphedSynthesis(S, 4, noise_mode="const")
+    for seed in (3, 4):
+        ws = torch.randn(4, S.num_ws, 64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(seed))
+        with torch.no_grad():
+            eager = S(ws, noise_mode="const")
+        assert torch.equal(gs(ws), eager)

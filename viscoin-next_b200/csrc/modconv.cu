@@ -69,7 +69,7 @@ template <> __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(floa
 // s_scale / s_bias point at the shared-memory copies for channel co0 (scale may be NULL = 1, bias NULL = 0).
 template <typename T, int ACT>
 __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_t (&acc)[32], T* __restrict__ ybase,
-                                               int co0, float noise, const float* __restrict__ s_scale,
+                                               int co0, int co_end, float noise, const float* __restrict__ s_scale,
                                                const float* __restrict__ s_bias, bool has_scale) {
   float v[32];
 #pragma unroll
@@ -83,7 +83,7 @@ __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_
     }
     v[j] = r;
   }
-  if (a.vec_store && co0 + 32 <= a.cout) {
+  if (a.vec_store && co0 + 32 <= co_end) {
     constexpr int V = 16 / sizeof(T);
 #pragma unroll
     for (int j = 0; j < 32; j += V) {
@@ -96,17 +96,18 @@ __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_
     const int64_t cs = a.ys[1];
 #pragma unroll
     for (int j = 0; j < 32; ++j)
-      if (co0 + j < a.cout) ybase[(int64_t)(co0 + j) * cs] = cvt_out<T>(v[j]);
+      if (co0 + j < co_end) ybase[(int64_t)(co0 + j) * cs] = cvt_out<T>(v[j]);
   }
 }
 
 template <typename T>
 __device__ __forceinline__ void epilogue_dispatch(const IgemmArgs& a, const uint32_t (&acc)[32], T* ybase, int co0,
-                                                  float noise, const float* s_scale, const float* s_bias, bool has_scale) {
-  if (a.act == 0) epilogue_store<T, -1>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
-  else if (a.act == VCN_ACT_LRELU) epilogue_store<T, VCN_ACT_LRELU>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
-  else if (a.act == VCN_ACT_LINEAR) epilogue_store<T, VCN_ACT_LINEAR>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
-  else epilogue_store<T, 0>(a, acc, ybase, co0, noise, s_scale, s_bias, has_scale);
+                                                  int co_end, float noise, const float* s_scale, const float* s_bias,
+                                                  bool has_scale) {
+  if (a.act == 0) epilogue_store<T, -1>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
+  else if (a.act == VCN_ACT_LRELU) epilogue_store<T, VCN_ACT_LRELU>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
+  else if (a.act == VCN_ACT_LINEAR) epilogue_store<T, VCN_ACT_LINEAR>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
+  else epilogue_store<T, 0>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
 }
 
 struct TileCoord {
@@ -252,6 +253,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (ok && a.noise) noise = a.noise[(int64_t)n * a.noise_stride_n + (int64_t)oy * a.out_w + ox];
       const int64_t yoff = ok ? (int64_t)n * a.ys[0] + (int64_t)oy * a.ys[2] + (int64_t)ox * a.ys[3] : 0;
       const float* gscale = (a.scale && !stage_scale && ok) ? a.scale + (int64_t)n * a.cout : nullptr;
+      const int co_end = min(a.cout, tc.co0 + a.n_tile);  // channels past the tile belong to another CTA
       named_bar_sync(1, kEpilogueWarps * 32);
       mbar_wait(tmem_full_bar + as, aph);
       tcgen05_fence_after();
@@ -279,9 +281,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             has_scale = true;
           }
           const float* bip = sp + a.n_tile + c;
-          if (a.y_dtype == VCN_F32) epilogue_dispatch<float>(a, acc, static_cast<float*>(a.y) + yoff, tc.co0 + c, noise, scp, bip, has_scale);
-          else if (a.y_dtype == VCN_BF16) epilogue_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + yoff, tc.co0 + c, noise, scp, bip, has_scale);
-          else epilogue_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, tc.co0 + c, noise, scp, bip, has_scale);
+          if (a.y_dtype == VCN_F32) epilogue_dispatch<float>(a, acc, static_cast<float*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale);
+          else if (a.y_dtype == VCN_BF16) epilogue_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale);
+          else epilogue_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale);
         }
       }
       // hand the accumulator stage back to the MMA warp
@@ -390,6 +392,11 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   // two accumulator stages of n_tile fp32 columns each must fit the 512 TMEM columns
   a.n_tile = (d->cout + 15) / 16 * 16;
   if (a.n_tile > 256) a.n_tile = 256;
+  // few M tiles (tiny resolutions): narrower out-channel tiles spread the weight stream over more SMs - one CTA
+  // ingests only ~75 GB/s through TMA, so a 4.7 MB weight tensor on 2 CTAs is latency/bandwidth bound
+  while (a.n_tile > 32 && a.n_tile % 32 == 0 &&
+         (int64_t)a.tiles_m * a.num_phases * ((d->cout + a.n_tile - 1) / a.n_tile) < sm_count() / 2)
+    a.n_tile /= 2;
   const int tiles_co = (d->cout + a.n_tile - 1) / a.n_tile;
   const int64_t total = (int64_t)a.tiles_m * a.num_phases * tiles_co;
   VCN_REQUIRE(total <= 0x7fffffffLL, "conv_igemm: too many tiles");

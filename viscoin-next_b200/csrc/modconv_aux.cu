@@ -49,25 +49,48 @@ __global__ void __launch_bounds__(256) modulate_pack_kernel(const T* __restrict_
   }
 }
 
-// channels-fastest input (xs_c == 1): plain vectorisable elementwise pass, 2 channels per thread
+// channels-fastest input (xs_c == 1): elementwise pass, 8 channels (16 bytes of bf16 output) per thread
 template <typename T>
 __global__ void __launch_bounds__(256) modulate_pack_cl_kernel(const T* __restrict__ x, int64_t xs_n, int64_t xs_h,
                                                                int64_t xs_w, const float* __restrict__ styles,
                                                                __nv_bfloat16* __restrict__ xhat, int n_img, int cin,
-                                                               int cin_pad, int h, int w) {
-  const int64_t pairs = (int64_t)cin_pad / 2;
-  const int64_t total = (int64_t)n_img * h * w * pairs;
+                                                               int cin_pad, int h, int w, int vec_in) {
+  const int groups = cin_pad / 8;
+  const int64_t total = (int64_t)n_img * h * w * groups;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % pairs) * 2;
-    int64_t r = i / pairs;
+    const int c = (int)(i % groups) * 8;
+    int64_t r = i / groups;
     const int px = (int)(r % w); r /= w;
     const int py = (int)(r % h);
     const int n = (int)(r / h);
     const T* src = x + n * xs_n + py * xs_h + px * xs_w + c;
-    float v0 = 0.f, v1 = 0.f;
-    if (c < cin) v0 = to_acc<T>(src[0]) * (styles ? styles[(int64_t)n * cin + c] : 1.f);
-    if (c + 1 < cin) v1 = to_acc<T>(src[1]) * (styles ? styles[(int64_t)n * cin + c + 1] : 1.f);
-    *reinterpret_cast<__nv_bfloat162*>(xhat + (((int64_t)n * h + py) * w + px) * cin_pad + c) = __floats2bfloat162_rn(v0, v1);
+    float v[8];
+    if (vec_in && c + 8 <= cin) {
+      if constexpr (sizeof(T) == 2) {
+        const Vec16<T> in = *reinterpret_cast<const Vec16<T>*>(src);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = to_acc<T>(in.v[k]);
+      } else {
+#pragma unroll
+        for (int h4 = 0; h4 < 2; ++h4) {
+          const Vec16<T> in = *reinterpret_cast<const Vec16<T>*>(src + h4 * 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) v[h4 * 4 + k] = to_acc<T>(in.v[k]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = (c + k < cin) ? to_acc<T>(src[k]) : 0.f;
+    }
+    if (styles) {
+      const float* sp = styles + (int64_t)n * cin + c;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] *= (c + k < cin) ? sp[k] : 0.f;
+    }
+    Vec16<__nv_bfloat16> o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o.v[k] = __float2bfloat16_rn(v[k]);
+    *reinterpret_cast<Vec16<__nv_bfloat16>*>(xhat + (((int64_t)n * h + py) * w + px) * cin_pad + c) = o;
   }
 }
 
@@ -284,12 +307,14 @@ int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* 
                  int w, cudaStream_t st) {
   const T* px = static_cast<const T*>(x);
   __nv_bfloat16* po = static_cast<__nv_bfloat16*>(xhat);
-  if (xs[1] == 1 && cin > 1 && cin % 2 == 0) {
-    const int64_t total = (int64_t)n * h * w * (cin_pad / 2);
+  if (xs[1] == 1 && cin > 1) {
+    const int64_t total = (int64_t)n * h * w * (cin_pad / 8);
     int64_t grid = (total + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
     if (grid > cap) grid = cap;
-    modulate_pack_cl_kernel<T><<<(unsigned)grid, 256, 0, st>>>(px, xs[0], xs[2], xs[3], styles, po, n, cin, cin_pad, h, w);
+    const int64_t vq = 16 / (int64_t)sizeof(T);
+    const int vec_in = aligned16(x) && xs[0] % vq == 0 && xs[2] % vq == 0 && xs[3] % vq == 0;
+    modulate_pack_cl_kernel<T><<<(unsigned)grid, 256, 0, st>>>(px, xs[0], xs[2], xs[3], styles, po, n, cin, cin_pad, h, w, vec_in);
     VCN_LAUNCH_CHECK("modulate_pack_cl_kernel");
     return VCN_OK;
   }

@@ -344,3 +344,29 @@ class GeneratorAdapted(torch.nn.Module):
 
     def gen_from_w(self, w, **synthesis_kwargs):
         return self.synthesis(w, **synthesis_kwargs)
+
+
+class GraphedSynthesis:
+    """CUDA-graph replay of ``SynthesisNetwork.forward`` for a fixed batch size (inference): the ~175 launches of a
+    256x256 forward are captured once - the tensor maps are kernel parameters, so the graph holds them - and replayed
+    with one host call.  ``noise_mode='random'`` draws fresh noise on every replay (torch registers the generator
+    state with the graph)."""
+
+    def __init__(self, synthesis, batch, noise_mode="const"):
+        p = next(synthesis.parameters())
+        self.synthesis, self.noise_mode = synthesis, noise_mode
+        self.ws = torch.zeros([batch, synthesis.num_ws, synthesis.w_dim], device=p.device)
+        side = torch.cuda.Stream(device=p.device)
+        side.wait_stream(torch.cuda.current_stream(p.device))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(2):  # packs the frozen weights, binds contexts, fills the allocator
+                synthesis(self.ws, noise_mode=noise_mode)
+        torch.cuda.current_stream(p.device).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.img = synthesis(self.ws, noise_mode=noise_mode)
+
+    def __call__(self, ws):
+        self.ws.copy_(ws, non_blocking=True)
+        self.graph.replay()
+        return self.img
