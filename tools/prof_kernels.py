@@ -1,0 +1,81 @@
+"""Profiling driver: the dominant kernels at their BASELINE shapes, a few launches each (for `ncu --set full -k regex:...`).
+
+    python tools/prof_kernels.py [conv] [tconv] [fir] [fircl] [bias]
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+import viscoin_next_b200 as V  # noqa: E402
+from viscoin_next_b200 import _lib  # noqa: E402
+
+M = V.modconv
+what = set(sys.argv[1:]) or {"conv", "tconv", "fir", "fircl", "bias"}
+iters = 3
+dev = "cuda"
+f4 = V.upfirdn2d.setup_filter([1, 3, 3, 1], device=dev)
+
+
+def timed(name, fn, work, unit):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    print("%-46s %.4f ms  %.1f %s" % (name, ms, work / ms / 1e9 * (1e3 if unit == "GB/s" else 1), unit), flush=True)
+
+
+if "conv" in what:
+    for n, cin, cout, r in [(8, 128, 128, 256), (8, 256, 256, 128), (8, 512, 512, 64)]:
+        x = torch.randn(n, cin, r, r, device=dev)
+        w = torch.randn(cout, cin, 3, 3, device=dev)
+        xh = M.modulate_pack(x, None)
+        wt, _ = M.pack_weights(w)
+        for dt, cl in [(torch.float32, False), (torch.bfloat16, True)]:
+            y = M.conv_igemm(xh, wt, _lib.CONV_FPROP, cout, 3, 3, out_dtype=dt, channels_last=cl)
+            timed("conv FPROP %d->%d @%d %s" % (cin, cout, r, "bf16 NHWC" if cl else "f32 NCHW"),
+                  lambda: M.conv_igemm(xh, wt, _lib.CONV_FPROP, cout, 3, 3, out=y), 2.0 * n * cout * cin * 9 * r * r, "TFLOP/s")
+        del x, w, xh, wt, y
+
+if "tconv" in what:
+    for n, cin, cout, r in [(8, 256, 128, 128), (8, 512, 256, 64)]:
+        x = torch.randn(n, cin, r, r, device=dev)
+        w = torch.randn(cout, cin, 3, 3, device=dev)
+        xh = M.modulate_pack(x, None)
+        wt, _ = M.pack_weights(w)
+        for dt, cl in [(torch.float32, False), (torch.bfloat16, True)]:
+            y = M.conv_igemm(xh, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=dt, channels_last=cl)
+            timed("conv TCONV2 %d->%d @%d %s" % (cin, cout, r, "bf16 NHWC" if cl else "f32 NCHW"),
+                  lambda: M.conv_igemm(xh, wt, _lib.CONV_TCONV2, cout, 3, 3, out=y), 2.0 * n * cout * cin * 9 * r * r, "TFLOP/s")
+        del x, w, xh, wt, y
+
+if "fir" in what:
+    for n, c, r in [(8, 128, 257), (8, 256, 129), (8, 512, 65)]:
+        x = torch.randn(n, c, r, r, device=dev)
+        y = V.upfirdn2d.upfirdn2d(x, f4, padding=[1, 1, 1, 1], gain=4)
+        timed("upfirdn2d A f32 NCHW [%d,%d,%d,%d]" % (n, c, r, r),
+              lambda: V.upfirdn2d.upfirdn2d(x, f4, padding=[1, 1, 1, 1], gain=4), (x.numel() + y.numel()) * 4, "GB/s")
+        del x, y
+    x = torch.randn(8, 128, 256, 256, device=dev)
+    y = V.upfirdn2d.upfirdn2d(x, f4, padding=[2, 2, 2, 2], gain=4, flip_filter=True)
+    timed("upfirdn2d A' f32 NCHW [8,128,256,256]", lambda: V.upfirdn2d.upfirdn2d(x, f4, padding=[2, 2, 2, 2], gain=4, flip_filter=True),
+          (x.numel() + y.numel()) * 4, "GB/s")
+    del x, y
+
+if "fircl" in what:
+    for n, c, r in [(8, 128, 257), (8, 256, 129), (8, 512, 65)]:
+        x = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+        y = V.upfirdn2d.upfirdn2d(x, f4, padding=[1, 1, 1, 1], gain=4)
+        timed("upfirdn2d A bf16 NHWC [%d,%d,%d,%d]" % (n, c, r, r),
+              lambda: V.upfirdn2d.upfirdn2d(x, f4, padding=[1, 1, 1, 1], gain=4), (x.numel() + y.numel()) * 2, "GB/s")
+        del x, y
+
+if "bias" in what:
+    x = torch.randn(8, 128, 256, 256, device=dev)
+    b = torch.randn(128, device=dev)
+    timed("bias_act lrelu fwd f32 [8,128,256,256]", lambda: V.bias_act.bias_act(x, b, act="lrelu"), 2 * x.numel() * 4, "GB/s")

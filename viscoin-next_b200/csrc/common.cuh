@@ -96,6 +96,14 @@ template <typename T> __device__ __forceinline__ void st_stream(T* p, const Vec1
                : "memory");
 }
 
+// 4-byte asynchronous global->shared copy (LDGSTS); !valid = write zeros without touching global memory.
+__device__ __forceinline__ void cp_async4_zfill(uint32_t dst_smem, const void* src, bool valid) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst_smem), "l"(src), "r"(valid ? 4 : 0) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

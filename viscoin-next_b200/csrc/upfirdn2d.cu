@@ -165,11 +165,24 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
       const bool row_ok = gy >= 0 && gy < a.in_h && pl < planes;
       const T* src = px + ((int64_t)pl * a.in_h + gy) * a.in_w;
       T* dst = tile + (size_t)rr * g.iwp;
-      for (int cc = lane; cc < g.iwp; cc += 32) {
-        const int gx = ix0 + cc;
-        dst[cc] = (row_ok && gx >= 0 && gx < a.in_w) ? src[gx] : from_acc<T>(S(0));
+      if constexpr (sizeof(T) == 4) {
+        // odd row pitch (the 2H+1 transposed-conv intermediate): rows are only 4-byte aligned, so neither TMA nor
+        // 16-byte loads apply.  4-byte cp.async (LDGSTS) with zero fill: the whole halo tile is in flight at once,
+        // no registers staged, a warp covers 128 contiguous bytes per instruction.
+        const uint32_t d0 = smem_u32(dst);
+        for (int cc = lane; cc < g.iwp; cc += 32) {
+          const int gx = ix0 + cc;
+          const bool ok = row_ok && gx >= 0 && gx < a.in_w;
+          cp_async4_zfill(d0 + (uint32_t)cc * 4u, ok ? src + gx : px, ok);
+        }
+      } else {
+        for (int cc = lane; cc < g.iwp; cc += 32) {
+          const int gx = ix0 + cc;
+          dst[cc] = (row_ok && gx >= 0 && gx < a.in_w) ? src[gx] : from_acc<T>(S(0));
+        }
       }
     }
+    if constexpr (sizeof(T) == 4) cp_async_wait_all();
   }
   __syncthreads();
   if (g.use_tma) mbar_wait(bar, 0);

@@ -1,0 +1,104 @@
+"""dp - data-parallel gradient exchange for the VisCoIN train step: one process per GPU, one bucketed
+all-reduce (mean) per step over NCCL, launched from autograd hooks so that it overlaps the rest of backward.
+
+The reference trains on a single device (viscoin/training/viscoin.py:84-223 has no collective at all); the only
+distributed code in the reference tree is StyleGAN2-ADA's per-parameter ``all_reduce`` after backward
+(stylegan2_ada/training/training_loop.py:300-307, not overlapped).  Here:
+
+  * the gradients of all trainable parameters live in a few flat fp32 buffers ("buckets", filled in reverse
+    registration order = roughly the order backward produces them); ``p.grad`` is a view into its bucket, so autograd
+    accumulates straight into the communication buffer and no gather / scatter copies exist;
+  * a post-accumulate hook counts the parameters of a bucket that are ready; the last one launches
+    ``all_reduce(bucket, async_op=True)`` (NCCL runs it on its own stream, concurrently with the remaining backward
+    kernels); ``finish()`` waits for the handles before the optimizer reads the gradients.
+
+Works with any torch.distributed backend (tests use gloo with world_size 2 on CPU).
+"""
+
+import torch
+import torch.distributed as dist
+
+
+class GradBuckets:
+    def __init__(self, params, bucket_bytes=64 << 20, group=None):
+        self.params = [p for p in params if p.requires_grad]
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.buckets = []      # flat fp32 tensors
+        self.members = []      # list of lists of params
+        self._pending = []     # per bucket: params still to arrive in this backward
+        self._handles = []
+        self._bucket_of = {}
+        cur, cur_bytes = [], 0
+        for p in reversed(self.params):
+            assert p.dtype == torch.float32, "trainable parameters are fp32 master weights"
+            nbytes = p.numel() * 4
+            if cur and cur_bytes + nbytes > bucket_bytes:
+                self._seal(cur)
+                cur, cur_bytes = [], 0
+            cur.append(p)
+            cur_bytes += nbytes
+        if cur:
+            self._seal(cur)
+        for p in self.params:
+            p.register_post_accumulate_grad_hook(self._on_grad)
+        self.reset()
+
+    def _seal(self, plist):
+        dev = plist[0].device
+        total = sum((p.numel() + 63) // 64 * 64 for p in plist)  # 256-byte aligned slices
+        flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        off = 0
+        for p in plist:
+            p.grad = flat[off:off + p.numel()].view_as(p)
+            self._bucket_of[p] = len(self.buckets)
+            off += (p.numel() + 63) // 64 * 64
+        self.buckets.append(flat)
+        self.members.append(list(plist))
+
+    def reset(self):
+        """Zero the gradients (replaces optimizer.zero_grad(): the views must stay attached to the buckets)."""
+        for flat in self.buckets:
+            flat.zero_()
+        self._pending = [len(m) for m in self.members]
+        self._handles = []
+
+    def _on_grad(self, p):
+        b = self._bucket_of[p]
+        self._pending[b] -= 1
+        if self._pending[b] == 0 and self.world > 1:
+            self._launch(b)
+
+    def _launch(self, b):
+        flat = self.buckets[b]
+        backend = dist.get_backend(self.group)
+        if backend == "nccl":
+            self._handles.append((dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True), None))
+        else:
+            self._handles.append((dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True), flat))
+
+    def finish(self):
+        """Wait for the exchange of this step; parameters whose gradient never arrived (unused in this step) are
+        exchanged now so that every rank issues the same collectives."""
+        if self.world > 1:
+            for b, left in enumerate(self._pending):
+                if left > 0:
+                    self._launch(b)
+                    self._pending[b] = 0
+            for h, flat in self._handles:
+                h.wait()
+                if flat is not None:
+                    flat.div_(self.world)
+        self._handles = []
+
+    def numel(self):
+        return sum(p.numel() for p in self.params)
+
+
+def broadcast_parameters(modules, src=0, group=None):
+    """Identical initial replicas: rank `src`'s parameters and buffers to every rank."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    for m in modules:
+        for t in list(m.parameters()) + list(m.buffers()):
+            dist.broadcast(t.data, src=src, group=group)

@@ -235,7 +235,9 @@ class SynthesisNetwork(torch.nn.Module):
             block_ws.append(ws.narrow(1, w_idx, block.num_conv + block.num_torgb))
             w_idx += block.num_conv
         x = img = None
-        fast = (not torch.is_grad_enabled()) and ws.is_cuda and set(block_kwargs) <= {"noise_mode"} \
+        # nothing to differentiate (no_grad, or frozen weights and a constant ws): resident bf16-NHWC inference pipeline
+        no_grad = (not torch.is_grad_enabled()) or not (ws.requires_grad or any(p.requires_grad for p in self.parameters()))
+        fast = no_grad and ws.is_cuda and set(block_kwargs) <= {"noise_mode"} \
             and all(getattr(self, f"b{res}").architecture in ("skip", "orig") for res in self.block_resolutions)
         for res, cur_ws in zip(self.block_resolutions, block_ws):
             if fast:  # inference: activations stay resident as bf16 NHWC, no per-layer layout / modulation passes

@@ -1,0 +1,108 @@
+"""viscoin_models - the networks around the synthesis path in one VisCoIN training iteration, with the reference's
+parameter names (their ``state_dict``s load unchanged).  These are NOT hot-path kernels: plain PyTorch modules over
+library convolutions (cuDNN) - the hot path they feed is ``networks.GeneratorAdapted`` / ``networks.Generator``.
+
+  Classifier        viscoin/models/classifiers.py:13-92   (HF ``ResNetModel(ResNetConfig())`` = ResNet-50 + Linear)
+  ConceptExtractor  viscoin/models/concept_extractors.py:20-141   (Psi)
+  Explainer         viscoin/models/explainers.py:13-56            (Theta)
+  LPIPS             third-party ``lpips`` v0.1.4 (flake.nix:33-42), net='vgg', version 0.1: restated from the published
+                    algorithm on torchvision's VGG-16 feature stack (the package is not installable offline; random-init)
+"""
+
+import torch
+from torch import nn
+
+
+class Classifier(nn.Module):
+    def __init__(self, output_classes=200):
+        super().__init__()
+        from transformers import ResNetConfig, ResNetModel  # third-party arithmetic, same as the reference
+        self.resnet = ResNetModel(ResNetConfig())
+        self.last_size = self.resnet.config.hidden_sizes[-1]
+        self.linear = nn.Linear(self.last_size, output_classes)
+        nn.init.kaiming_normal_(self.linear.weight)
+
+    def forward(self, x):
+        results = self.resnet(x, output_hidden_states=True)
+        output_state = results["pooler_output"].view(-1, self.last_size)
+        return self.linear(output_state), results["hidden_states"]
+
+
+class ConceptExtractor(nn.Module):
+    def __init__(self, n_concepts=256, latent_channels=512, input_channels1=512, input_channels2=1024, input_channels3=2048):
+        super().__init__()
+        self.latent_channels, self.n_concepts = latent_channels, n_concepts
+        self.conv1 = nn.Conv2d(input_channels1, latent_channels, kernel_size=5, padding=2, stride=4)
+        self.conv2 = nn.Conv2d(input_channels2, latent_channels, kernel_size=3, padding=1, stride=2)
+        self.conv3 = nn.Conv2d(input_channels3, latent_channels, kernel_size=3, padding=1, stride=1)
+        self.conv4 = nn.Conv2d(3 * latent_channels, 3 * latent_channels, kernel_size=3, padding=1, stride=1)
+        self.pool = nn.AdaptiveAvgPool2d(3)
+        self.conv5 = nn.Conv2d(3 * latent_channels, n_concepts, kernel_size=1, padding=0, stride=1)
+        self.linear1 = nn.Linear(latent_channels * 3 * 9, 9 * n_concepts, bias=True)
+        self.linear2 = nn.Linear(9 * n_concepts, 9 * n_concepts, bias=False)
+        self.activ = nn.ReLU()
+
+    def forward(self, latent_layers):
+        assert len(latent_layers) == 3, "Input should be a tuple of 3 tensors"
+        x1 = self.activ(self.conv1(latent_layers[0]))
+        x2 = self.activ(self.conv2(latent_layers[1]))
+        x3 = self.activ(self.conv3(latent_layers[2]))
+        x = self.activ(self.conv4(torch.cat((x1, x2, x3), 1)))
+        x1 = self.pool(self.activ(self.conv5(x)))
+        x2 = self.pool(x).reshape(-1, self.latent_channels * 3 * 9)
+        x2 = self.activ(self.linear1(x2))
+        x2 = self.activ(self.linear2(x2))
+        return x1, x2
+
+
+class Explainer(nn.Module):
+    def __init__(self, n_concepts=256, n_classes=200):
+        super().__init__()
+        self.dropout = nn.Dropout(0.01)
+        self.pool = nn.AdaptiveMaxPool2d(1)
+        self.linear = nn.Linear(n_concepts, n_classes, bias=True)
+
+    def forward(self, x):
+        return self.linear(self.pool(self.dropout(x)).flatten(start_dim=1))
+
+
+_VGG_SLICES = [(0, 4), (4, 9), (9, 16), (16, 23), (23, 30)]  # relu1_2, relu2_2, relu3_3, relu4_3, relu5_3
+_VGG_CHANNELS = [64, 128, 256, 512, 512]
+
+
+class LPIPS(nn.Module):
+    """lpips.LPIPS(net='vgg') forward: scale -> 5 VGG-16 feature taps -> unit-normalise over channels -> squared
+    difference -> non-negative 1x1 'lin' weights -> spatial mean -> sum over taps.  Output [N,1,1,1]."""
+
+    def __init__(self):
+        super().__init__()
+        import torchvision
+        feats = torchvision.models.vgg16(weights=None).features
+        self.slices = nn.ModuleList([nn.Sequential(*[feats[i] for i in range(a, b)]) for a, b in _VGG_SLICES])
+        self.lins = nn.ParameterList([nn.Parameter(torch.rand(1, c, 1, 1) / c) for c in _VGG_CHANNELS])
+        self.register_buffer("shift", torch.tensor([-0.030, -0.088, -0.188]).view(1, 3, 1, 1))
+        self.register_buffer("scale", torch.tensor([0.458, 0.448, 0.450]).view(1, 3, 1, 1))
+        self.requires_grad_(False)
+        self.eval()
+
+    def features(self, x):
+        out = []
+        x = (x - self.shift) / self.scale
+        for s in self.slices:
+            x = s(x)
+            out.append(x)
+        return out
+
+    @staticmethod
+    def _unit(f, eps=1e-10):
+        f = f.float()
+        return f / (f.square().sum(dim=1, keepdim=True).sqrt() + eps)
+
+    def forward(self, in0, in1):
+        n = in0.shape[0]
+        f = self.features(torch.cat([in0, in1]))  # one batched pass over both image sets
+        val = 0
+        for k, fk in enumerate(f):
+            d = (self._unit(fk[:n]) - self._unit(fk[n:])).square()
+            val = val + (d * self.lins[k]).sum(dim=1, keepdim=True).mean(dim=[2, 3], keepdim=True)
+        return val

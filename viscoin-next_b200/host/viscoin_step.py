@@ -1,0 +1,188 @@
+"""viscoin_step - one VisCoIN training iteration (the consumer of the synthesis hot path) and its
+data-parallel form.  Follows viscoin/training/viscoin.py:140-223 statement by statement:
+
+    fake  = synthetic_samples(generator_gan, N)                       utils.py:26-39        hot path, forward only
+    classes, hidden = f(cat[real, fake])                              viscoin.py:173
+    phi, phi2 = Psi(hidden[-3:]) ; expl = Theta(phi)                  :174-175
+    acc / concept-regularisation / output-fidelity / orthogonality    :181-190, losses.py:66-96,165-175
+    rebuilt, ws = viscoin_gan(z1=phi, z2=phi2, return_latents=True)   :193-195             hot path, fwd + dx/dstyles bwd
+    rec = L1 + L2 + gamma*CE(f(rebuilt), f(x)) + beta*LPIPS           :196-205, losses.py:125-157
+    gan = mse(ws, fixed_w_avg)                                        :207, losses.py:178-192
+    total.backward() ; Adam(Psi + Theta) ; Adam(viscoin_gan.mapping)  :215-223
+
+The synthesis network is ONE module shared by both generators and frozen (gan.py:142, viscoin.py:116); the classifier
+is frozen and in eval mode (:114-115).  Data parallelism = batch sharding only: every rank runs this step on its own
+8 real + 8 fake images, and the trainable gradients are averaged by ``dp.GradBuckets`` while backward is still running.
+"""
+
+import itertools
+
+import torch
+import torch.nn.functional as F
+
+from . import dp as _dp
+from . import networks as _networks
+from . import viscoin_models as _models
+
+
+# ---- losses (viscoin/training/losses.py) ------------------------------------------------------------------------------
+
+
+def cross_cross_entropy_loss(prediction, target_prediction):
+    """losses.py:25-29."""
+    p = F.softmax(prediction.float(), dim=1)
+    t = F.softmax(target_prediction.float(), dim=1)
+    return (p.log() * -t).sum(dim=1).mean()
+
+
+def concept_regularization_loss(concept_embeddings):
+    """losses.py:66-80: l1(normalised max-pooled concepts) + l1(concepts)."""
+    pooled = F.adaptive_max_pool2d(concept_embeddings, 1).flatten(start_dim=1)
+    normed = F.normalize(pooled, p=2, dim=1)
+    return normed.abs().mean() + concept_embeddings.abs().mean()
+
+
+def concept_orthogonality_loss(model):
+    """losses.py:83-96."""
+    w = model.conv5.weight.view(model.n_concepts, -1)
+    nw = F.normalize(w, dim=1).abs()
+    return ((nw @ nw.T).sum() - model.n_concepts) / (model.n_concepts ** 2)
+
+
+def output_fidelity_loss(original_classes, explainer_classes):
+    """losses.py:165-175."""
+    return cross_cross_entropy_loss(explainer_classes, original_classes.detach())
+
+
+def reconstruction_loss(reconstructed, original, reconstructed_classes, original_classes, lpips_net, lambda_classes=0.1,
+                        lambda_lpips=3.0):
+    """losses.py:125-157.  L1 and L2 share one pass over the difference."""
+    diff = reconstructed.float() - original.float()
+    return (diff.abs().mean() + diff.square().mean()
+            + lambda_classes * cross_cross_entropy_loss(reconstructed_classes, original_classes.detach())
+            + lambda_lpips * lpips_net(reconstructed, original).mean())
+
+
+def gan_regularization_loss(gan_latents, model):
+    """losses.py:178-192."""
+    return (gan_latents - model.mapping.fixed_w_avg.detach()).square().mean()
+
+
+def synthetic_samples(gan, n_samples, device, generator=None):
+    """utils.py:26-39: z ~ N(0,1) on the host, forward through the non-adapted generator."""
+    z = torch.randn(n_samples, gan.z_dim, generator=generator)
+    return gan(z.to(device), None)
+
+
+# ---- the step ---------------------------------------------------------------------------------------------------------
+
+
+class VisCoINParams:
+    """VisCoINTrainingParams, viscoin.py:49-81 (CUB defaults)."""
+    learning_rate = 1e-4
+    cd_fid_iteration = 100
+    batch_size = 8
+    alpha, beta, gamma, delta = 0.5, 3.0, 0.1, 0.2
+
+
+class VisCoINTrainer:
+    """Holds the five networks + LPIPS + the two Adam optimizers and runs ``step(real, labels, i)``.
+
+    amp: None = fp32 library convolutions (TF32 as torch's cuDNN default, like the reference on a GPU);
+         torch.bfloat16 = autocast for the library networks f / Psi / VGG (the synthesis path always runs bf16 tensor-core
+         operands with fp32 accumulation)."""
+
+    def __init__(self, device, n_classes=200, seed=0, amp=torch.bfloat16, channels_last=True, params=None, models=None,
+                 deterministic=False, fused_adam=None):
+        self.device = torch.device(device)
+        self.p = params or VisCoINParams()
+        self.amp = amp if self.device.type == "cuda" else None
+        self.channels_last = channels_last and self.device.type == "cuda"
+        torch.manual_seed(seed)
+        if models is None:
+            classifier = _models.Classifier(n_classes)
+            concept_extractor = _models.ConceptExtractor()
+            explainer = _models.Explainer(n_classes=n_classes)
+            generator_gan = _networks.Generator(z_dim=512, c_dim=0, w_dim=512, img_resolution=256, img_channels=3,
+                                                mapping_kwargs={"num_layers": 2})
+            viscoin_gan = _networks.GeneratorAdapted.from_gan(generator_gan)
+            lpips = _models.LPIPS()
+        else:
+            classifier, concept_extractor, explainer, generator_gan, viscoin_gan, lpips = models
+        # viscoin.py:113-123
+        classifier.eval().requires_grad_(False)
+        viscoin_gan.synthesis.requires_grad_(False)
+        generator_gan.requires_grad_(False)  # a trained G_ema snapshot is stored frozen (SURVEY 3.1 footnote)
+        self.classifier = classifier.to(self.device)
+        self.concept_extractor = concept_extractor.to(self.device)
+        self.explainer = explainer.to(self.device)
+        self.viscoin_gan = viscoin_gan.to(self.device)
+        self.generator_gan = generator_gan.to(self.device)
+        self.lpips = lpips.to(self.device)
+        if self.channels_last:
+            for m in (self.classifier, self.concept_extractor, self.lpips):
+                m.to(memory_format=torch.channels_last)
+        self.deterministic = deterministic
+        _dp.broadcast_parameters([self.classifier, self.concept_extractor, self.explainer, self.viscoin_gan,
+                                  self.generator_gan, self.lpips])
+        # viscoin.py:130-134; gradients live in flat buckets (dp.GradBuckets) whether or not there are peers
+        gan_params = list(self.viscoin_gan.mapping.parameters())
+        main_params = list(itertools.chain(self.concept_extractor.parameters(), self.explainer.parameters()))
+        # backward reaches the mapping network before Psi: register in forward order, buckets fill in reverse
+        self.buckets = _dp.GradBuckets(main_params + gan_params)
+        fused = (self.device.type == "cuda") if fused_adam is None else fused_adam
+        self.gan_optimizer = torch.optim.Adam(gan_params, lr=self.p.learning_rate, fused=fused)
+        self.optimizer = torch.optim.Adam(main_params, lr=self.p.learning_rate, fused=fused)
+
+    def trainable_numel(self):
+        return self.buckets.numel()
+
+    def _autocast(self):
+        return torch.autocast("cuda", dtype=self.amp, enabled=self.amp is not None)
+
+    def _f(self, images):
+        if self.channels_last:
+            images = images.contiguous(memory_format=torch.channels_last)
+        with self._autocast():
+            logits, hidden = self.classifier(images)
+        return logits.float(), hidden
+
+    def forward_losses(self, real_images, labels, i, fake_images=None, z_generator=None):
+        p = self.p
+        self.concept_extractor.train()
+        self.explainer.train(not self.deterministic)
+        self.viscoin_gan.train()
+        if fake_images is None:
+            fake_images = synthetic_samples(self.generator_gan, len(real_images), self.device, z_generator)
+        all_images = torch.cat([real_images, fake_images.to(real_images.dtype)])
+        classes, hidden = self._f(all_images)
+        with self._autocast():
+            encoded_concepts, extra_info = self.concept_extractor(hidden[-3:])
+        encoded_concepts, extra_info = encoded_concepts.float(), extra_info.float()
+        explainer_classes = self.explainer(encoded_concepts)
+        losses = {"acc": F.cross_entropy(classes[: len(labels)], labels)}
+        if i > p.cd_fid_iteration:
+            losses["cr"] = p.delta * concept_regularization_loss(encoded_concepts)
+            losses["of"] = p.alpha * output_fidelity_loss(classes, explainer_classes)
+        losses["ortho"] = concept_orthogonality_loss(self.concept_extractor)
+        rebuilt_images, gan_latents = self.viscoin_gan(z1=encoded_concepts, z2=extra_info, return_latents=True)
+        rebuilt_classes, _ = self._f(rebuilt_images)
+        with self._autocast():
+            lp = lambda a, b: self.lpips(a.contiguous(memory_format=torch.channels_last) if self.channels_last else a,
+                                         b.contiguous(memory_format=torch.channels_last) if self.channels_last else b)
+            losses["rec"] = reconstruction_loss(rebuilt_images, all_images, rebuilt_classes, classes, lp, p.gamma, p.beta)
+        losses["gan"] = gan_regularization_loss(gan_latents, self.viscoin_gan)
+        return losses
+
+    def step(self, real_images, labels, i=1000, fake_images=None, z_generator=None):
+        """One iteration (gradient_accumulation = 1).  Returns the dict of detached loss terms + 'total'."""
+        losses = self.forward_losses(real_images, labels, i, fake_images, z_generator)
+        total = sum(losses.values())
+        total.backward()
+        self.buckets.finish()
+        self.optimizer.step()
+        self.gan_optimizer.step()
+        self.buckets.reset()
+        out = {k: v.detach() for k, v in losses.items()}
+        out["total"] = total.detach()
+        return out
