@@ -283,6 +283,7 @@ class Synthesis:
 
     def step(self):
         if self.graphed is not None:
+            self.graph_launches = getattr(self, "graph_launches", 0) + self.graphed.launches
             return self.graphed(self.ws)
         with torch.no_grad():
             return self.S(self.ws, noise_mode="const")
@@ -342,7 +343,100 @@ class Synthesis:
         return time.perf_counter() - t0
 
 
-WORKLOADS = {"opsweep": OpSweep, "synthesis": Synthesis}
+class TrainStep:
+    """BASELINE.json configs[3]/[4]: the full VisCoIN ensemble train step (ResNet-50 f, Psi, Theta, generator
+    reconstruction and its losses, two Adam updates), batch 8 real + 8 fake images per GPU at 256x256, random-init,
+    synthetic CUB-shaped data.  Under torchrun every rank runs its own shard and the 96 M trainable gradients are
+    all-reduced (mean) over NCCL while backward is still running (viscoin_next_b200.dp.GradBuckets)."""
+
+    metric = "VisCoIN train steps/s @256^2 b8/GPU"
+    unit = "steps/s (x GPUs: one step = 8 real + 8 fake images on each GPU)"
+    dtype = "bf16"
+    l2_note = "activations per step (GBs) far exceed L2; no flush needed"
+
+    def __init__(self, batch):
+        self.n = batch
+        self.name = ("VisCoIN ensemble train step (ResNet-50 f + Psi + Theta + G reconstruction losses + LPIPS-VGG16, Adam), "
+                     "%d real + %d fake images/GPU at 256x256, random-init, i > cd_fid_iteration (all six losses)" % (batch, batch))
+
+    def units_per_step(self):
+        return 1.0
+
+    def setup(self, device, seed):
+        import viscoin_next_b200 as V
+        self.V = V
+        self.tr = V.viscoin_step.VisCoINTrainer(device, seed=0)  # identical replicas (seed 0 + broadcast)
+        g = torch.Generator(device=device).manual_seed(seed)     # rank-distinct data
+        self.real = torch.randn(self.n, 3, 256, 256, device=device, generator=g)
+        self.labels = torch.randint(0, 200, (self.n,), device=device, generator=g)
+        self.zgen = torch.Generator().manual_seed(seed)
+        self.last = None
+
+    def step(self):
+        self.last = self.tr.step(self.real, self.labels, 1000, z_generator=self.zgen)
+        return self.last
+
+    def e2e_setup(self, device):
+        self.hreal = self.real.cpu().pin_memory()
+        self.hlabels = self.labels.cpu().pin_memory()
+        self.h2d = self.hreal.numel() * 4 + self.hlabels.numel() * 8 + self.n * 512 * 4  # images, labels, z of the fake batch
+        self.d2h = 4
+
+    def e2e_step(self, device):
+        out = self.tr.step(self.hreal.to(device, non_blocking=True), self.hlabels.to(device, non_blocking=True), 1000,
+                           z_generator=self.zgen)
+        self.loss_value = float(out["total"])  # device -> host read of the step's result
+
+    def roofline(self, device, peaks, iters=20):
+        r = Synthesis.roofline(self, device, peaks, iters)
+        r["note"] = "dominant hand-written kernel of the step: the tcgen05 implicit GEMM at the heaviest synthesis layer shape"
+        return r
+
+    RES = 256
+
+    def cpu_step(self, n_sample, seed=0):
+        """Oracle port of the same step on the host cores: n_sample real + n_sample fake images, forward + backward."""
+        from oracle import ref_step as RS
+        if not hasattr(self, "_cpu_state"):
+            import viscoin_next_b200 as V
+            VM, N = V.viscoin_models, V.networks
+            torch.manual_seed(0)
+            sd = lambda m: {k: v.detach().clone() for k, v in m.state_dict().items()}
+            gen = N.Generator(z_dim=512, c_dim=0, w_dim=512, img_resolution=256, img_channels=3, mapping_kwargs={"num_layers": 2})
+            lp = VM.LPIPS()
+            st = {"classifier": sd(VM.Classifier(200)), "concept_extractor": sd(VM.ConceptExtractor()),
+                  "explainer": sd(VM.Explainer()), "viscoin_gan": sd(N.GeneratorAdapted.from_gan(gen)),
+                  "generator_gan": sd(gen)}
+            st["lpips_convs"] = [(l.weight.detach(), l.bias.detach()) for s in lp.slices for l in s if isinstance(l, torch.nn.Conv2d)]
+            st["lpips_lins"] = [p.detach() for p in lp.lins]
+            st["_f"] = RS.make_classifier(st["classifier"])
+            for grp in ("concept_extractor", "explainer"):
+                for v in st[grp].values():
+                    if v.is_floating_point():
+                        v.requires_grad_(True)
+            for k, v in st["viscoin_gan"].items():
+                if k.startswith("mapping."):
+                    v.requires_grad_(True)
+            self._cpu_state = st
+        st = self._cpu_state
+        from oracle import ref_net as RN
+        g = torch.Generator().manual_seed(seed)
+        real = torch.randn(n_sample, 3, 256, 256, generator=g)
+        labels = torch.randint(0, 200, (n_sample,), generator=g)
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            fake = RN.generator(torch.randn(n_sample, 512, generator=g), st["generator_gan"], 256, mapping_layers=2, training=True)
+        out = RS.step_losses(st, real, labels, fake, noise_mode="random")
+        out.pop("_rebuilt")
+        sum(out.values()).backward()
+        dt = time.perf_counter() - t0
+        for grp in ("concept_extractor", "explainer", "viscoin_gan"):
+            for v in st[grp].values():
+                v.grad = None
+        return dt
+
+
+WORKLOADS = {"opsweep": OpSweep, "synthesis": Synthesis, "trainstep": TrainStep}
 
 
 def pick_workload(args):
@@ -354,7 +448,7 @@ def pick_workload(args):
     return WORKLOADS[name](args.batch)
 
 
-DEFAULT_WORKLOAD = "synthesis"
+DEFAULT_WORKLOAD = "trainstep"
 
 
 def run_reference(args, world, rank):
@@ -404,7 +498,7 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    launches0 = lib.vcn_launch_count()
+    launches0 = lib.vcn_launch_count() + getattr(wl, "graph_launches", 0)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record()
@@ -413,7 +507,7 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     barrier(world)
-    launches = lib.vcn_launch_count() - launches0
+    launches = lib.vcn_launch_count() + getattr(wl, "graph_launches", 0) - launches0  # eager launches + graph-replayed ones
     clocks = sampler.stop() if rank == 0 else None
     ms = max_over_ranks(e0.elapsed_time(e1), world, device)
     value = wl.units_per_step() * world * args.steps / (ms * 1e-3)

@@ -156,6 +156,11 @@ int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t
                          int n, int c, int c_pad, int h, int w, void* stream);
 int vcn_modconv_bwd_finish(float* dxhat, const int64_t ds[4], const void* x, int x_dtype, const int64_t xs[4],
                            const float* styles, float* dsum, int n, int c, int h, int w, void* stream);
+/* Resident 16-bit channels-last pipeline: dxhat is a dense bf16 [n,h,w,c_pad] buffer (the DGRAD / SCONV2 GEMM output),
+ * x the layer input (bf16, channel stride 1, strides xs); dx = dxhat * styles[n,c] in place, dsum[n,c] += sum_p dxhat*x.
+ * vcn_modconv_bwd_pack takes the same route on its own when dy / y are 16-bit with channel stride 1. */
+int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, const int64_t xs[4], const float* styles,
+                              float* dsum, int n, int c, int c_pad, int h, int w, void* stream);
 int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const float* dcoef, const float* wsq,
                    int n, int cin, int cout, void* stream);
 

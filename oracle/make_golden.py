@@ -262,14 +262,58 @@ def golden_networks(networks):
     _save("networks", **out)
 
 
+def golden_step():
+    """VisCoIN step components: Psi, Theta and the loss terms of viscoin/training/losses.py, from the REAL reference
+    modules (``lpips`` is not installable offline: the module is stubbed and the LPIPS term patched to zero, so the
+    perceptual term stays unpinned - see oracle/ref_step.py)."""
+    import types
+    stub = types.ModuleType("lpips")
+    stub.LPIPS = object
+    sys.modules.setdefault("lpips", stub)
+    from viscoin.models.concept_extractors import ConceptExtractor
+    from viscoin.models.explainers import Explainer
+    from viscoin.training import losses as L
+    L.lpips_loss = lambda a, b: torch.zeros(())
+    g = torch.Generator().manual_seed(4321)
+    torch.manual_seed(4321)
+    psi = ConceptExtractor(n_concepts=8, latent_channels=16, input_channels1=16, input_channels2=32, input_channels3=64)
+    theta = Explainer(n_concepts=8, n_classes=10).eval()
+    h = [torch.randn(2, 16, 28, 28, generator=g).requires_grad_(True), torch.randn(2, 32, 14, 14, generator=g).requires_grad_(True),
+         torch.randn(2, 64, 7, 7, generator=g).requires_grad_(True)]
+    phi, phi2 = psi(tuple(h))
+    expl = theta(phi)
+    dphi, dphi2 = torch.randn(phi.shape, generator=g), torch.randn(phi2.shape, generator=g)
+    dh = torch.autograd.grad([phi, phi2], h, [dphi, dphi2])
+    out = {"psi." + k: _np(v) for k, v in psi.state_dict().items()}
+    out.update({"theta." + k: _np(v) for k, v in theta.state_dict().items()})
+    out.update({"h0": _np(h[0]), "h1": _np(h[1]), "h2": _np(h[2]), "phi": _np(phi), "phi2": _np(phi2), "expl": _np(expl),
+                "dphi": _np(dphi), "dphi2": _np(dphi2), "dh0": _np(dh[0]), "dh1": _np(dh[1]), "dh2": _np(dh[2])})
+    a, b = torch.randn(4, 10, generator=g), torch.randn(4, 10, generator=g)
+    out.update({"cls_a": _np(a), "cls_b": _np(b), "loss.cce": _np(L.cross_cross_entropy_loss(a, b)),
+                "loss.of": _np(L.output_fidelity_loss(a, b)),
+                "loss.cr": _np(L.concept_regularization_loss(phi)), "loss.ortho": _np(L.concept_orthogonality_loss(psi))})
+    x0, x1 = torch.randn(4, 3, 16, 16, generator=g), torch.randn(4, 3, 16, 16, generator=g)
+    out.update({"img_a": _np(x0), "img_b": _np(x1),
+                "loss.rec_nolpips": _np(L.reconstruction_loss(x0, x1, a, b, 0.1, 3.0))})
+    ws = torch.randn(4, 14, 32, generator=g)
+    w_avg = torch.randn(32, generator=g)
+    model = types.SimpleNamespace(mapping=types.SimpleNamespace(fixed_w_avg=w_avg))
+    out.update({"ws": _np(ws), "w_avg": _np(w_avg), "loss.gan": _np(L.gan_regularization_loss(ws, model))})
+    _save("step", **out)
+
+
 def main():
     bias_act, upfirdn2d, conv2d_resample, fma, networks = _import_reference()
     torch.set_num_threads(max(1, len(os.sched_getaffinity(0))))
     print(f"reference at {REF_ROOT}, torch {torch.__version__}")
+    if len(sys.argv) > 1 and sys.argv[1] == "step":
+        golden_step()
+        return
     golden_bias_act(bias_act)
     golden_upfirdn2d(upfirdn2d)
     golden_conv_modconv(upfirdn2d, conv2d_resample, fma, networks)
     golden_networks(networks)
+    golden_step()
 
 
 if __name__ == "__main__":

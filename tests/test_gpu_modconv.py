@@ -180,3 +180,68 @@ def test_errors():
     y = M.modulated_conv2d(x.cuda(), w, torch.ones(1, 8, device="cuda"), padding=1)
     with pytest.raises(_lib.VcnError):
         y.sum().backward()  # weight gradient: not implemented, must fail loudly
+
+
+RESIDENT_CASES = [
+    # n, cin, cout, res, k, up, demod, noise, act        (cin % 8 == 0: the resident pipeline's requirement)
+    (2, 64, 64, 16, 3, 1, True, "rand", "lrelu"),
+    (3, 128, 64, 8, 3, 2, True, "const", "lrelu"),
+    (2, 64, 3, 32, 1, 1, False, None, "linear"),       # ToRGB: leaves the pipeline, fp32 NCHW out
+    (1, 72, 136, 9, 3, 2, True, "rand", "lrelu"),
+    (2, 256, 128, 32, 3, 2, True, "rand", "lrelu"),
+    (4, 512, 512, 4, 3, 1, True, "const", "lrelu"),
+    (2, 96, 40, 12, 3, 1, True, "rand", None),
+]
+TOL_RES_FWD, TOL_RES_GRAD = 1.5e-2, 3e-2  # + one bf16 rounding (2^-9) of the stored output / input gradient
+
+
+@pytest.mark.parametrize("case", RESIDENT_CASES, ids=[str(c) for c in RESIDENT_CASES])
+def test_resident_bf16_channels_last_layer_vs_oracle(case):
+    """Training-mode resident pipeline: bf16 channels_last activations in, bf16 channels_last out (fp32 NCHW for ToRGB),
+    gradients dx (bf16 channels_last), dstyles, dbias - against the fp32 oracle fed the same bf16-rounded input."""
+    M = _M()
+    n, cin, cout, res, k, up, demod, noise_kind, act = case
+    g = torch.Generator().manual_seed(7 + sum(v for v in case[:6]))
+    x = torch.randn(n, cin, res, res, generator=g).bfloat16().float().requires_grad_(True)
+    w = torch.randn(cout, cin, k, k, generator=g)
+    s = (torch.randn(n, cin, generator=g) * 0.5 + 1).requires_grad_(True)
+    b = (torch.randn(cout, generator=g) * 0.3).requires_grad_(True)
+    ro = res * up
+    noise = None
+    if noise_kind == "rand":
+        noise = torch.randn(n, 1, ro, ro, generator=g) * 0.4
+    elif noise_kind == "const":
+        noise = torch.randn(ro, ro, generator=g) * 0.4
+    f4 = R.setup_filter([1, 3, 3, 1])
+    clamp = 2.5 if act == "lrelu" else None
+    sm = s * (1 / math.sqrt(cin)) if not demod else s
+    z_ref = R.modulated_conv2d(x, w, sm, noise=noise, up=up, padding=k // 2, resample_filter=f4, demodulate=demod,
+                               flip_weight=(up == 1), fused_modconv=False)
+    y_ref = R.bias_act(z_ref, b, act=act, clamp=clamp) if act is not None else z_ref
+    dy = torch.randn(y_ref.shape, generator=g).bfloat16().float()
+    want = [x, s] + ([b] if act is not None else [])
+
+    xc = x.detach().cuda().bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    sc = s.detach().cuda().requires_grad_(True)
+    bc = b.detach().cuda().requires_grad_(True)
+    smc = sc * (1 / math.sqrt(cin)) if not demod else sc
+    nc = noise.cuda() if noise is not None else None
+    y = M.modconv_layer(xc, w.cuda(), smc, noise=nc, bias=bc if act is not None else None, up=up, padding=k // 2,
+                        resample_filter=f4.cuda(), demodulate=demod, flip_weight=(up == 1), act=act, clamp=clamp)
+    if cout % 8 == 0:
+        assert y.dtype == torch.bfloat16 and y.is_contiguous(memory_format=torch.channels_last)
+        dyc = dy.cuda().bfloat16().contiguous(memory_format=torch.channels_last)
+    else:
+        assert y.dtype == torch.float32 and y.is_contiguous()
+        dyc = dy.cuda()
+    grads = torch.autograd.grad(y, [xc, sc] + ([bc] if act is not None else []), dyc)
+    assert grads[0].dtype == torch.bfloat16 and grads[0].shape == xc.shape
+    assert _rel(y, y_ref) <= TOL_RES_FWD, _rel(y, y_ref)
+    if act == "lrelu":  # gradients at the activation pattern of the CUDA forward (see test_layer_vs_oracle)
+        yc = y.detach().float().cpu()
+        slope = torch.where(yc > 0, 1.0, 0.2) * math.sqrt(2) * (yc.abs() < clamp)
+        grads_ref = torch.autograd.grad((z_ref + b.reshape(1, -1, 1, 1)) * slope, want, dy)
+    else:
+        grads_ref = torch.autograd.grad(y_ref, want, dy)
+    for gname, a, r in zip(("dx", "ds", "db"), grads, grads_ref):
+        assert _rel(a, r) <= TOL_RES_GRAD, (gname, _rel(a, r))

@@ -89,6 +89,28 @@ def test_generator_adapted_golden(golden):
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in GA.mapping.parameters())
 
 
+def test_generator_adapted_golden_resident_bf16(golden):
+    """Same golden case through the training-mode resident pipeline (bf16 channels_last activations between layers,
+    forward and backward).  Storage rounding (2^-9 per layer) on top of the bf16 operands: image <= 4e-2, dz (L2) <= 1.5e-1."""
+    from viscoin_next_b200 import networks as N
+    g = golden("networks")
+    GA = N.GeneratorAdapted(z_dim=8, w_dim=32, img_resolution=32, synthesis_kwargs=dict(channel_base=512, channel_max=16),
+                            mapping_kwargs=dict(coarse_layer=2, mid_layer=10, num_layers=1))
+    GA.load_state_dict(g.sub("GA.sd."), strict=True)
+    GA = GA.cuda().train()
+    GA.synthesis.requires_grad_(False)
+    GA.synthesis.resident_bf16 = True
+    z1 = g.t("GA.z1", device="cuda").requires_grad_(True)
+    z2 = g.t("GA.z2", device="cuda").requires_grad_(True)
+    img, ws = GA(z1, z2, return_latents=True, noise_mode="const")
+    assert img.dtype == torch.float32
+    e_img = _rel(img, g.t("GA.img"))
+    dz1, dz2 = torch.autograd.grad(img, [z1, z2], g.t("GA.dimg", device="cuda"))
+    e1, e2 = _rel2(dz1, g.t("GA.dz1")), _rel2(dz2, g.t("GA.dz2"))
+    print("resident: img %.3e dz1 %.3e dz2 %.3e" % (e_img, e1, e2))
+    assert e_img <= 4e-2 and e1 <= 1.5e-1 and e2 <= 1.5e-1
+
+
 def test_full_size_synthesis_runs():
     """BASELINE config 1 shape: 256x256, batch 8, default channels; finite output of the right shape, and batch
     independence (sample i of a batch == the same w alone), a size-independent property of the path."""

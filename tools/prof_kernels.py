@@ -11,8 +11,9 @@ import viscoin_next_b200 as V  # noqa: E402
 from viscoin_next_b200 import _lib  # noqa: E402
 
 M = V.modconv
-what = set(sys.argv[1:]) or {"conv", "tconv", "fir", "fircl", "bias"}
-iters = 3
+what = set(a for a in sys.argv[1:] if a != "quick") or {"conv", "tconv", "fir", "fircl", "bias"}
+quick = "quick" in sys.argv[1:]  # first shape of each family, one timed launch (for ncu --set full)
+iters = 1 if quick else 3
 dev = "cuda"
 f4 = V.upfirdn2d.setup_filter([1, 3, 3, 1], device=dev)
 
@@ -31,7 +32,7 @@ def timed(name, fn, work, unit):
 
 
 if "conv" in what:
-    for n, cin, cout, r in [(8, 128, 128, 256), (8, 256, 256, 128), (8, 512, 512, 64)]:
+    for n, cin, cout, r in [(8, 128, 128, 256), (8, 256, 256, 128), (8, 512, 512, 64)][:1 if quick else 3]:
         x = torch.randn(n, cin, r, r, device=dev)
         w = torch.randn(cout, cin, 3, 3, device=dev)
         xh = M.modulate_pack(x, None)
@@ -43,7 +44,7 @@ if "conv" in what:
         del x, w, xh, wt, y
 
 if "tconv" in what:
-    for n, cin, cout, r in [(8, 256, 128, 128), (8, 512, 256, 64)]:
+    for n, cin, cout, r in [(8, 256, 128, 128), (8, 512, 256, 64)][:1 if quick else 2]:
         x = torch.randn(n, cin, r, r, device=dev)
         w = torch.randn(cout, cin, 3, 3, device=dev)
         xh = M.modulate_pack(x, None)
@@ -55,7 +56,7 @@ if "tconv" in what:
         del x, w, xh, wt, y
 
 if "fir" in what:
-    for n, c, r in [(8, 128, 257), (8, 256, 129), (8, 512, 65)]:
+    for n, c, r in [(8, 128, 257), (8, 256, 129), (8, 512, 65)][:1 if quick else 3]:
         x = torch.randn(n, c, r, r, device=dev)
         y = V.upfirdn2d.upfirdn2d(x, f4, padding=[1, 1, 1, 1], gain=4)
         timed("upfirdn2d A f32 NCHW [%d,%d,%d,%d]" % (n, c, r, r),
@@ -68,7 +69,7 @@ if "fir" in what:
     del x, y
 
 if "fircl" in what:
-    for n, c, r in [(8, 128, 257), (8, 256, 129), (8, 512, 65)]:
+    for n, c, r in [(8, 128, 257), (8, 256, 129), (8, 512, 65)][:1 if quick else 3]:
         x = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
         y = V.upfirdn2d.upfirdn2d(x, f4, padding=[1, 1, 1, 1], gain=4)
         timed("upfirdn2d A bf16 NHWC [%d,%d,%d,%d]" % (n, c, r, r),

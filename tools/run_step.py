@@ -1,0 +1,57 @@
+"""Run a few VisCoIN train steps on cuda:0 and print the time per step and a per-phase breakdown (CUDA events).
+
+    python tools/run_step.py [steps] [amp: bf16|fp32]
+"""
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+import viscoin_next_b200 as V  # noqa: E402
+
+steps = int(sys.argv[1]) if len(sys.argv) > 1 else 5
+amp = torch.bfloat16 if (len(sys.argv) < 3 or sys.argv[2] == "bf16") else None
+dev = torch.device("cuda:0")
+t0 = time.time()
+tr = V.viscoin_step.VisCoINTrainer(dev, amp=amp)
+print("built in %.1fs, trainable %.1f M params, %d buckets" % (time.time() - t0, tr.trainable_numel() / 1e6, len(tr.buckets.buckets)), flush=True)
+g = torch.Generator(device=dev).manual_seed(0)
+real = torch.randn(8, 3, 256, 256, device=dev, generator=g)
+labels = torch.randint(0, 200, (8,), device=dev, generator=g)
+
+
+def ev():
+    e = torch.cuda.Event(enable_timing=True)
+    e.record()
+    return e
+
+
+for it in range(steps):
+    torch.cuda.synchronize()
+    w0 = time.perf_counter()
+    e = [ev()]
+    losses = tr.forward_losses(real, labels, 1000)
+    e.append(ev())
+    total = sum(losses.values())
+    total.backward()
+    e.append(ev())
+    tr.buckets.finish()
+    tr.optimizer.step()
+    tr.gan_optimizer.step()
+    tr.buckets.reset()
+    e.append(ev())
+    torch.cuda.synchronize()
+    w1 = time.perf_counter()
+    print("step %d: total loss %.4f | fwd %.2f ms  bwd %.2f ms  opt %.2f ms | gpu %.2f ms  wall %.2f ms" % (
+        it, float(total), e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2]), e[2].elapsed_time(e[3]), e[0].elapsed_time(e[3]),
+        (w1 - w0) * 1e3), flush=True)
+print({k: round(float(v), 5) for k, v in losses.items()})
+print("max mem %.2f GB" % (torch.cuda.max_memory_allocated() / 2 ** 30))
+
+if os.environ.get("VCN_STEP_PROFILE", "0") == "1":
+    from torch.profiler import profile, ProfilerActivity
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        tr.step(real, labels)
+        torch.cuda.synchronize()
+    print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))

@@ -57,6 +57,7 @@ SIGNATURES = {
     "vcn_modconv_bwd_pack": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _c.POINTER(UpfirdnEpilogue),
                                   _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_modconv_bwd_finish": (_i, [_vp, _c.POINTER(_i64 * 4), _vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _vp]),
+    "vcn_modconv_bwd_finish_cl": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_demod_grad": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
 }
 

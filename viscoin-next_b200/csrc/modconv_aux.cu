@@ -348,6 +348,12 @@ int run_pack(const void* w, int cout, int cin, int taps, int transpose_io, void*
 }  // namespace
 }  // namespace vcn
 
+namespace vcn {
+int bwd_pack_cl_try(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
+                    const vcn_upfirdn2d_epilogue* epi, void* dy0, float* gsum, float* db, int n, int c, int c_pad, int h,
+                    int w, int act, float alpha, float gain, float clamp, cudaStream_t st);  // modconv_bwd_cl.cu
+}
+
 extern "C" {
 
 int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat, int n, int cin,
@@ -422,6 +428,11 @@ int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t
   VCN_REQUIRE((a.act == 0 && !gsum) || y, "modconv_bwd_pack: y is required with an activation or when gsum is requested");
   dim3 grid((unsigned)((h * w + 127) / 128), (unsigned)((c_pad + 63) / 64), (unsigned)n);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  {  // 16-bit channels-last operands: streaming kernel of modconv_bwd_cl.cu
+    const int rc = bwd_pack_cl_try(dy, y, dtype, a.dys, a.ys, epi, dy0, gsum, db, n, c, c_pad, h, w, a.act, a.alpha, a.gain,
+                                   a.clamp, st);
+    if (rc >= 0) return rc;
+  }
   switch (dtype) {
     case VCN_F32: modconv_bwd_pack_kernel<float><<<grid, 256, 0, st>>>(a); break;
     case VCN_F16: modconv_bwd_pack_kernel<__half><<<grid, 256, 0, st>>>(a); break;

@@ -1,0 +1,188 @@
+// modconv_bwd_cl.cu - backward helpers of the fused synthesis layer for RESIDENT 16-bit channels-last activations
+// (the training-mode pipeline: activations stay bf16 NHWC between layers, forward and backward).
+//
+//   bwd_pack_cl   : dz = bias_act'(dy; y),  gsum[n,c] += sum_p dz * (y0*d),  db[c] += sum_p dz,  dy0 = dz * d[n,c]
+//                   dy, y : 16-bit, channels fastest (stride 1 on c);  dy0 : bf16 NHWC [n,h,w,c_pad]
+//                   (autograd of networks.py:69-72 fma + :302-304 bias_act, bias_act.py:160-175)
+//   bwd_finish_cl : dx = dxhat * s[n,c] in place (bf16 NHWC), dsum[n,c] += sum_p dxhat * x   (autograd of networks.py:64)
+//
+// Both are one streaming pass: a thread owns 8 consecutive channels (one 16-byte vector) and walks a chunk of pixels;
+// threads of a CTA that share a channel group combine their partial sums through shared memory, one atomicAdd per
+// (CTA, channel).  HBM-bound: 6 bytes per element each (two 16-bit reads + one 16-bit write).
+#include <string.h>
+
+#include "common.cuh"
+
+namespace vcn {
+namespace {
+
+struct BwdClArgs {
+  const void* dy; const void* y;       // pack: incoming gradient / stored output.  finish: dy = dxhat (in/out), y = x
+  int64_t as[4], bs[4];                // element strides (n, c, h, w) of dy and of y; c-stride is 1
+  const float* noise; int64_t noise_stride_n;
+  const float* bias; const float* scale;  // pack: scale = d[n,c].  finish: scale = styles[n,c]
+  __nv_bfloat16* out;                  // pack: dy0 [n,h,w,c_pad]
+  float* sum_nc; float* sum_c;         // pack: gsum, db.  finish: dsum, unused
+  int n, c, c_pad, h, w, chunk;
+  int act; float alpha, gain, clamp;
+};
+
+__device__ __forceinline__ bool aligned16_dev(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <typename T> __device__ __forceinline__ void load8(const T* p, bool vec, int valid, float (&v)[8]) {
+  if (vec) {
+    const Vec16<T> in = *reinterpret_cast<const Vec16<T>*>(p);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = to_acc<T>(in.v[k]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = k < valid ? to_acc<T>(p[k]) : 0.f;
+  }
+}
+
+// Reduce per-thread partials over the threads that share a channel group and add them to dst[c0 + k].
+__device__ __forceinline__ void group_reduce_add(float (*red)[8], const float (&acc)[8], int tid, int groups, int rows,
+                                                 float* dst, int c_valid) {
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < 8; ++k) red[tid][k] = acc[k];
+  __syncthreads();
+  if (tid < groups * 8) {
+    const int g = tid >> 3, k = tid & 7;
+    float t = 0.f;
+    for (int j = 0; j < rows; ++j) t += red[j * groups + g][k];
+    if (g * 8 + k < c_valid) atomicAdd(dst + g * 8 + k, t);
+  }
+}
+
+template <typename T, bool FINISH>
+__global__ void __launch_bounds__(256) modconv_bwd_cl_kernel(const BwdClArgs a) {
+  __shared__ float red[256][8];
+  const int tid = threadIdx.x, n = blockIdx.y;
+  const int groups = a.c_pad >> 3;        // <= 256
+  const int rows = 256 / groups;          // pixels in flight per CTA iteration
+  const int g = tid % groups, row = tid / groups;
+  const bool active = row < rows;
+  const int c = g * 8;
+  const int valid = min(8, a.c - c);      // channels of this group that exist (<= 0: padding group)
+  const int hw = a.h * a.w;
+  const int p_end = min(hw, (int)(blockIdx.x + 1) * a.chunk);
+  float sc[8], bi[8], acc0[8], acc1[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const bool ok = k < valid;
+    sc[k] = (a.scale && ok) ? a.scale[(int64_t)n * a.c + c + k] : (FINISH ? 0.f : 1.f);
+    bi[k] = (!FINISH && a.bias && a.act && ok) ? a.bias[c + k] : 0.f;
+    acc0[k] = acc1[k] = 0.f;
+  }
+  if (FINISH && !a.scale) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sc[k] = 1.f;
+  }
+  const T* pa = static_cast<const T*>(a.dy) + (int64_t)n * a.as[0] + c;
+  const T* pb = a.y ? static_cast<const T*>(a.y) + (int64_t)n * a.bs[0] + c : nullptr;
+  const bool va = valid == 8 && ((a.as[0] | a.as[2] | a.as[3]) & 7) == 0 && aligned16_dev(a.dy);
+  const bool vb = valid == 8 && ((a.bs[0] | a.bs[2] | a.bs[3]) & 7) == 0 && aligned16_dev(a.y);
+  if (active) {
+    for (int p = blockIdx.x * a.chunk + row; p < p_end; p += rows) {
+      const int py = p / a.w, px = p - py * a.w;
+      float u[8], v[8];
+      load8<T>(pa + py * a.as[2] + px * a.as[3], va, valid, u);
+      if (pb) load8<T>(pb + py * a.bs[2] + px * a.bs[3], vb, valid, v);
+      else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = 0.f;
+      }
+      Vec16<__nv_bfloat16> o;
+      if (FINISH) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          acc0[k] = fmaf(u[k], v[k], acc0[k]);
+          o.v[k] = __float2bfloat16_rn(u[k] * sc[k]);
+        }
+        // in place: dxhat is a dense [n,h,w,c_pad] bf16 buffer
+        *reinterpret_cast<Vec16<__nv_bfloat16>*>(const_cast<T*>(pa) + py * a.as[2] + px * a.as[3]) = o;
+      } else {
+        float nz = 0.f;
+        if (a.noise) nz = a.noise[(int64_t)n * a.noise_stride_n + p];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float dz = u[k], r = v[k];
+          if (a.act) {  // first derivative of bias_act keyed on the stored output (bias_act.cu:48,72,141)
+            const float yy = v[k] / a.gain;
+            const bool neg = a.act == VCN_ACT_LRELU && !(yy > 0.f);
+            dz = (neg ? u[k] * a.alpha : u[k]) * a.gain;
+            if (a.clamp >= 0.f && !(v[k] > -a.clamp && v[k] < a.clamp)) dz = 0.f;
+            r = (neg ? yy / a.alpha : yy) - bi[k];
+          }
+          r -= nz;
+          acc0[k] = fmaf(dz, r, acc0[k]);
+          acc1[k] += dz;
+          o.v[k] = __float2bfloat16_rn(k < valid ? dz * sc[k] : 0.f);
+        }
+        *reinterpret_cast<Vec16<__nv_bfloat16>*>(a.out + ((int64_t)n * hw + p) * a.c_pad + c) = o;
+      }
+    }
+  }
+  if (!active) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc0[k] = acc1[k] = 0.f;
+  }
+  if (a.sum_nc) group_reduce_add(red, acc0, tid, groups, rows, a.sum_nc + (int64_t)n * a.c, a.c);
+  if (!FINISH && a.sum_c) group_reduce_add(red, acc1, tid, groups, rows, a.sum_c, a.c);
+}
+
+template <bool FINISH>
+int launch(BwdClArgs& a, int dtype, cudaStream_t st, const char* name) {
+  const int hw = a.h * a.w;
+  const int rows = 256 / (a.c_pad >> 3);
+  // about 16 CTAs per SM in total, at least 32 pixel iterations each
+  int chunk = hw;
+  while (chunk > 32 * rows && (int64_t)a.n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 16) chunk = (chunk + 1) / 2;
+  a.chunk = chunk;
+  dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)a.n);
+  if (dtype == VCN_BF16) modconv_bwd_cl_kernel<__nv_bfloat16, FINISH><<<grid, 256, 0, st>>>(a);
+  else modconv_bwd_cl_kernel<__half, FINISH><<<grid, 256, 0, st>>>(a);
+  VCN_LAUNCH_CHECK(name);
+  return VCN_OK;
+}
+
+}  // namespace
+
+// Entry used by vcn_modconv_bwd_pack when dy / y are 16-bit with channel stride 1.  Returns -1 when not applicable.
+int bwd_pack_cl_try(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
+                    const vcn_upfirdn2d_epilogue* epi, void* dy0, float* gsum, float* db, int n, int c, int c_pad, int h,
+                    int w, int act, float alpha, float gain, float clamp, cudaStream_t st) {
+  if (!(dtype == VCN_BF16 || dtype == VCN_F16)) return -1;
+  if (dys[1] != 1 || (y && ys[1] != 1) || c_pad > 2048) return -1;
+  BwdClArgs a;
+  memset(&a, 0, sizeof(a));
+  a.dy = dy; a.y = y;
+  for (int i = 0; i < 4; ++i) { a.as[i] = dys[i]; a.bs[i] = y ? ys[i] : 0; }
+  if (epi) { a.noise = epi->noise; a.noise_stride_n = epi->noise_stride_n; a.bias = epi->bias; a.scale = epi->scale; }
+  a.out = static_cast<__nv_bfloat16*>(dy0); a.sum_nc = gsum; a.sum_c = db;
+  a.n = n; a.c = c; a.c_pad = c_pad; a.h = h; a.w = w;
+  a.act = act; a.alpha = alpha; a.gain = gain; a.clamp = clamp;
+  return launch<false>(a, dtype, st, "modconv_bwd_pack_cl_kernel");
+}
+
+}  // namespace vcn
+
+extern "C" int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, const int64_t xs[4], const float* styles,
+                                         float* dsum, int n, int c, int c_pad, int h, int w, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(n >= 0 && c >= 1 && h >= 1 && w >= 1, "modconv_bwd_finish_cl: bad shape");
+  VCN_REQUIRE(c_pad >= c && c_pad % 8 == 0 && c_pad <= 2048, "modconv_bwd_finish_cl: c_pad must be a multiple of 8 in [c, 2048]");
+  VCN_REQUIRE(dtype == VCN_BF16, "modconv_bwd_finish_cl: dxhat / x must be bf16");
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(dxhat != nullptr, "modconv_bwd_finish_cl: dxhat must not be NULL");
+  VCN_REQUIRE(!dsum || (x && xs && xs[1] == 1), "modconv_bwd_finish_cl: dsum needs a channels-last x");
+  BwdClArgs a;
+  memset(&a, 0, sizeof(a));
+  a.dy = dxhat; a.y = dsum ? x : nullptr;
+  a.as[0] = (int64_t)h * w * c_pad; a.as[1] = 1; a.as[2] = (int64_t)w * c_pad; a.as[3] = c_pad;
+  for (int i = 0; i < 4; ++i) a.bs[i] = (dsum && xs) ? xs[i] : 0;
+  a.scale = styles; a.sum_nc = dsum;
+  a.n = n; a.c = c; a.c_pad = c_pad; a.h = h; a.w = w;
+  return launch<true>(a, dtype, static_cast<cudaStream_t>(stream), "modconv_bwd_finish_cl_kernel");
+}

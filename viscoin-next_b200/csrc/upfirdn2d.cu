@@ -111,7 +111,9 @@ struct TileGeom {
   int use_tma, vec_store;
 };
 
-template <typename T, int UP, int DOWN, int PHX, int PHY>
+// EPI: 0 = plain FIR (gain folded into the taps; nothing after the accumulation), 1 = fused scale / noise / bias with a
+// linear or lrelu activation (the synthesis layers), 2 = any activation (run-time dispatch).
+template <typename T, int UP, int DOWN, int PHX, int PHY, int EPI>
 __global__ void __launch_bounds__(256)
 upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_constant__ CUtensorMap tmap) {
   using S = typename Acc<T>::type;
@@ -122,45 +124,36 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   constexpr int NV = (UP == 1) ? (WC + V - 1) / V : 0;             // 16-byte loads per window row (UP==1)
   constexpr int WCL = (UP == 1) ? NV * V : WC;
 
+  // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ... with two shared-memory buffers - the halo tile of
+  // the next tile is in flight (TMA or cp.async) while this one is filtered and stored.
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  T* tile = reinterpret_cast<T*>(smem_raw);
   const int tile_elems = g.tp * g.ih * g.iwp;
-  float* sflt = reinterpret_cast<float*>(smem_raw + (((size_t)tile_elems * sizeof(T) + 15) & ~(size_t)15));
-  uint64_t* bar = reinterpret_cast<uint64_t*>(sflt + kF * kF);
+  const size_t buf_bytes = ((size_t)tile_elems * sizeof(T) + 127) & ~(size_t)127;
+  float* sflt = reinterpret_cast<float*>(smem_raw + 2 * buf_bytes);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sflt + kF * kF);  // [2]
 
   const int tid = threadIdx.x;
-  int bid = blockIdx.x;
-  const int bx = bid % g.tiles_x; bid /= g.tiles_x;
-  const int by = bid % g.tiles_y;
-  const int bp = bid / g.tiles_y;
-  const int tile_ox = bx * g.tw, tile_oy = by * g.th, plane0 = bp * g.tp;
   const int planes = a.n * a.c;
-  // first staged input column/row: ceil((tile_o*DOWN - pad0) / UP)
-  const int ix0 = -floor_div(-(tile_ox * DOWN - a.padx0), UP);
-  const int iy0 = -floor_div(-(tile_oy * DOWN - a.pady0), UP);
+  const int total_tiles = g.tiles_x * g.tiles_y * g.tiles_p;
 
-  if (g.use_tma) {
-    if (tid == 0) {
-      mbar_init(bar, 1);
-      fence_mbar_init();
+  auto issue = [&](int t, int b) {
+    T* tile = reinterpret_cast<T*>(smem_raw + b * buf_bytes);
+    const int bx = t % g.tiles_x, by = (t / g.tiles_x) % g.tiles_y, bp = t / (g.tiles_x * g.tiles_y);
+    const int plane0 = bp * g.tp;
+    // first staged input column/row: ceil((tile_o*DOWN - pad0) / UP)
+    const int ix0 = -floor_div(-(bx * g.tw * DOWN - a.padx0), UP);
+    const int iy0 = -floor_div(-(by * g.th * DOWN - a.pady0), UP);
+    if (g.use_tma) {
+      if (tid == 0) {
+        mbar_expect_tx(bar + b, (uint32_t)(tile_elems * sizeof(T)));
+        tma_load_3d(tile, &tmap, bar + b, ix0, iy0, plane0);
+      }
+      return;
     }
-    __syncthreads();
-    if (tid == 0) {
-      mbar_expect_tx(bar, (uint32_t)(tile_elems * sizeof(T)));
-      tma_load_3d(tile, &tmap, bar, ix0, iy0, plane0);
-    }
-  }
-  if (tid < kF * kF) {
-    const int fy = tid / kF, fx = tid % kF;
-    float w = 0.f;
-    if (fy < a.fh && fx < a.fw) w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
-    sflt[tid] = w;
-  }
-  if (!g.use_tma) {
     const T* __restrict__ px = static_cast<const T*>(a.x);
     const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
     for (int rr = warp; rr < g.tp * g.ih; rr += nwarps) {
-      const int p = rr / g.ih, r = rr - p * g.ih;
+      const int p = g.tp == 1 ? 0 : rr / g.ih, r = rr - p * g.ih;
       const int gy = iy0 + r, pl = plane0 + p;
       const bool row_ok = gy >= 0 && gy < a.in_h && pl < planes;
       const T* src = px + ((int64_t)pl * a.in_h + gy) * a.in_w;
@@ -182,10 +175,22 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
         }
       }
     }
-    if constexpr (sizeof(T) == 4) cp_async_wait_all();
+  };
+
+  if (g.use_tma && tid == 0) {
+    mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
+    fence_mbar_init();
+  }
+  if (tid < kF * kF) {
+    const int fy = tid / kF, fx = tid % kF;
+    float w = 0.f;
+    if (fy < a.fh && fx < a.fw) w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
+    sflt[tid] = w * a.gain;  // the reference scales the filter too (upfirdn2d.py:193)
   }
   __syncthreads();
-  if (g.use_tma) mbar_wait(bar, 0);
+  issue(blockIdx.x, 0);
+  cp_async_commit();
 
   S flt[kF][kF];
 #pragma unroll
@@ -197,6 +202,17 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   const int t_y = (tid / g.tx) % g.ty;
   const int t_p = tid / (g.tx * g.ty);
   const int rx = t_x * MC, ry = t_y * kMR;
+  int it = 0;
+  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+  const int b = it & 1;
+  if (t + (int)gridDim.x < total_tiles) issue(t + gridDim.x, b ^ 1);
+  cp_async_commit();
+  cp_async_wait_1();       // this thread's copies of tile t have landed ...
+  __syncthreads();         // ... and everybody else's
+  if (g.use_tma) mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
+  const T* tile = reinterpret_cast<const T*>(smem_raw + b * buf_bytes);
+  const int tile_ox = (t % g.tiles_x) * g.tw, tile_oy = ((t / g.tiles_x) % g.tiles_y) * g.th;
+  const int plane0 = (t / (g.tiles_x * g.tiles_y)) * g.tp;
   const T* wbase = tile + ((size_t)t_p * g.ih + (ry * DOWN) / UP) * g.iwp + (rx * DOWN) / UP;
 
   S acc[kMR][MC];
@@ -238,8 +254,17 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
 
   const int plane = plane0 + t_p;
   const int ox = tile_ox + rx, oy_base = tile_oy + ry;
-  if (plane >= planes || ox >= a.out_w) return;
+  if (plane < planes && ox < a.out_w) {
   T* __restrict__ py = static_cast<T*>(a.y) + (int64_t)plane * a.out_h * a.out_w;
+  // per-thread constants of the fused epilogue (the plane is fixed per thread)
+  S sc = S(1), bi = S(0);
+  const float* nrow = nullptr;
+  if constexpr (EPI != 0) {
+    if (a.scale) sc = S(a.scale[plane]);
+    if (a.act && a.bias) bi = S(a.bias[plane % a.c]);
+    if (a.noise) nrow = a.noise + (int64_t)(plane / a.c) * a.noise_stride_n;
+  }
+  const bool full = ox + MC <= a.out_w;
 #pragma unroll
   for (int r = 0; r < kMR; ++r) {
     const int oy = oy_base + r;
@@ -247,17 +272,33 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
     Vec16<T> out;
 #pragma unroll
     for (int c = 0; c < MC; ++c) {
-      const int oxc = ox + c < a.out_w ? ox + c : a.out_w - 1;
-      out.v[c] = from_acc<T>(epilogue<S>(a, acc[r][c], plane, oy, oxc));
+      S v = acc[r][c];
+      if constexpr (EPI != 0) {
+        v *= sc;
+        if (nrow) v += S(nrow[(int64_t)oy * a.out_w + (ox + c < a.out_w ? ox + c : a.out_w - 1)]);
+        if constexpr (EPI == 1) {
+          if (a.act) {  // linear (alpha = 1) or lrelu
+            v += bi;
+            v = (v > S(0) ? v : v * S(a.act == VCN_ACT_LRELU ? a.alpha : 1.f)) * S(a.act_gain);
+            if (a.clamp >= 0.f) v = (v > S(-a.clamp) && v < S(a.clamp)) ? v : (v >= S(0) ? S(a.clamp) : S(-a.clamp));
+          }
+        } else {
+          if (a.act) v = act_eval<S, 0>(v + bi, S(0), S(0), S(1), a.act, 0, S(a.alpha), S(a.act_gain), S(a.clamp));
+        }
+      }
+      out.v[c] = from_acc<T>(v);
     }
     T* dst = py + (int64_t)oy * a.out_w + ox;
-    if (g.vec_store && ox + MC <= a.out_w) {
+    if (g.vec_store && full) {
       st_stream(dst, out);
     } else {
 #pragma unroll
       for (int c = 0; c < MC; ++c)
         if (ox + c < a.out_w) dst[c] = out.v[c];
     }
+  }
+  }
+  __syncthreads();  // buffer b is free for the tile after next
   }
 }
 
@@ -457,8 +498,8 @@ TileGeom make_geom(const UpfirdnArgs& a, int up, int down) {
   return g;
 }
 
-template <typename T, int UP, int DOWN, int PHX, int PHY>
-int launch_tile(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st) {
+template <typename T, int UP, int DOWN, int PHX, int PHY, int EPI>
+int launch_tile_epi(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st) {
   const size_t e = sizeof(T);
   const int planes = a.n * a.c;
   CUtensorMap tmap;
@@ -481,14 +522,28 @@ int launch_tile(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st) {
     if (rc) return rc;
   }
   g.vec_store = aligned16(a.y) && ((size_t)a.out_w * e) % 16 == 0;
-  const size_t smem = (((size_t)g.tp * g.ih * g.iwp * e + 15) & ~(size_t)15) + kF * kF * sizeof(float) + 16;
-  auto kern = upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY>;
+  const size_t buf_bytes = ((size_t)g.tp * g.ih * g.iwp * e + 127) & ~(size_t)127;
+  const size_t smem = 2 * buf_bytes + kF * kF * sizeof(float) + 16;
+  auto kern = upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY, EPI>;
   if (smem > 48 * 1024) VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t grid = (int64_t)g.tiles_x * g.tiles_y * g.tiles_p;
-  if (grid > 0x7fffffffLL) { set_error("upfirdn2d: grid too large"); return VCN_ERR_INVALID; }
+  const int64_t tiles = (int64_t)g.tiles_x * g.tiles_y * g.tiles_p;
+  if (tiles > 0x7fffffffLL) { set_error("upfirdn2d: too many tiles"); return VCN_ERR_INVALID; }
+  // persistent: as many CTAs as stay resident (at most 4 per SM; shared memory may allow fewer)
+  int per_sm = (int)((200 * 1024) / (smem + 1024));
+  if (per_sm > 4) per_sm = 4;
+  if (per_sm < 1) per_sm = 1;
+  int64_t grid = (int64_t)sm_count() * per_sm;
+  if (grid > tiles) grid = tiles;
   kern<<<(unsigned)grid, g.tx * g.ty * g.tp, smem, st>>>(a, g, tmap);
   VCN_LAUNCH_CHECK("upfirdn2d_tile_kernel");
   return VCN_OK;
+}
+
+template <typename T, int UP, int DOWN, int PHX, int PHY>
+int launch_tile(const UpfirdnArgs& a, const TileGeom& g, int dtype, cudaStream_t st) {
+  if (!a.scale && !a.noise && !a.act) return launch_tile_epi<T, UP, DOWN, PHX, PHY, 0>(a, g, dtype, st);
+  if (a.act == 0 || a.act == VCN_ACT_LINEAR || a.act == VCN_ACT_LRELU) return launch_tile_epi<T, UP, DOWN, PHX, PHY, 1>(a, g, dtype, st);
+  return launch_tile_epi<T, UP, DOWN, PHX, PHY, 2>(a, g, dtype, st);
 }
 
 template <typename T>

@@ -193,6 +193,25 @@ def bwd_finish(dxhat, x, styles, want_dsum):
     return dsum
 
 
+def bwd_finish_cl(dxhat, x, styles, want_dsum):
+    """vcn_modconv_bwd_finish_cl on the resident pipeline: dxhat bf16 logical [N,C,H,W] in channels_last memory with C a
+    multiple of 8 (the GEMM output), scaled by s in place; returns dsum [N,C] = sum_p dxhat*x (or None)."""
+    lib = _lib.load()
+    n, c, h, w = dxhat.shape
+    assert dxhat.dtype == torch.bfloat16 and dxhat.is_contiguous(memory_format=torch.channels_last) and c % 8 == 0
+    dsum = torch.zeros([n, c], dtype=torch.float32, device=dxhat.device) if want_dsum else None
+    if n == 0:
+        return dsum
+    if want_dsum:
+        assert x.dtype == torch.bfloat16 and x.stride(1) == 1 and x.shape == dxhat.shape
+    with torch.cuda.device(dxhat.device):
+        st = lib.vcn_modconv_bwd_finish_cl(_lib.ptr(dxhat), _lib.ptr(x) if want_dsum else None, _lib.dtype_code(dxhat.dtype),
+                                           ctypes.byref(_strides4(x)) if want_dsum else None, _lib.ptr(styles), _lib.ptr(dsum),
+                                           n, c, c, h, w, _lib.current_stream(dxhat.device))
+    _lib.check(st, "vcn_modconv_bwd_finish_cl")
+    return dsum
+
+
 def demod_grad(ds, styles, gsum, dcoef, wsq):
     lib = _lib.load()
     n, cin = ds.shape
@@ -258,14 +277,22 @@ class _ModConvLayer(torch.autograd.Function):
         d = demod_coefs(styles32, wsq) if demodulate else None
         xhat = modulate_pack(x, styles32)
         epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
+        # resident pipeline: 16-bit channels-last activations stay 16-bit channels-last (forward and backward); a ToRGB
+        # layer (cout < 8) leaves it and writes fp32 NCHW for the image accumulation
+        resident = x.dtype == torch.bfloat16 and x.stride(1) == 1 and cin % 8 == 0
+        cl_out = resident and cout % 8 == 0
+        out_dtype = x.dtype if (cl_out or not resident) else torch.float32
         if up == 1:
             kind = _lib.CONV_FPROP if flip_weight else _lib.CONV_DGRAD
-            y = conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=x.dtype, epilogue=epi)
+            y = conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=out_dtype, channels_last=cl_out, epilogue=epi)
         else:
-            z = conv_igemm(xhat, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=torch.float32)
+            z = conv_igemm(xhat, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=torch.bfloat16 if cl_out else torch.float32,
+                           channels_last=cl_out)
             f = resample_filter.to(device=x.device, dtype=torch.float32)
+            fmt = torch.channels_last if cl_out else torch.contiguous_format
             y = _upfirdn2d.launch(z, f, 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi,
-                                  out=torch.empty([n, cout, 2 * h, 2 * w], dtype=x.dtype, device=x.device))
+                                  out=torch.empty([n, cout, 2 * h, 2 * w], dtype=out_dtype, device=x.device, memory_format=fmt))
+        ctx.resident = resident
         ctx.cfg = cfg
         ctx.has = (styles is not None, noise is not None, bias is not None)
         ctx.save_for_backward(x, weight, styles32, noise, bias, resample_filter, d, wsq, y)
@@ -282,9 +309,13 @@ class _ModConvLayer(torch.autograd.Function):
                                 "freezes the synthesis weights, viscoin/training/viscoin.py:116)")
         n, cin, h, w = x.shape
         cout, _, kh, kw = weight.shape
-        dy = dy.contiguous() if not dy.is_contiguous() else dy
+        resident = ctx.resident
         if dy.dtype != y.dtype:
             dy = dy.to(y.dtype)
+        if y.stride(1) == 1 and y.shape[1] > 1:
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        elif not dy.is_contiguous():
+            dy = dy.contiguous()
         epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
         want_g = demodulate and need_s
         dy0, gsum, db = bwd_pack(dy, y if (act is not None or want_g) else None, epi, want_g, need_b and bias is not None)
@@ -293,7 +324,8 @@ class _ModConvLayer(torch.autograd.Function):
             if up == 1:
                 wt_t, _ = _packed(weight, True, False, False)
                 kind = _lib.CONV_DGRAD if flip_weight else _lib.CONV_FPROP
-                dxhat = conv_igemm(dy0, wt_t, kind, cin, kh, kw, out_dtype=torch.float32)
+                dxhat = conv_igemm(dy0, wt_t, kind, cin, kh, kw, out_dtype=torch.bfloat16 if resident else torch.float32,
+                                   channels_last=resident)
             else:
                 wt_t, _ = _packed(weight, True, bool(flip_weight), False)
                 f = resample_filter.to(device=x.device, dtype=torch.float32)
@@ -301,8 +333,12 @@ class _ModConvLayer(torch.autograd.Function):
                 dz = _upfirdn2d.launch(dy0.permute(0, 3, 1, 2), f, 1, 1, 1, 1, 2, 2, 2, 2, True, 4.0)
                 dz = dz.permute(0, 2, 3, 1)
                 assert dz.is_contiguous()
-                dxhat = conv_igemm(dz, wt_t, _lib.CONV_SCONV2, cin, 3, 3, out_dtype=torch.float32)
-            ds1 = bwd_finish(dxhat, x, styles32, need_s and styles32 is not None)
+                dxhat = conv_igemm(dz, wt_t, _lib.CONV_SCONV2, cin, 3, 3, out_dtype=torch.bfloat16 if resident else torch.float32,
+                                   channels_last=resident)
+            if resident:
+                ds1 = bwd_finish_cl(dxhat, x, styles32, need_s and styles32 is not None)
+            else:
+                ds1 = bwd_finish(dxhat, x, styles32, need_s and styles32 is not None)
             if need_x:
                 dx = dxhat if x.dtype == torch.float32 else dxhat.to(x.dtype)
             if need_s and styles32 is not None:

@@ -182,12 +182,17 @@ class SynthesisBlock(torch.nn.Module):
             img = img.add_(y) if img is not None else y
         return act, img
 
-    def forward(self, x, img, ws, force_fp32=False, fused_modconv=None, **layer_kwargs):
+    def forward(self, x, img, ws, force_fp32=False, fused_modconv=None, resident=False, **layer_kwargs):
+        """resident=True (training on the 'skip' / 'orig' architectures): activations are bf16 channels_last tensors from
+        block to block, forward and backward (modconv._ModConvLayer keeps them that way); img stays fp32 NCHW."""
         assert tuple(ws.shape[1:]) == (self.num_conv + self.num_torgb, self.w_dim)
         w_iter = iter(ws.unbind(dim=1))
+        resident = resident and self.architecture != "resnet"
         if self.in_channels == 0:
             x = self.const.to(torch.float32).unsqueeze(0).repeat([ws.shape[0], 1, 1, 1])
-        else:
+            if resident:
+                x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        elif not resident:
             x = x.to(torch.float32)
         if self.in_channels == 0:
             x = self.conv1(x, next(w_iter), **layer_kwargs)
@@ -214,6 +219,9 @@ class SynthesisNetwork(torch.nn.Module):
         super().__init__()
         self.w_dim, self.img_resolution, self.img_channels = w_dim, img_resolution, img_channels
         self.img_resolution_log2 = int(np.log2(img_resolution))
+        # differentiable forward with bf16 channels_last activations between layers (see SynthesisBlock.forward); off by
+        # default: the reference's configurations store fp32 (networks.py:382-383 with num_fp16_res = 0)
+        self.resident_bf16 = False
         self.block_resolutions = [2 ** i for i in range(2, self.img_resolution_log2 + 1)]
         channels_dict = {res: min(channel_base // res, channel_max) for res in self.block_resolutions}
         self.num_ws = 0
@@ -243,7 +251,7 @@ class SynthesisNetwork(torch.nn.Module):
             if fast:  # inference: activations stay resident as bf16 NHWC, no per-layer layout / modulation passes
                 x, img = getattr(self, f"b{res}").forward_nhwc(x, img, cur_ws, **block_kwargs)
             else:
-                x, img = getattr(self, f"b{res}")(x, img, cur_ws, **block_kwargs)
+                x, img = getattr(self, f"b{res}")(x, img, cur_ws, resident=self.resident_bf16, **block_kwargs)
         return img
 
 
@@ -364,9 +372,12 @@ class GraphedSynthesis:
             for _ in range(2):  # packs the frozen weights, binds contexts, fills the allocator
                 synthesis(self.ws, noise_mode=noise_mode)
         torch.cuda.current_stream(p.device).wait_stream(side)
+        from .. import _lib
+        count0 = _lib.load().vcn_launch_count()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph), torch.no_grad():
             self.img = synthesis(self.ws, noise_mode=noise_mode)
+        self.launches = int(_lib.load().vcn_launch_count() - count0)  # libvcn kernels one replay launches
 
     def __call__(self, ws):
         self.ws.copy_(ws, non_blocking=True)

@@ -28,6 +28,24 @@ class Classifier(nn.Module):
         return self.linear(output_state), results["hidden_states"]
 
 
+def calibrate_batchnorm(model, images):
+    """Random-init harness only (the reference always loads a trained f): one forward in train mode with cumulative
+    averaging so that every BatchNorm's running statistics equal the batch statistics of `images`.  Without it a
+    random-init ResNet-50 in eval mode (running mean 0 / var 1) produces logits of magnitude 1e2..1e3, for which the
+    reference's own ``softmax(...).log()`` (losses.py:27) is -inf * 0 = NaN."""
+    bns = [m for m in model.modules() if isinstance(m, nn.BatchNorm2d)]
+    for m in bns:
+        m.reset_running_stats()
+        m.momentum = None
+    was_training = model.training
+    model.train()
+    with torch.no_grad():
+        model(images)
+    model.train(was_training)
+    for m in bns:
+        m.momentum = 0.1
+
+
 class ConceptExtractor(nn.Module):
     def __init__(self, n_concepts=256, latent_channels=512, input_channels1=512, input_channels2=1024, input_channels3=2048):
         super().__init__()
@@ -95,8 +113,10 @@ class LPIPS(nn.Module):
 
     @staticmethod
     def _unit(f, eps=1e-10):
+        # lpips.normalize_tensor: f / (sqrt(sum f^2) + eps).  The 1e-30 under the root only matters where a pixel's
+        # feature vector is exactly zero: the value is unchanged (0 / eps) but the gradient is 0 instead of 0 * inf = NaN
         f = f.float()
-        return f / (f.square().sum(dim=1, keepdim=True).sqrt() + eps)
+        return f / ((f.square().sum(dim=1, keepdim=True) + 1e-30).sqrt() + eps)
 
     def forward(self, in0, in1):
         n = in0.shape[0]

@@ -30,9 +30,9 @@ from . import viscoin_models as _models
 
 def cross_cross_entropy_loss(prediction, target_prediction):
     """losses.py:25-29."""
-    p = F.softmax(prediction.float(), dim=1)
+    # log_softmax == softmax(...).log() wherever the latter is finite; it stays finite when a probability underflows
     t = F.softmax(target_prediction.float(), dim=1)
-    return (p.log() * -t).sum(dim=1).mean()
+    return (F.log_softmax(prediction.float(), dim=1) * -t).sum(dim=1).mean()
 
 
 def concept_regularization_loss(concept_embeddings):
@@ -120,9 +120,18 @@ class VisCoINTrainer:
         self.generator_gan = generator_gan.to(self.device)
         self.lpips = lpips.to(self.device)
         if self.channels_last:
-            for m in (self.classifier, self.concept_extractor, self.lpips):
+            for m in (self.classifier, self.lpips):  # frozen nets only: trainable grads are views into flat buckets
                 m.to(memory_format=torch.channels_last)
+        if models is None:
+            # random-init harness: give f's BatchNorms the statistics of the images it will see (noise-like "real"
+            # images and smooth generated ones); a trained f ships with its own (see calibrate_batchnorm)
+            with torch.no_grad():
+                fakes = synthetic_samples(self.generator_gan, 4, self.device, torch.Generator().manual_seed(seed)).float()
+            noise = torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(seed + 1)).to(self.device)
+            _models.calibrate_batchnorm(self.classifier, torch.cat([noise, fakes]))
         self.deterministic = deterministic
+        self.viscoin_gan.synthesis.resident_bf16 = self.amp is not None  # bf16 run: activations stay bf16 NHWC
+        self.synthesis_kwargs = {}  # e.g. {'noise_mode': 'const'} for parity runs; the reference passes none (:193)
         _dp.broadcast_parameters([self.classifier, self.concept_extractor, self.explainer, self.viscoin_gan,
                                   self.generator_gan, self.lpips])
         # viscoin.py:130-134; gradients live in flat buckets (dp.GradBuckets) whether or not there are peers
@@ -165,7 +174,8 @@ class VisCoINTrainer:
             losses["cr"] = p.delta * concept_regularization_loss(encoded_concepts)
             losses["of"] = p.alpha * output_fidelity_loss(classes, explainer_classes)
         losses["ortho"] = concept_orthogonality_loss(self.concept_extractor)
-        rebuilt_images, gan_latents = self.viscoin_gan(z1=encoded_concepts, z2=extra_info, return_latents=True)
+        rebuilt_images, gan_latents = self.viscoin_gan(z1=encoded_concepts, z2=extra_info, return_latents=True,
+                                                       **self.synthesis_kwargs)
         rebuilt_classes, _ = self._f(rebuilt_images)
         with self._autocast():
             lp = lambda a, b: self.lpips(a.contiguous(memory_format=torch.channels_last) if self.channels_last else a,
