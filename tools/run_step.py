@@ -54,4 +54,32 @@ if os.environ.get("VCN_STEP_PROFILE", "0") == "1":
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         tr.step(real, labels)
         torch.cuda.synchronize()
-    print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
+    from torch.autograd import DeviceType
+    cats, tot = {}, 0.0
+    for e in prof.key_averages():
+        if e.device_type != DeviceType.CUDA:
+            continue
+        name, t = e.key, e.self_device_time_total
+        if "vcn::" in name:
+            c = "ours  " + name.split("::")[-1].split("(")[0].split("<")[0]
+        elif "elementwise" in name or "reduce_kernel" in name or "vectorized" in name or "Pool" in name or "pool" in name:
+            c = "torch elementwise/reduce/pool"
+        elif "batch_norm" in name or "bn_" in name:
+            c = "torch batch_norm"
+        elif "Memcpy" in name or "Memset" in name:
+            c = "memcpy/memset"
+        elif "adam" in name.lower():
+            c = "fused adam"
+        else:
+            c = "library conv/gemm + other"
+            cats.setdefault("  lib: " + name[:60], [0.0, 0])
+            cats["  lib: " + name[:60]][0] += t
+            cats["  lib: " + name[:60]][1] += e.count
+        cats.setdefault(c, [0.0, 0])
+        cats[c][0] += t
+        cats[c][1] += e.count
+        tot += t
+    top = sorted(cats.items(), key=lambda kv: -kv[1][0])
+    for k, (t, n) in [kv for kv in top if not kv[0].startswith("  lib")] + [kv for kv in top if kv[0].startswith("  lib")][:12]:
+        print("%9.3f ms %5d x  %s" % (t / 1e3, n, k))
+    print("device total %.3f ms" % (tot / 1e3))

@@ -1,0 +1,186 @@
+// lpips_tap.cu - one feature tap of the LPIPS perceptual distance, fused (the reconstruction-loss
+// reductions of viscoin/training/losses.py:113-157; algorithm of the third-party `lpips` v0.1.4 package):
+//
+//   d[n] = mean_p  sum_c lin[c] * ( a[n,p,c] / (|a[n,p,:]| + eps)  -  b[n,p,c] / (|b[n,p,:]| + eps) )^2,   eps = 1e-10
+//
+// a, b: channels-fastest feature maps (VGG-16 relu taps, 64..512 channels, 16-bit under autocast or fp32).  The torch
+// formulation materialises ~10 full-size fp32 temporaries forward and as many backward; here the forward reads a and b
+// once (a lane group keeps a pixel's channel vector in registers: two phases - norms, then the weighted squared
+// difference - without re-reading) and the backward reads them once more and writes da.  HBM-bound.
+//   backward:  da_c = g[n]/HW * ( 2 lin_c u_c / na  -  2 a_c T / (na^2 |a|) ),  u = a/na - b/nb,  T = sum_c lin_c u_c a_c,
+//              na = |a| + eps (the second term is 0 where |a| = 0).
+#include <string.h>
+
+#include "common.cuh"
+
+namespace vcn {
+namespace {
+
+constexpr int kMaxVec = 2;  // 16-byte... 8-channel vectors per lane: C <= 8 * 32 * kMaxVec = 512
+
+struct LpipsArgs {
+  const void* a; const void* b;
+  int64_t as[4], bs[4];   // (n, c, h, w) element strides, c-stride 1
+  const float* lin;
+  float* val;             // [n], accumulated (forward)
+  const float* gval;      // [n] (backward)
+  void* da;               // dense channels-last [n,h,w,c], dtype of a (backward)
+  int n, c, h, w;
+  float scale;            // 1 / (h*w)
+};
+
+template <typename T> __device__ __forceinline__ void ld8(const T* p, float (&v)[8]) {
+  if constexpr (sizeof(T) == 2) {
+    const Vec16<T> in = *reinterpret_cast<const Vec16<T>*>(p);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = to_acc<T>(in.v[k]);
+  } else {
+    const float4 lo = *reinterpret_cast<const float4*>(p), hi = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
+  }
+}
+
+__device__ __forceinline__ float group_sum(float v, int width) {
+  for (int o = width >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// G lanes per pixel (power of two <= 32), NV vectors of 8 channels per lane: C = 8 * G * NV.
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(256) lpips_tap_kernel(const LpipsArgs a, const int G, const int NV, const int chunk) {
+  const int n = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane / G, gl = lane % G;         // pixel slot inside the warp, lane inside the group
+  const int ppw = 32 / G;                          // pixels per warp per iteration
+  const int hw = a.h * a.w;
+  const int p_end = min(hw, (int)(blockIdx.x + 1) * chunk);
+  float lin[kMaxVec][8];
+#pragma unroll
+  for (int v = 0; v < kMaxVec; ++v)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) lin[v][k] = v < NV ? a.lin[(v * G + gl) * 8 + k] : 0.f;
+  const T* pa = static_cast<const T*>(a.a) + (int64_t)n * a.as[0];
+  const T* pb = static_cast<const T*>(a.b) + (int64_t)n * a.bs[0];
+  const float g = BWD ? a.gval[n] * a.scale : 0.f;
+  float acc = 0.f;
+  for (int p0 = blockIdx.x * chunk + warp * ppw; p0 < p_end; p0 += 8 * ppw) {
+    const int p = p0 + sub;
+    const bool ok = p < p_end;
+    const int py = ok ? p / a.w : 0, px = ok ? p - py * a.w : 0;
+    float x[kMaxVec][8], y[kMaxVec][8];
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int v = 0; v < kMaxVec; ++v) {
+      if (v < NV && ok) {
+        const int c = (v * G + gl) * 8;
+        ld8<T>(pa + py * a.as[2] + px * a.as[3] + c, x[v]);
+        ld8<T>(pb + py * a.bs[2] + px * a.bs[3] + c, y[v]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[v][k] = y[v][k] = 0.f;
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { s0 = fmaf(x[v][k], x[v][k], s0); s1 = fmaf(y[v][k], y[v][k], s1); }
+    }
+    s0 = group_sum(s0, G); s1 = group_sum(s1, G);
+    const float n0 = sqrtf(s0), ia = 1.f / (n0 + 1e-10f), ib = 1.f / (sqrtf(s1) + 1e-10f);
+    float d = 0.f;  // forward: sum lin u^2.  backward: T = sum lin u a
+#pragma unroll
+    for (int v = 0; v < kMaxVec; ++v)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float u = x[v][k] * ia - y[v][k] * ib;
+        d = fmaf(lin[v][k] * u, BWD ? x[v][k] : u, d);
+      }
+    d = group_sum(d, G);
+    if (!BWD) {
+      if (ok && gl == 0) acc += d;
+    } else if (ok) {
+      const float k2 = n0 > 0.f ? 2.f * g * d * ia * ia / n0 : 0.f, k1 = 2.f * g * ia;
+#pragma unroll
+      for (int v = 0; v < kMaxVec; ++v) {
+        if (v < NV) {
+          const int c = (v * G + gl) * 8;
+          T* dst = static_cast<T*>(a.da) + ((int64_t)n * hw + p) * a.c + c;
+          float o[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) o[k] = k1 * lin[v][k] * (x[v][k] * ia - y[v][k] * ib) - k2 * x[v][k];
+          if constexpr (sizeof(T) == 2) {
+            Vec16<T> ov;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) ov.v[k] = from_acc<T>(o[k]);
+            *reinterpret_cast<Vec16<T>*>(dst) = ov;
+          } else {
+            *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(o[4], o[5], o[6], o[7]);
+          }
+        }
+      }
+    }
+  }
+  if (!BWD) {
+    __shared__ float red[8];
+    acc = warp_sum(acc);
+    if (lane == 0) red[warp] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 8; ++i) t += red[i];
+      atomicAdd(a.val + n, t * a.scale);
+    }
+  }
+}
+
+template <bool BWD>
+int run(const void* fa, const void* fb, int dtype, const int64_t* as, const int64_t* bs, const float* lin, float* val,
+        const float* gval, void* da, int n, int c, int h, int w, cudaStream_t st, const char* name) {
+  VCN_REQUIRE(n >= 0 && c >= 8 && h >= 1 && w >= 1, "%s: bad shape", name);
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(fa && fb && lin && as && bs, "%s: NULL pointer", name);
+  VCN_REQUIRE(as[1] == 1 && bs[1] == 1, "%s: feature maps must be channels-last (channel stride 1)", name);
+  const int vecs = c / 8;
+  VCN_REQUIRE(c % 8 == 0 && vecs <= 32 * kMaxVec, "%s: channels (%d) must be a multiple of 8, at most %d", name, c, 256 * kMaxVec);
+  int G = 1;
+  while (G < 32 && G < vecs) G <<= 1;
+  const int NV = (vecs + G - 1) / G;
+  VCN_REQUIRE(G * NV == vecs, "%s: channels/8 (%d) must be a power of two or a multiple of 32", name, vecs);
+  const int64_t align = dtype == VCN_F32 ? 4 : 8;
+  VCN_REQUIRE(aligned16(fa) && aligned16(fb) && (as[0] | as[2] | as[3]) % align == 0 && (bs[0] | bs[2] | bs[3]) % align == 0,
+              "%s: feature maps must be 16-byte aligned per pixel", name);
+  LpipsArgs a;
+  memset(&a, 0, sizeof(a));
+  a.a = fa; a.b = fb; a.lin = lin; a.val = val; a.gval = gval; a.da = da;
+  for (int i = 0; i < 4; ++i) { a.as[i] = as[i]; a.bs[i] = bs[i]; }
+  a.n = n; a.c = c; a.h = h; a.w = w; a.scale = 1.f / ((float)h * (float)w);
+  const int hw = h * w;
+  int chunk = hw;
+  const int per_iter = 8 * (32 / G);
+  while (chunk > 8 * per_iter && (int64_t)n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 16) chunk = (chunk + 1) / 2;
+  chunk = (chunk + per_iter - 1) / per_iter * per_iter;
+  dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)n);
+  switch (dtype) {
+    case VCN_F32: lpips_tap_kernel<float, BWD><<<grid, 256, 0, st>>>(a, G, NV, chunk); break;
+    case VCN_F16: lpips_tap_kernel<__half, BWD><<<grid, 256, 0, st>>>(a, G, NV, chunk); break;
+    case VCN_BF16: lpips_tap_kernel<__nv_bfloat16, BWD><<<grid, 256, 0, st>>>(a, G, NV, chunk); break;
+    default: set_error("%s: unsupported dtype %d", name, dtype); return VCN_ERR_INVALID;
+  }
+  VCN_LAUNCH_CHECK(name);
+  return VCN_OK;
+}
+
+}  // namespace
+}  // namespace vcn
+
+extern "C" int vcn_lpips_tap_fwd(const void* fa, const void* fb, int dtype, const int64_t as[4], const int64_t bs[4],
+                                 const float* lin, float* val, int n, int c, int h, int w, void* stream) {
+  VCN_REQUIRE(val != nullptr || n == 0, "lpips_tap_fwd: val must not be NULL");
+  return vcn::run<false>(fa, fb, dtype, as, bs, lin, val, nullptr, nullptr, n, c, h, w, static_cast<cudaStream_t>(stream),
+                         "lpips_tap_fwd");
+}
+
+extern "C" int vcn_lpips_tap_bwd(const void* fa, const void* fb, int dtype, const int64_t as[4], const int64_t bs[4],
+                                 const float* lin, const float* gval, void* da, int n, int c, int h, int w, void* stream) {
+  VCN_REQUIRE((gval != nullptr && da != nullptr) || n == 0, "lpips_tap_bwd: gval and da must not be NULL");
+  return vcn::run<true>(fa, fb, dtype, as, bs, lin, nullptr, gval, da, n, c, h, w, static_cast<cudaStream_t>(stream),
+                        "lpips_tap_bwd");
+}

@@ -47,11 +47,11 @@ __device__ __forceinline__ void group_reduce_add(float (*red)[8], const float (&
 #pragma unroll
   for (int k = 0; k < 8; ++k) red[tid][k] = acc[k];
   __syncthreads();
-  if (tid < groups * 8) {
-    const int g = tid >> 3, k = tid & 7;
+  for (int ch = tid; ch < groups * 8; ch += 256) {  // up to 2048 channels on 256 threads
+    const int g = ch >> 3, k = ch & 7;
     float t = 0.f;
     for (int j = 0; j < rows; ++j) t += red[j * groups + g][k];
-    if (g * 8 + k < c_valid) atomicAdd(dst + g * 8 + k, t);
+    if (ch < c_valid) atomicAdd(dst + ch, t);
   }
 }
 

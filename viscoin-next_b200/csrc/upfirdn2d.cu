@@ -136,13 +136,30 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   const int planes = a.n * a.c;
   const int total_tiles = g.tiles_x * g.tiles_y * g.tiles_p;
 
-  auto issue = [&](int t, int b) {
+  // tile index -> (bx, by, bp), advanced incrementally by gridDim.x (no integer divisions in the loop)
+  struct TileIdx { int bx, by, bp; };
+  auto decompose = [&](int t) {
+    TileIdx r;
+    r.bx = t % g.tiles_x; r.by = (t / g.tiles_x) % g.tiles_y; r.bp = t / (g.tiles_x * g.tiles_y);
+    return r;
+  };
+  const TileIdx stride = decompose((int)gridDim.x);
+  auto advance = [&](TileIdx v) {
+    v.bx += stride.bx;
+    if (v.bx >= g.tiles_x) { v.bx -= g.tiles_x; ++v.by; }
+    v.by += stride.by;
+    if (v.by >= g.tiles_y) { v.by -= g.tiles_y; ++v.bp; }
+    v.bp += stride.bp;
+    return v;
+  };
+  constexpr int KMAX = 5;  // staged row pitch <= 160 elements on the cp.async path (host guarantees it)
+
+  auto issue = [&](const TileIdx ti, int b) {
     T* tile = reinterpret_cast<T*>(smem_raw + b * buf_bytes);
-    const int bx = t % g.tiles_x, by = (t / g.tiles_x) % g.tiles_y, bp = t / (g.tiles_x * g.tiles_y);
-    const int plane0 = bp * g.tp;
+    const int plane0 = ti.bp * g.tp;
     // first staged input column/row: ceil((tile_o*DOWN - pad0) / UP)
-    const int ix0 = -floor_div(-(bx * g.tw * DOWN - a.padx0), UP);
-    const int iy0 = -floor_div(-(by * g.th * DOWN - a.pady0), UP);
+    const int ix0 = -floor_div(-(ti.bx * g.tw * DOWN - a.padx0), UP);
+    const int iy0 = -floor_div(-(ti.by * g.th * DOWN - a.pady0), UP);
     if (g.use_tma) {
       if (tid == 0) {
         mbar_expect_tx(bar + b, (uint32_t)(tile_elems * sizeof(T)));
@@ -152,23 +169,41 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
     }
     const T* __restrict__ px = static_cast<const T*>(a.x);
     const int warp = tid >> 5, lane = tid & 31, nwarps = blockDim.x >> 5;
-    for (int rr = warp; rr < g.tp * g.ih; rr += nwarps) {
-      const int p = g.tp == 1 ? 0 : rr / g.ih, r = rr - p * g.ih;
-      const int gy = iy0 + r, pl = plane0 + p;
-      const bool row_ok = gy >= 0 && gy < a.in_h && pl < planes;
-      const T* src = px + ((int64_t)pl * a.in_h + gy) * a.in_w;
-      T* dst = tile + (size_t)rr * g.iwp;
-      if constexpr (sizeof(T) == 4) {
-        // odd row pitch (the 2H+1 transposed-conv intermediate): rows are only 4-byte aligned, so neither TMA nor
-        // 16-byte loads apply.  4-byte cp.async (LDGSTS) with zero fill: the whole halo tile is in flight at once,
-        // no registers staged, a warp covers 128 contiguous bytes per instruction.
-        const uint32_t d0 = smem_u32(dst);
-        for (int cc = lane; cc < g.iwp; cc += 32) {
-          const int gx = ix0 + cc;
-          const bool ok = row_ok && gx >= 0 && gx < a.in_w;
-          cp_async4_zfill(d0 + (uint32_t)cc * 4u, ok ? src + gx : px, ok);
+    const int nrows = g.tp * g.ih;
+    if constexpr (sizeof(T) == 4) {
+      // odd row pitch (the 2H+1 transposed-conv intermediate): rows are only 4-byte aligned, so neither TMA nor
+      // 16-byte loads apply.  4-byte cp.async (LDGSTS) with zero fill: the whole halo tile is in flight at once,
+      // no registers staged, a warp covers 128 contiguous bytes per instruction.  Column validity is a per-thread
+      // bit mask computed once per tile; the row loop only moves two pointers.
+      const int gx0 = ix0 + lane;
+      uint32_t in_tile = 0, in_image = 0;
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        const int cc = lane + 32 * k, gx = gx0 + 32 * k;
+        if (cc < g.iwp) in_tile |= 1u << k;
+        if (cc < g.iwp && gx >= 0 && gx < a.in_w) in_image |= 1u << k;
+      }
+      for (int rr = warp; rr < nrows; rr += nwarps) {
+        const int p = g.tp == 1 ? 0 : rr / g.ih, r = rr - p * g.ih;
+        const int gy = iy0 + r, pl = plane0 + p;
+        const uint32_t row_mask = (gy >= 0 && gy < a.in_h && pl < planes) ? in_image : 0u;
+        const T* srow = px + ((int64_t)pl * a.in_h + gy) * a.in_w + gx0;
+        const uint32_t drow = smem_u32(tile + (size_t)rr * g.iwp + lane);
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+          if (in_tile & (1u << k)) {
+            const bool ok = (row_mask >> k) & 1u;
+            cp_async4_zfill(drow + 128u * k, ok ? srow + 32 * k : px, ok);
+          }
         }
-      } else {
+      }
+    } else {
+      for (int rr = warp; rr < nrows; rr += nwarps) {
+        const int p = g.tp == 1 ? 0 : rr / g.ih, r = rr - p * g.ih;
+        const int gy = iy0 + r, pl = plane0 + p;
+        const bool row_ok = gy >= 0 && gy < a.in_h && pl < planes;
+        const T* src = px + ((int64_t)pl * a.in_h + gy) * a.in_w;
+        T* dst = tile + (size_t)rr * g.iwp;
         for (int cc = lane; cc < g.iwp; cc += 32) {
           const int gx = ix0 + cc;
           dst[cc] = (row_ok && gx >= 0 && gx < a.in_w) ? src[gx] : from_acc<T>(S(0));
@@ -189,7 +224,8 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
     sflt[tid] = w * a.gain;  // the reference scales the filter too (upfirdn2d.py:193)
   }
   __syncthreads();
-  issue(blockIdx.x, 0);
+  TileIdx cur = decompose((int)blockIdx.x);
+  issue(cur, 0);
   cp_async_commit();
 
   S flt[kF][kF];
@@ -205,14 +241,16 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   int it = 0;
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
   const int b = it & 1;
-  if (t + (int)gridDim.x < total_tiles) issue(t + gridDim.x, b ^ 1);
+  const TileIdx nxt = advance(cur);
+  if (t + (int)gridDim.x < total_tiles) issue(nxt, b ^ 1);
   cp_async_commit();
   cp_async_wait_1();       // this thread's copies of tile t have landed ...
   __syncthreads();         // ... and everybody else's
   if (g.use_tma) mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
   const T* tile = reinterpret_cast<const T*>(smem_raw + b * buf_bytes);
-  const int tile_ox = (t % g.tiles_x) * g.tw, tile_oy = ((t / g.tiles_x) % g.tiles_y) * g.th;
-  const int plane0 = (t / (g.tiles_x * g.tiles_y)) * g.tp;
+  const int tile_ox = cur.bx * g.tw, tile_oy = cur.by * g.th;
+  const int plane0 = cur.bp * g.tp;
+  cur = nxt;
   const T* wbase = tile + ((size_t)t_p * g.ih + (ry * DOWN) / UP) * g.iwp + (rx * DOWN) / UP;
 
   S acc[kMR][MC];
@@ -522,6 +560,7 @@ int launch_tile_epi(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st
     if (rc) return rc;
   }
   g.vec_store = aligned16(a.y) && ((size_t)a.out_w * e) % 16 == 0;
+  if (!g.use_tma && e == 4 && g.iwp > 160) { set_error("upfirdn2d: staged pitch %d exceeds the cp.async path", g.iwp); return VCN_ERR_UNSUPPORTED; }
   const size_t buf_bytes = ((size_t)g.tp * g.ih * g.iwp * e + 127) & ~(size_t)127;
   const size_t smem = 2 * buf_bytes + kF * kF * sizeof(float) + 16;
   auto kern = upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY, EPI>;
