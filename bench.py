@@ -371,9 +371,20 @@ class TrainStep:
         self.labels = torch.randint(0, 200, (self.n,), device=device, generator=g)
         self.zgen = torch.Generator().manual_seed(seed)
         self.last = None
+        self.graph = os.environ.get("VCN_BENCH_GRAPH", "1") == "1"
+
+    @property
+    def graph_launches(self):
+        return self.tr.graph_launches
+
+    def _step(self, real, labels):
+        if self.graph:  # whole iteration replayed from one CUDA graph (first calls run eagerly and capture)
+            return self.tr.step_graphed(real, labels, 1000, z_generator=self.zgen)
+        return self.tr.step(real.to(self.tr.device, non_blocking=True), labels.to(self.tr.device, non_blocking=True), 1000,
+                            z_generator=self.zgen)
 
     def step(self):
-        self.last = self.tr.step(self.real, self.labels, 1000, z_generator=self.zgen)
+        self.last = self._step(self.real, self.labels)
         return self.last
 
     def e2e_setup(self, device):
@@ -383,8 +394,7 @@ class TrainStep:
         self.d2h = 4
 
     def e2e_step(self, device):
-        out = self.tr.step(self.hreal.to(device, non_blocking=True), self.hlabels.to(device, non_blocking=True), 1000,
-                           z_generator=self.zgen)
+        out = self._step(self.hreal, self.hlabels)  # pinned host buffers -> device inside the step
         self.loss_value = float(out["total"])  # device -> host read of the step's result
 
     def roofline(self, device, peaks, iters=20):

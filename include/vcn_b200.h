@@ -164,6 +164,17 @@ int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, const int64
 int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const float* dcoef, const float* wsq,
                    int n, int cin, int cout, void* stream);
 
+/* ---- LPIPS feature tap (the reconstruction-loss reductions next to the hot path) -----------------------
+ * One tap of lpips v0.1.4 (`normalize_tensor` -> squared difference -> 1x1 `lin` -> spatial mean), as called from
+ * viscoin/training/losses.py:113-123:
+ *   val[n] += mean_p sum_c lin[c] * (a[n,p,c]/(|a[n,p,:]|+1e-10) - b[n,p,c]/(|b[n,p,:]|+1e-10))^2
+ * fa, fb: [n,c,h,w] feature maps with channel stride 1 (channels_last), f32 / f16 / bf16, strides as/bs in elements;
+ * c a multiple of 8, c/8 a power of two or a multiple of 32, c <= 512.  val must be zeroed by the caller.
+ * bwd: da (dense channels-last [n,h,w,c], dtype of fa) = gval[n] * d val[n] / d fa. */
+int vcn_lpips_tap_fwd(const void* fa, const void* fb, int dtype, const int64_t as[4], const int64_t bs[4],
+                      const float* lin, float* val, int n, int c, int h, int w, void* stream);
+int vcn_lpips_tap_bwd(const void* fa, const void* fb, int dtype, const int64_t as[4], const int64_t bs[4],
+                      const float* lin, const float* gval, void* da, int n, int c, int h, int w, void* stream);
 
 #ifdef __cplusplus
 }

@@ -47,9 +47,24 @@ for it in range(steps):
         it, float(total), e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2]), e[2].elapsed_time(e[3]), e[0].elapsed_time(e[3]),
         (w1 - w0) * 1e3), flush=True)
 print({k: round(float(v), 5) for k, v in losses.items()})
+if os.environ.get("VCN_STEP_GRAPH", "1") == "1":
+    del tr
+    torch.cuda.empty_cache()
+    tr = V.viscoin_step.VisCoINTrainer(dev, amp=amp)  # fresh: no gradient accumulator may be bound to the default stream
+    zg = torch.Generator().manual_seed(1)
+    for it in range(8):
+        torch.cuda.synchronize()
+        w0 = time.perf_counter()
+        e0 = ev()
+        out = tr.step_graphed(real, labels, 1000, z_generator=zg)
+        e1 = ev()
+        torch.cuda.synchronize()
+        print("graphed step %d: total %.4f gpu %.2f ms wall %.2f ms" % (it, float(out["total"]), e0.elapsed_time(e1), (time.perf_counter() - w0) * 1e3), flush=True)
 print("max mem %.2f GB" % (torch.cuda.max_memory_allocated() / 2 ** 30))
 
 if os.environ.get("VCN_STEP_PROFILE", "0") == "1":
+    tr = V.viscoin_step.VisCoINTrainer(dev, amp=amp)
+    tr.step(real, labels)
     from torch.profiler import profile, ProfilerActivity
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         tr.step(real, labels)

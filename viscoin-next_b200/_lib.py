@@ -58,6 +58,8 @@ SIGNATURES = {
                                   _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_modconv_bwd_finish": (_i, [_vp, _c.POINTER(_i64 * 4), _vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _vp]),
     "vcn_modconv_bwd_finish_cl": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vcn_lpips_tap_fwd": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _vp]),
+    "vcn_lpips_tap_bwd": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "vcn_demod_grad": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
 }
 

@@ -113,8 +113,12 @@ struct TileGeom {
 
 // EPI: 0 = plain FIR (gain folded into the taps; nothing after the accumulation), 1 = fused scale / noise / bias with a
 // linear or lrelu activation (the synthesis layers), 2 = any activation (run-time dispatch).
-template <typename T, int UP, int DOWN, int PHX, int PHY, int EPI>
-__global__ void __launch_bounds__(256)
+// STG: 0 = halo tile staged by TMA / cp.async / plain loads into two buffers; 1 = fp32, one plane per tile, row pitch not
+// 16-byte aligned (the 2H+1 intermediate): the NEXT tile is prefetched into registers with coalesced 4-byte loads while
+// this one is filtered, then written to the single buffer - 2 instructions per element instead of ~14 for 4-byte
+// cp.async (address math + the LDGSTS issue sequence), which made the kernel issue-bound.
+template <typename T, int UP, int DOWN, int PHX, int PHY, int EPI, int STG>
+__global__ void __launch_bounds__(256, STG != 0 ? 3 : 1)
 upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_constant__ CUtensorMap tmap) {
   using S = typename Acc<T>::type;
   constexpr int V = Vec16<T>::N;   // elements per 16 bytes
@@ -153,6 +157,47 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
     return v;
   };
   constexpr int KMAX = 5;  // staged row pitch <= 160 elements on the cp.async path (host guarantees it)
+
+  // register path shapes: STG 1 = up to 40 rows x 160 columns (wide tiles), STG 2 = up to 72 rows x 96 columns (64-wide)
+  constexpr int RMAX = STG == 2 ? 9 : 5, RK = STG == 2 ? 3 : 5;
+  T pre[STG != 0 ? RMAX : 1][STG != 0 ? RK : 1];
+  auto fetch = [&](const TileIdx ti) {  // STG == 1: tile ti -> registers (tp == 1, blockDim == 256)
+    if constexpr (STG != 0) {
+      const int warp = tid >> 5, lane = tid & 31;
+      const int ix0 = ti.bx * g.tw * DOWN - a.padx0, iy0 = ti.by * g.th * DOWN - a.pady0;  // UP == 1
+      const T* __restrict__ base = static_cast<const T*>(a.x) + (int64_t)ti.bp * a.in_h * a.in_w;
+      const int gx0 = ix0 + lane;
+      uint32_t in_image = 0;
+#pragma unroll
+      for (int k = 0; k < RK; ++k) {
+        const int gx = gx0 + 32 * k;
+        if (lane + 32 * k < g.iwp && gx >= 0 && gx < a.in_w) in_image |= 1u << k;
+      }
+#pragma unroll
+      for (int j = 0; j < RMAX; ++j) {
+        const int gy = iy0 + warp + 8 * j;
+        const bool row_ok = warp + 8 * j < g.ih && gy >= 0 && gy < a.in_h;
+        const T* srow = base + (int64_t)gy * a.in_w + gx0;
+#pragma unroll
+        for (int k = 0; k < RK; ++k)
+          pre[j][k] = (row_ok && ((in_image >> k) & 1u)) ? __ldg(srow + 32 * k) : T(0);
+      }
+    }
+  };
+  auto stash = [&]() {  // registers -> the (single) shared buffer
+    if constexpr (STG != 0) {
+      const int warp = tid >> 5, lane = tid & 31;
+      T* tile = reinterpret_cast<T*>(smem_raw);
+#pragma unroll
+      for (int j = 0; j < RMAX; ++j) {
+        if (warp + 8 * j < g.ih) {
+#pragma unroll
+          for (int k = 0; k < RK; ++k)
+            if (lane + 32 * k < g.iwp) tile[(warp + 8 * j) * g.iwp + lane + 32 * k] = pre[j][k];
+        }
+      }
+    }
+  };
 
   auto issue = [&](const TileIdx ti, int b) {
     T* tile = reinterpret_cast<T*>(smem_raw + b * buf_bytes);
@@ -225,8 +270,14 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   }
   __syncthreads();
   TileIdx cur = decompose((int)blockIdx.x);
-  issue(cur, 0);
-  cp_async_commit();
+  if constexpr (STG != 0) {
+    fetch(cur);
+    stash();
+    __syncthreads();
+  } else {
+    issue(cur, 0);
+    cp_async_commit();
+  }
 
   S flt[kF][kF];
 #pragma unroll
@@ -240,13 +291,18 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   const int rx = t_x * MC, ry = t_y * kMR;
   int it = 0;
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-  const int b = it & 1;
+  const int b = STG != 0 ? 0 : (it & 1);
   const TileIdx nxt = advance(cur);
-  if (t + (int)gridDim.x < total_tiles) issue(nxt, b ^ 1);
-  cp_async_commit();
-  cp_async_wait_1();       // this thread's copies of tile t have landed ...
-  __syncthreads();         // ... and everybody else's
-  if (g.use_tma) mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
+  const bool has_next = t + (int)gridDim.x < total_tiles;
+  if constexpr (STG != 0) {
+    if (has_next) fetch(nxt);   // loads stay in flight while this tile is filtered
+  } else {
+    if (has_next) issue(nxt, b ^ 1);
+    cp_async_commit();
+    cp_async_wait_1();       // this thread's copies of tile t have landed ...
+    __syncthreads();         // ... and everybody else's
+    if (g.use_tma) mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
+  }
   const T* tile = reinterpret_cast<const T*>(smem_raw + b * buf_bytes);
   const int tile_ox = cur.bx * g.tw, tile_oy = cur.by * g.th;
   const int plane0 = cur.bp * g.tp;
@@ -337,6 +393,10 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   }
   }
   __syncthreads();  // buffer b is free for the tile after next
+  if constexpr (STG != 0) {
+    if (has_next) stash();
+    __syncthreads();
+  }
   }
 }
 
@@ -538,6 +598,7 @@ TileGeom make_geom(const UpfirdnArgs& a, int up, int down) {
 
 template <typename T, int UP, int DOWN, int PHX, int PHY, int EPI>
 int launch_tile_epi(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st) {
+  constexpr bool kCanReg = sizeof(T) == 4 && UP == 1;
   const size_t e = sizeof(T);
   const int planes = a.n * a.c;
   CUtensorMap tmap;
@@ -563,17 +624,35 @@ int launch_tile_epi(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st
   if (!g.use_tma && e == 4 && g.iwp > 160) { set_error("upfirdn2d: staged pitch %d exceeds the cp.async path", g.iwp); return VCN_ERR_UNSUPPORTED; }
   const size_t buf_bytes = ((size_t)g.tp * g.ih * g.iwp * e + 127) & ~(size_t)127;
   const size_t smem = 2 * buf_bytes + kF * kF * sizeof(float) + 16;
-  auto kern = upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY, EPI>;
-  if (smem > 48 * 1024) VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const bool reg_ok = kCanReg && !g.use_tma && g.tp == 1 && g.tx * g.ty == 256;
+  const int reg_path = !reg_ok ? 0 : (g.ih <= 40 && g.iwp <= 160) ? 1 : (g.ih <= 72 && g.iwp <= 96) ? 2 : 0;
   const int64_t tiles = (int64_t)g.tiles_x * g.tiles_y * g.tiles_p;
   if (tiles > 0x7fffffffLL) { set_error("upfirdn2d: too many tiles"); return VCN_ERR_INVALID; }
-  // persistent: as many CTAs as stay resident (at most 4 per SM; shared memory may allow fewer)
-  int per_sm = (int)((200 * 1024) / (smem + 1024));
-  if (per_sm > 4) per_sm = 4;
-  if (per_sm < 1) per_sm = 1;
-  int64_t grid = (int64_t)sm_count() * per_sm;
-  if (grid > tiles) grid = tiles;
-  kern<<<(unsigned)grid, g.tx * g.ty * g.tp, smem, st>>>(a, g, tmap);
+  if (reg_path) {
+    if constexpr (kCanReg) {
+      auto kern = reg_path == 1 ? upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY, EPI, 1> : upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY, EPI, 2>;
+      static int per_sm_cache[3] = {0, 0, 0};  // resident CTAs per SM of each instantiation (registers bound it)
+      int& per_sm = per_sm_cache[reg_path];
+      if (per_sm == 0) {
+        int nb = 0;
+        VCN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, 256, smem));
+        per_sm = nb < 1 ? 1 : nb;
+      }
+      int64_t grid = (int64_t)sm_count() * per_sm;
+      if (grid > tiles) grid = tiles;
+      kern<<<(unsigned)grid, 256, smem, st>>>(a, g, tmap);
+    }
+  } else {
+    auto kern = upfirdn2d_tile_kernel<T, UP, DOWN, PHX, PHY, EPI, 0>;
+    if (smem > 48 * 1024) VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // persistent: as many CTAs as stay resident (at most 4 per SM; shared memory may allow fewer)
+    int per_sm = (int)((200 * 1024) / (smem + 1024));
+    if (per_sm > 4) per_sm = 4;
+    if (per_sm < 1) per_sm = 1;
+    int64_t grid = (int64_t)sm_count() * per_sm;
+    if (grid > tiles) grid = tiles;
+    kern<<<(unsigned)grid, g.tx * g.ty * g.tp, smem, st>>>(a, g, tmap);
+  }
   VCN_LAUNCH_CHECK("upfirdn2d_tile_kernel");
   return VCN_OK;
 }

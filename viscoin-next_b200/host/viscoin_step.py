@@ -140,8 +140,14 @@ class VisCoINTrainer:
         # backward reaches the mapping network before Psi: register in forward order, buckets fill in reverse
         self.buckets = _dp.GradBuckets(main_params + gan_params)
         fused = (self.device.type == "cuda") if fused_adam is None else fused_adam
-        self.gan_optimizer = torch.optim.Adam(gan_params, lr=self.p.learning_rate, fused=fused)
-        self.optimizer = torch.optim.Adam(main_params, lr=self.p.learning_rate, fused=fused)
+        # capturable: step counters and lr live on the device, so the update can sit inside a CUDA graph (step_graphed)
+        cap = fused and self.device.type == "cuda"
+        lr = torch.tensor(self.p.learning_rate, device=self.device) if cap else self.p.learning_rate
+        self.gan_optimizer = torch.optim.Adam(gan_params, lr=lr, fused=fused, capturable=cap)
+        self.optimizer = torch.optim.Adam(main_params, lr=lr, fused=fused, capturable=cap)
+        self._graphs = {}
+        self.graph_launches = 0  # libvcn kernel launches replayed from graphs so far
+        self._eager_calls = 0
 
     def trainable_numel(self):
         return self.buckets.numel()
@@ -183,6 +189,53 @@ class VisCoINTrainer:
             losses["rec"] = reconstruction_loss(rebuilt_images, all_images, rebuilt_classes, classes, lp, p.gamma, p.beta)
         losses["gan"] = gan_regularization_loss(gan_latents, self.viscoin_gan)
         return losses
+
+    def step_graphed(self, real_images, labels, i=1000, z_generator=None, warm=2):
+        """step() replayed from ONE CUDA graph: the ~2500 kernel launches of an iteration (library networks, the sm_100a
+        synthesis kernels with their tensor maps as kernel parameters, both Adam updates, the bucket memsets and - under
+        torch.distributed - the NCCL all-reduces) are captured once per (batch size, i > cd_fid_iteration) and then cost
+        one host call.  The first `warm` calls run eagerly (they fill the weight-pack caches and the allocator); z is
+        drawn on the host every call like utils.py:37 and copied into the graph's static input."""
+        n = len(real_images)
+        key = (n, i > self.p.cd_fid_iteration)
+        z = torch.randn(n, self.generator_gan.z_dim, generator=z_generator)
+        if self._eager_calls < warm and key not in self._graphs:
+            # eager warm-up on a SIDE stream: autograd binds each parameter's gradient accumulator to the stream it first
+            # runs on, and the legacy default stream cannot take part in a capture
+            self._eager_calls += 1
+            if not hasattr(self, "_side"):
+                self._side = torch.cuda.Stream(device=self.device)
+            cur = torch.cuda.current_stream(self.device)
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):
+                with torch.no_grad():
+                    fake = self.generator_gan(z.to(self.device), None)
+                out = self.step(real_images.to(self.device, copy=True), labels.to(self.device, copy=True), i, fake_images=fake)
+            cur.wait_stream(self._side)
+            return out
+        if key not in self._graphs:
+            from .. import _lib
+            st = {"real": torch.empty(real_images.shape, dtype=real_images.dtype, device=self.device),
+                  "labels": torch.empty(labels.shape, dtype=labels.dtype, device=self.device),
+                  "z": torch.empty(n, self.generator_gan.z_dim, device=self.device)}
+            st["real"].copy_(real_images); st["labels"].copy_(labels); st["z"].copy_(z)
+            torch.cuda.synchronize(self.device)
+            count0 = _lib.load().vcn_launch_count()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                with torch.no_grad():
+                    fake = self.generator_gan(st["z"], None)
+                st["out"] = self.step(st["real"], st["labels"], i, fake_images=fake)
+            st["graph"] = graph
+            st["launches"] = int(_lib.load().vcn_launch_count() - count0)  # libvcn kernels per replay
+            self._graphs[key] = st
+        st = self._graphs[key]
+        st["real"].copy_(real_images, non_blocking=True)
+        st["labels"].copy_(labels, non_blocking=True)
+        st["z"].copy_(z, non_blocking=True)
+        st["graph"].replay()
+        self.graph_launches += st["launches"]
+        return st["out"]
 
     def step(self, real_images, labels, i=1000, fake_images=None, z_generator=None):
         """One iteration (gradient_accumulation = 1).  Returns the dict of detached loss terms + 'total'."""
