@@ -109,7 +109,7 @@ def dist_setup(args):
         backend = "nccl" if torch.cuda.is_available() and args.impl == "ours" else "gloo"
         if torch.cuda.is_available():
             torch.cuda.set_device(local)
-        dist.init_process_group(backend=backend)
+        dist.init_process_group(backend=backend, device_id=torch.device("cuda", local) if backend == "nccl" else None)
     return world, rank, local
 
 
@@ -568,8 +568,13 @@ def main():
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
-        import torch.distributed as dist
-        dist.destroy_process_group()
+        # CUDA graphs that captured NCCL collectives keep the communicator busy: tearing the process group down under them
+        # can hang.  Everything is printed and synchronised: leave without the teardown.
+        sys.stdout.flush()
+        sys.stderr.flush()
+        torch.cuda.synchronize()
+        barrier(world)
+        os._exit(0)
 
 
 if __name__ == "__main__":

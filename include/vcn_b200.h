@@ -161,6 +161,14 @@ int vcn_modconv_bwd_finish(float* dxhat, const int64_t ds[4], const void* x, int
  * vcn_modconv_bwd_pack takes the same route on its own when dy / y are 16-bit with channel stride 1. */
 int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, const int64_t xs[4], const float* styles,
                               float* dsum, int n, int c, int c_pad, int h, int w, void* stream);
+/* Weight gradient of the convolution under modulated_conv2d (the ATen/cuDNN wgrad reached from conv2d_gradfix.py:38,43):
+ *   kind 0: dw[co][ci][ky][kx] += sum_{n,p} dy0[n,p,co] * xhat[n, p + (ky-kh/2, kx-kw/2), ci]          (VCN_CONV_FPROP)
+ *   kind 1: dw[co][ci][ky][kx] += sum_{n,i,j} dy0[n, 2i+ky, 2j+kx, co] * xhat[n,i,j,ci]               (VCN_CONV_TCONV2)
+ * dy0 bf16 NHWC [n,dy_h,dy_w,cout_pad], xhat bf16 NHWC [n,h,w,cin_pad] (the operands of the forward / input-gradient
+ * GEMMs, as they are); dw fp32 [cout,cin,kh,kw], ACCUMULATED (zero it first).  tcgen05 GEMM with both operands MN-major,
+ * split over pixels across CTAs. */
+int vcn_conv_wgrad(const void* dy0, const void* xhat, float* dw, int kind, int n, int h, int w, int cin_pad, int cin,
+                   int cout_pad, int cout, int kh, int kw, int dy_h, int dy_w, void* stream);
 int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const float* dcoef, const float* wsq,
                    int n, int cin, int cout, void* stream);
 

@@ -178,8 +178,8 @@ def test_errors():
         M.modulated_conv2d(x.cuda(), torch.zeros(8, 8, 3, 3).cuda(), torch.ones(1, 8).cuda(), down=2, padding=1)
     w = torch.zeros(8, 8, 3, 3, device="cuda", requires_grad=True)
     y = M.modulated_conv2d(x.cuda(), w, torch.ones(1, 8, device="cuda"), padding=1)
-    with pytest.raises(_lib.VcnError):
-        y.sum().backward()  # weight gradient: not implemented, must fail loudly
+    y.sum().backward()  # weight gradient (vcn_conv_wgrad): x = 0 gives exactly 0
+    assert w.grad is not None and float(w.grad.abs().max()) == 0.0
 
 
 RESIDENT_CASES = [
@@ -245,3 +245,50 @@ def test_resident_bf16_channels_last_layer_vs_oracle(case):
         grads_ref = torch.autograd.grad(y_ref, want, dy)
     for gname, a, r in zip(("dx", "ds", "db"), grads, grads_ref):
         assert _rel(a, r) <= TOL_RES_GRAD, (gname, _rel(a, r))
+
+
+WGRAD_CASES = [
+    # n, cin, cout, res, k, up, demod, resident
+    (2, 64, 64, 16, 3, 1, True, False),
+    (3, 128, 64, 8, 3, 2, True, False),
+    (2, 64, 3, 32, 1, 1, False, False),        # ToRGB
+    (2, 96, 40, 12, 3, 1, True, True),
+    (1, 72, 136, 9, 3, 2, True, True),
+    (4, 512, 512, 4, 3, 1, True, True),        # b4.conv1: 2 co tiles, 2 ci tiles
+    (2, 256, 128, 32, 3, 2, False, True),
+    (2, 320, 200, 20, 3, 1, True, False),      # ragged channel tiles, pixel boxes overhanging the image
+]
+
+
+@pytest.mark.parametrize("case", WGRAD_CASES, ids=[str(c) for c in WGRAD_CASES])
+def test_weight_gradient_vs_oracle(case):
+    """dL/dW of modulated_conv2d (config 3 of SURVEY 8(d): Generator training) on the MN-major tcgen05 wgrad GEMM, including
+    the path through the demodulation coefficients, against autograd of the fp32 oracle.  bf16 operands: <= 2e-2."""
+    M = _M()
+    n, cin, cout, res, k, up, demod, resident = case
+    g = torch.Generator().manual_seed(31 + sum(int(v) for v in case))
+    x = torch.randn(n, cin, res, res, generator=g).bfloat16().float()
+    w = torch.randn(cout, cin, k, k, generator=g).requires_grad_(True)
+    s = torch.randn(n, cin, generator=g) * 0.5 + 1
+    ro = res * up
+    noise = torch.randn(n, 1, ro, ro, generator=g) * 0.4
+    f4 = R.setup_filter([1, 3, 3, 1])
+    sm = s * (1 / math.sqrt(cin)) if not demod else s
+    y_ref = R.modulated_conv2d(x, w, sm, noise=noise, up=up, padding=k // 2, resample_filter=f4, demodulate=demod,
+                               flip_weight=(up == 1), fused_modconv=False)
+    dy = torch.randn(y_ref.shape, generator=g).bfloat16().float()
+    (dw_ref,) = torch.autograd.grad(y_ref, [w], dy)
+
+    xc = x.cuda()
+    if resident:
+        xc = xc.bfloat16().contiguous(memory_format=torch.channels_last)
+    wc = w.detach().cuda().requires_grad_(True)
+    y = M.modulated_conv2d(xc, wc, sm.cuda(), noise=noise.cuda(), up=up, padding=k // 2, resample_filter=f4.cuda(),
+                           demodulate=demod, flip_weight=(up == 1))
+    dyc = dy.cuda().to(y.dtype)
+    if y.stride(1) == 1:
+        dyc = dyc.contiguous(memory_format=torch.channels_last)
+    (dw,) = torch.autograd.grad(y, [wc], dyc)
+    assert dw.shape == w.shape and dw.dtype == torch.float32
+    e = _rel(dw, dw_ref)
+    assert e <= TOL_GRAD, e

@@ -60,6 +60,7 @@ SIGNATURES = {
     "vcn_modconv_bwd_finish_cl": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_lpips_tap_fwd": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _vp]),
     "vcn_lpips_tap_bwd": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    "vcn_conv_wgrad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "vcn_demod_grad": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
 }
 

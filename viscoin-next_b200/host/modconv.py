@@ -212,6 +212,22 @@ def bwd_finish_cl(dxhat, x, styles, want_dsum):
     return dsum
 
 
+def conv_wgrad(dy0, xhat, cout, cin, kh, kw, transposed=False):
+    """vcn_conv_wgrad: dy0 bf16 NHWC [N,OH,OW,Cout_pad], xhat bf16 NHWC [N,H,W,Cin_pad] -> dW fp32 [cout,cin,kh,kw]."""
+    lib = _lib.load()
+    n, h, w, cin_pad = xhat.shape
+    _, oh, ow, cout_pad = dy0.shape
+    assert dy0.dtype == torch.bfloat16 and xhat.dtype == torch.bfloat16 and dy0.is_contiguous() and xhat.is_contiguous()
+    dw = torch.zeros([cout, cin, kh, kw], dtype=torch.float32, device=xhat.device)
+    if n == 0:
+        return dw
+    with torch.cuda.device(xhat.device):
+        st = lib.vcn_conv_wgrad(_lib.ptr(dy0), _lib.ptr(xhat), _lib.ptr(dw), 1 if transposed else 0, n, h, w, cin_pad, cin,
+                                cout_pad, cout, kh, kw, oh, ow, _lib.current_stream(xhat.device))
+    _lib.check(st, "vcn_conv_wgrad")
+    return dw
+
+
 def demod_grad(ds, styles, gsum, dcoef, wsq):
     lib = _lib.load()
     n, cin = ds.shape
@@ -304,9 +320,6 @@ class _ModConvLayer(torch.autograd.Function):
         x, weight, styles32, noise, bias, resample_filter, d, wsq, y = ctx.saved_tensors
         up, demodulate, flip_weight, act, alpha, gain, clamp = ctx.cfg
         need_x, need_w, need_s, need_noise, need_b = ctx.needs_input_grad[:5]
-        if need_w:
-            raise _lib.VcnError("modulated_conv2d(impl='cuda'): the weight gradient is not implemented yet (VisCoIN "
-                                "freezes the synthesis weights, viscoin/training/viscoin.py:116)")
         n, cin, h, w = x.shape
         cout, _, kh, kw = weight.shape
         resident = ctx.resident
@@ -317,9 +330,16 @@ class _ModConvLayer(torch.autograd.Function):
         elif not dy.is_contiguous():
             dy = dy.contiguous()
         epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
-        want_g = demodulate and need_s
+        want_g = demodulate and (need_s or need_w)
         dy0, gsum, db = bwd_pack(dy, y if (act is not None or want_g) else None, epi, want_g, need_b and bias is not None)
-        dx = ds = dnoise = None
+        dx = ds = dnoise = dw = None
+        dz = None
+        if up == 2 and (need_x or need_s or need_w):
+            f = resample_filter.to(device=x.device, dtype=torch.float32)
+            # FIR^T: same op, flipped filter, padding fw-1-p = 2 (upfirdn2d.py:246-261); channels_last view of dy0
+            dz = _upfirdn2d.launch(dy0.permute(0, 3, 1, 2), f, 1, 1, 1, 1, 2, 2, 2, 2, True, 4.0)
+            dz = dz.permute(0, 2, 3, 1)
+            assert dz.is_contiguous()
         if need_x or need_s:
             if up == 1:
                 wt_t, _ = _packed(weight, True, False, False)
@@ -328,11 +348,6 @@ class _ModConvLayer(torch.autograd.Function):
                                    channels_last=resident)
             else:
                 wt_t, _ = _packed(weight, True, bool(flip_weight), False)
-                f = resample_filter.to(device=x.device, dtype=torch.float32)
-                # FIR^T: same op, flipped filter, padding fw-1-p = 2 (upfirdn2d.py:246-261); channels_last view of dy0
-                dz = _upfirdn2d.launch(dy0.permute(0, 3, 1, 2), f, 1, 1, 1, 1, 2, 2, 2, 2, True, 4.0)
-                dz = dz.permute(0, 2, 3, 1)
-                assert dz.is_contiguous()
                 dxhat = conv_igemm(dz, wt_t, _lib.CONV_SCONV2, cin, 3, 3, out_dtype=torch.bfloat16 if resident else torch.float32,
                                    channels_last=resident)
             if resident:
@@ -340,11 +355,27 @@ class _ModConvLayer(torch.autograd.Function):
             else:
                 ds1 = bwd_finish(dxhat, x, styles32, need_s and styles32 is not None)
             if need_x:
-                dx = dxhat if x.dtype == torch.float32 else dxhat.to(x.dtype)
+                dx = dxhat if x.dtype == dxhat.dtype else dxhat.to(x.dtype)
             if need_s and styles32 is not None:
                 ds = ds1
                 if demodulate:
                     ds = demod_grad(ds, styles32, gsum, d, wsq)
+        if need_w:
+            # dW = sum_n,p dy0 (x) xhat on the tensor cores (both operands as the other GEMMs use them), plus the path
+            # through the demodulation coefficients: d = rsqrt(sum (s W)^2) gives  -W * sum_n gsum d^2 s^2
+            xhat = modulate_pack(x, styles32)
+            if up == 1:
+                dw = conv_wgrad(dy0, xhat, cout, cin, kh, kw)
+                if not flip_weight:
+                    dw = dw.flip([2, 3])
+            else:
+                dw = conv_wgrad(dz, xhat, cout, cin, 3, 3, transposed=True)
+                if flip_weight:
+                    dw = dw.flip([2, 3])
+            if demodulate:
+                e = (gsum * d * d).t() @ styles32.square()
+                dw = dw - weight.detach().float() * e.reshape(cout, cin, 1, 1)
+            dw = dw.to(weight.dtype)
         if need_noise and noise is not None:
             # rare path (noise buffers are constants / fresh randn in the reference): dz summed over channels
             if act is not None:
@@ -357,7 +388,7 @@ class _ModConvLayer(torch.autograd.Function):
                 dnoise = dnoise.sum(dim=0).reshape(noise.shape)
             dnoise = dnoise.to(noise.dtype)
         del hold
-        return dx, None, ds, dnoise, (db.to(bias.dtype) if db is not None else None), None, None
+        return dx, dw, ds, dnoise, (db.to(bias.dtype) if db is not None else None), None, None
 
 
 def _check_cuda(x, what):
