@@ -301,31 +301,34 @@ class Synthesis:
             self.himg.copy_(img, non_blocking=True)
 
     def roofline(self, device, peaks, iters=20):
-        """conv_igemm on the heaviest layer shape b256.conv1: [N,128,256,256] x [128,128,3,3], 2*N*Cout*Cin*9*H*W FLOP."""
+        """conv_igemm on the heaviest layer shape b256.conv1 as the pipelines run it: [N,128,256,256] x [128,128,3,3], bf16 NHWC
+        in, bf16 NHWC out, fused lrelu epilogue; 2*N*Cout*Cin*9*H*W FLOP."""
         M = self.V.modconv
         n, c, r = self.n, 128, self.RES
         x = torch.randn(n, c, r, r, device=device)
         w = torch.randn(c, c, 3, 3, device=device)
         xh = M.modulate_pack(x, None)
         wt, _ = M.pack_weights(w)
-        out = torch.empty(n, c, r, r, device=device)
+        out = torch.empty(n, c, r, r, device=device, dtype=torch.bfloat16, memory_format=torch.channels_last)
+        bias = torch.zeros(c, device=device)
+        epi, hold = M.make_epilogue(bias=bias, act="lrelu")
         from viscoin_next_b200 import _lib
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
         for _ in range(3):
-            M.conv_igemm(xh, wt, _lib.CONV_FPROP, c, 3, 3, out=out)
+            M.conv_igemm(xh, wt, _lib.CONV_FPROP, c, 3, 3, out=out, epilogue=epi)
         times = []
         for _ in range(iters):
             flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            M.conv_igemm(xh, wt, _lib.CONV_FPROP, c, 3, 3, out=out)
+            M.conv_igemm(xh, wt, _lib.CONV_FPROP, c, 3, 3, out=out, epilogue=epi)
             e1.record()
             e1.synchronize()
             times.append(e0.elapsed_time(e1))
         ms = sum(times) / len(times)
         flop = 2.0 * n * c * c * 9 * r * r
         ach = flop / (ms * 1e-3) / 1e12
-        return {"kernel": "conv_igemm_kernel FPROP [%d,128,256,256]x[128,128,3,3] bf16->f32" % n, "bound": "tensor",
+        return {"kernel": "conv_igemm_kernel FPROP [%d,128,256,256]x[128,128,3,3] bf16 NHWC -> bf16 NHWC" % n, "bound": "tensor",
                 "achieved": round(ach, 1), "peak": peaks["bf16"], "unit": "TFLOP/s", "frac": round(ach / peaks["bf16"], 4),
                 "peak_source": peaks["src"] + " (burst cuBLAS bf16)", "traffic": None, "alg_flop_per_launch": flop,
                 "avg_launch_ms": round(ms, 5)}

@@ -25,7 +25,8 @@ def _compare(beta, gamma):
         dev = torch.device("cuda:0")
         params = V.viscoin_step.VisCoINParams()
         params.beta, params.gamma = beta, gamma
-        tr = V.viscoin_step.VisCoINTrainer(dev, seed=11, amp=None, channels_last=False, deterministic=True, params=params)
+        tr = V.viscoin_step.VisCoINTrainer(dev, seed=11, amp=None, channels_last=False, deterministic=True, params=params,
+                                           fold_bn=False)  # the oracle loads the unfolded HF state_dict
         tr.synthesis_kwargs = {"noise_mode": "const"}
         with torch.no_grad():
             for name, p in tr.viscoin_gan.synthesis.named_parameters():

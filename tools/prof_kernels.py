@@ -80,3 +80,17 @@ if "bias" in what:
     x = torch.randn(8, 128, 256, 256, device=dev)
     b = torch.randn(128, device=dev)
     timed("bias_act lrelu fwd f32 [8,128,256,256]", lambda: V.bias_act.bias_act(x, b, act="lrelu"), 2 * x.numel() * 4, "GB/s")
+
+if "bwdcl" in what:
+    n, c, r = 16, 128, 256
+    y = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    d = torch.rand(n, c, device=dev) + 0.5
+    b = torch.randn(c, device=dev)
+    epi, hold = M.make_epilogue(scale=d, bias=b, act="lrelu", clamp=256.0)
+    timed("bwd_pack_cl bf16 [16,128,256,256]", lambda: M.bwd_pack(dy, y, epi, True, True), 3 * y.numel() * 2, "GB/s")
+    s = torch.rand(n, c, device=dev) + 0.5
+    dxh = dy.clone()
+    timed("bwd_finish_cl bf16 [16,128,256,256]", lambda: M.bwd_finish_cl(dxh, y, s, True), 3 * y.numel() * 2, "GB/s")
+    x32 = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    timed("modulate_pack_cl bf16 [16,128,256,256]", lambda: M.modulate_pack(x32, s), 2 * y.numel() * 2, "GB/s")

@@ -260,17 +260,28 @@ __global__ void __launch_bounds__(256) modconv_bwd_finish_kernel(float* __restri
 }
 
 // ds[n,i] += s[n,i] * sum_o (-gsum[n,o] * d[n,o]^2) * wsq[o,i]
-__global__ void __launch_bounds__(128) demod_grad_kernel(float* __restrict__ ds, const float* __restrict__ styles,
+// block = 32 input channels x 8 slices of the output-channel sum (wsq rows are read coalesced), reduced through smem.
+__global__ void __launch_bounds__(256) demod_grad_kernel(float* __restrict__ ds, const float* __restrict__ styles,
                                                          const float* __restrict__ gsum, const float* __restrict__ dcoef,
                                                          const float* __restrict__ wsq, int n, int cin, int cout) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, in = blockIdx.y;
-  if (i >= cin) return;
+  __shared__ float red[8][33];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + lane, in = blockIdx.y;
   float acc = 0.f;
-  for (int o = 0; o < cout; ++o) {
-    const float d = dcoef[(int64_t)in * cout + o];
-    acc = fmaf(-gsum[(int64_t)in * cout + o] * d * d, wsq[(int64_t)o * cin + i], acc);
+  if (i < cin) {
+    for (int o = slice; o < cout; o += 8) {
+      const float d = dcoef[(int64_t)in * cout + o];
+      acc = fmaf(-gsum[(int64_t)in * cout + o] * d * d, wsq[(int64_t)o * cin + i], acc);
+    }
   }
-  ds[(int64_t)in * cin + i] += styles[(int64_t)in * cin + i] * acc;
+  red[slice][lane] = acc;
+  __syncthreads();
+  if (slice == 0 && i < cin) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += red[k][lane];
+    ds[(int64_t)in * cin + i] += styles[(int64_t)in * cin + i] * t;
+  }
 }
 
 
@@ -474,8 +485,8 @@ int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const floa
   VCN_REQUIRE(n >= 0 && cin >= 1 && cout >= 1, "demod_grad: bad shape");
   if (n == 0) return VCN_OK;
   VCN_REQUIRE(ds && styles && gsum && dcoef && wsq, "demod_grad: NULL pointer");
-  dim3 grid((unsigned)((cin + 127) / 128), (unsigned)n);
-  demod_grad_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(ds, styles, gsum, dcoef, wsq, n, cin, cout);
+  dim3 grid((unsigned)((cin + 31) / 32), (unsigned)n);
+  demod_grad_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(ds, styles, gsum, dcoef, wsq, n, cin, cout);
   VCN_LAUNCH_CHECK("demod_grad_kernel");
   return VCN_OK;
 }

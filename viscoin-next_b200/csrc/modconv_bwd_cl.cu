@@ -24,7 +24,7 @@ struct BwdClArgs {
   __nv_bfloat16* out;                  // pack: dy0 [n,h,w,c_pad]
   float* sum_nc; float* sum_c;         // pack: gsum, db.  finish: dsum, unused
   int n, c, c_pad, h, w, chunk;
-  int act; float alpha, gain, clamp;
+  int act; float alpha, gain, clamp, inv_gain, inv_alpha;
 };
 
 __device__ __forceinline__ bool aligned16_dev(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -109,11 +109,11 @@ __global__ void __launch_bounds__(256) modconv_bwd_cl_kernel(const BwdClArgs a) 
         for (int k = 0; k < 8; ++k) {
           float dz = u[k], r = v[k];
           if (a.act) {  // first derivative of bias_act keyed on the stored output (bias_act.cu:48,72,141)
-            const float yy = v[k] / a.gain;
+            const float yy = v[k] * a.inv_gain;
             const bool neg = a.act == VCN_ACT_LRELU && !(yy > 0.f);
             dz = (neg ? u[k] * a.alpha : u[k]) * a.gain;
             if (a.clamp >= 0.f && !(v[k] > -a.clamp && v[k] < a.clamp)) dz = 0.f;
-            r = (neg ? yy / a.alpha : yy) - bi[k];
+            r = (neg ? yy * a.inv_alpha : yy) - bi[k];
           }
           r -= nz;
           acc0[k] = fmaf(dz, r, acc0[k]);
@@ -163,6 +163,7 @@ int bwd_pack_cl_try(const void* dy, const void* y, int dtype, const int64_t dys[
   a.out = static_cast<__nv_bfloat16*>(dy0); a.sum_nc = gsum; a.sum_c = db;
   a.n = n; a.c = c; a.c_pad = c_pad; a.h = h; a.w = w;
   a.act = act; a.alpha = alpha; a.gain = gain; a.clamp = clamp;
+  a.inv_gain = gain != 0.f ? 1.f / gain : 0.f; a.inv_alpha = alpha != 0.f ? 1.f / alpha : 0.f;
   return launch<false>(a, dtype, st, "modconv_bwd_pack_cl_kernel");
 }
 

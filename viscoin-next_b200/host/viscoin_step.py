@@ -93,7 +93,7 @@ class VisCoINTrainer:
          operands with fp32 accumulation)."""
 
     def __init__(self, device, n_classes=200, seed=0, amp=torch.bfloat16, channels_last=True, params=None, models=None,
-                 deterministic=False, fused_adam=None):
+                 deterministic=False, fused_adam=None, fold_bn=True):
         self.device = torch.device(device)
         self.p = params or VisCoINParams()
         self.amp = amp if self.device.type == "cuda" else None
@@ -119,6 +119,7 @@ class VisCoINTrainer:
         self.viscoin_gan = viscoin_gan.to(self.device)
         self.generator_gan = generator_gan.to(self.device)
         self.lpips = lpips.to(self.device)
+        self.fold_bn = fold_bn
         if self.channels_last:
             for m in (self.classifier, self.lpips):  # frozen nets only: trainable grads are views into flat buckets
                 m.to(memory_format=torch.channels_last)
@@ -129,6 +130,10 @@ class VisCoINTrainer:
                 fakes = synthetic_samples(self.generator_gan, 4, self.device, torch.Generator().manual_seed(seed)).float()
             noise = torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(seed + 1)).to(self.device)
             _models.calibrate_batchnorm(self.classifier, torch.cat([noise, fakes]))
+        if self.fold_bn:  # f is frozen and in eval mode: conv + BN is one convolution
+            _models.fold_batchnorm(self.classifier)
+            if self.channels_last:
+                self.classifier.to(memory_format=torch.channels_last)
         self.deterministic = deterministic
         self.viscoin_gan.synthesis.resident_bf16 = self.amp is not None  # bf16 run: activations stay bf16 NHWC
         self.synthesis_kwargs = {}  # e.g. {'noise_mode': 'const'} for parity runs; the reference passes none (:193)
