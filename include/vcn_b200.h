@@ -45,6 +45,10 @@ int vcn_abi_version(void);
 const char* vcn_last_error(void);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 uint64_t vcn_launch_count(void);
+/* Profiling aid: with VCN_CONV_PROFILE=1 in the environment vcn_conv_igemm accumulates per-role cycle counters
+ * ([0] epilogue busy, [1] epilogue waiting, [2] MMA waiting for an accumulator, [3] MMA waiting for operands,
+ * [4] tiles, [5] TMA producer waiting for a stage, [6] k-blocks); synchronises the device. */
+int vcn_conv_profile_counters(uint64_t out[8], int reset);
 /* 0 iff `device` exists and is compute capability 10.x; fills sm count / L2 bytes when non-NULL. */
 int vcn_device_info(int device, int* sm_count, int64_t* l2_bytes, int* cc_major, int* cc_minor);
 

@@ -191,6 +191,11 @@ RESIDENT_CASES = [
     (2, 256, 128, 32, 3, 2, True, "rand", "lrelu"),
     (4, 512, 512, 4, 3, 1, True, "const", "lrelu"),
     (2, 96, 40, 12, 3, 1, True, "rand", None),
+    # 65..128 out channels with >= 256 pixels per sample: the swapped-operand GEMM (M = channels, N = 256 pixels)
+    (2, 128, 128, 32, 3, 1, True, "rand", "lrelu"),    # forward and input-gradient GEMM both swapped
+    (1, 96, 72, 24, 3, 1, True, "const", "lrelu"),     # partial channel tile, ragged pixel tiles
+    (2, 128, 96, 20, 3, 2, True, "rand", "lrelu"),     # transposed conv (4 phases) / stride-2 gather backward
+    (2, 80, 128, 17, 1, 1, False, None, "linear"),     # 1x1
 ]
 TOL_RES_FWD, TOL_RES_GRAD = 1.5e-2, 3e-2  # + one bf16 rounding (2^-9) of the stored output / input gradient
 

@@ -18,9 +18,21 @@ dev = "cuda"
 f4 = V.upfirdn2d.setup_filter([1, 3, 3, 1], device=dev)
 
 
+PROF = os.environ.get("VCN_CONV_PROFILE") == "1"  # per-role cycle counters of conv_igemm (see include/vcn_b200.h)
+
+
+def conv_counters(reset):
+    import ctypes
+    out = (ctypes.c_uint64 * 8)()
+    _lib.load().vcn_conv_profile_counters(out, int(reset))
+    return list(out)
+
+
 def timed(name, fn, work, unit):
     fn()
     torch.cuda.synchronize()
+    if PROF:
+        conv_counters(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
@@ -29,6 +41,12 @@ def timed(name, fn, work, unit):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
     print("%-46s %.4f ms  %.1f %s" % (name, ms, work / ms / 1e9 * (1e3 if unit == "GB/s" else 1), unit), flush=True)
+    if PROF and name.startswith("conv"):
+        c = conv_counters(True)
+        t = max(c[4], 1)
+        print("    per tile [cycles]: epilogue busy %.0f, epilogue waits %.0f | MMA waits: accumulator %.0f, operands %.0f | "
+              "producer waits %.0f | tiles/launch %.0f, k-blocks/tile %.1f" %
+              (c[0] / t, c[1] / t, c[2] / t, c[3] / t, c[5] / t, t / iters, c[6] / t), flush=True)
 
 
 if "conv" in what:

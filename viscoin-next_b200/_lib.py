@@ -44,6 +44,7 @@ SIGNATURES = {
     "vcn_abi_version": (_i, []),
     "vcn_last_error": (_c.c_char_p, []),
     "vcn_launch_count": (_c.c_uint64, []),
+    "vcn_conv_profile_counters": (_c.c_int, [_c.POINTER(_c.c_uint64), _c.c_int]),
     "vcn_device_info": (_i, [_i, _c.POINTER(_i), _c.POINTER(_i64), _c.POINTER(_i), _c.POINTER(_i)]),
     "vcn_bias_act_workspace": (_sz, [_i, _i64, _i64, _i64]),
     "vcn_bias_act": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _f, _f, _i64, _i64, _i64, _vp]),

@@ -14,6 +14,7 @@
 // A "plan" lists the taps; taps are partitioned into up to 4 accumulator groups (TMEM column ranges): the plain
 // convolution has one group of kh*kw taps, the stride-2 transposed convolution has its 4 output phases as groups
 // (4+2+2+1 taps) so that it costs exactly the reference's FLOPs (2*9*Cin*Cout per INPUT pixel).
+#include <stdlib.h>
 #include <string.h>
 
 #include "act_math.cuh"
@@ -47,6 +48,14 @@ struct IgemmArgs {
   int n, cout, out_h, out_w;
   int tw, th, tn, tiles_w, tiles_h, tiles_m, tiles_total;
   int n_tile, kblocks_c, stages, tmem_cols;
+  int swap;            // 1: operands swapped - UMMA M = 128 out-channels (weights), N = 256 pixels (see header)
+  int log_tw, log_th;  // swap: tile extents are powers of two
+  uint32_t pix_bytes, w_bytes;  // bytes of the pixel / weight operand in one pipeline stage
+  // staged output (16-bit channels-fastest y): the epilogue writes a 128B-swizzled [pixel][64 ch] tile per 64-channel
+  // block into shared memory and ONE thread hands it to TMA (full-line writes, bounds clipped by the tensor map)
+  int stage_out, out_blocks;
+  int prof;
+  uint32_t stage_bytes_out, stage_blk_bytes;
   int w_per_sample;
   void* y;
   int y_dtype;
@@ -70,7 +79,8 @@ template <> __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(floa
 template <typename T, int ACT>
 __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_t (&acc)[32], T* __restrict__ ybase,
                                                int co0, int co_end, float noise, const float* __restrict__ s_scale,
-                                               const float* __restrict__ s_bias, bool has_scale) {
+                                               const float* __restrict__ s_bias, bool has_scale,
+                                               unsigned char* __restrict__ stg_row, int stg_xor, int c_tile) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
@@ -83,7 +93,19 @@ __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_
     }
     v[j] = r;
   }
-  if (a.vec_store && co0 + 32 <= co_end) {
+  if (stg_row != nullptr) {
+    if constexpr (sizeof(T) == 2) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        Vec16<T> o;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o.v[k] = cvt_out<T>(v[j + k]);
+        const int ch = c_tile + j;  // channel offset inside the tile: block ch / 64, 16-byte chunk (ch % 64) / 8
+        *reinterpret_cast<Vec16<T>*>(stg_row + (size_t)(ch >> 6) * a.stage_blk_bytes +
+                                     ((uint32_t)(((ch & 63) >> 3) ^ stg_xor) << 4)) = o;
+      }
+    }
+  } else if (a.vec_store && co0 + 32 <= co_end) {
     constexpr int V = 16 / sizeof(T);
 #pragma unroll
     for (int j = 0; j < 32; j += V) {
@@ -103,12 +125,21 @@ __device__ __forceinline__ void epilogue_store(const IgemmArgs& a, const uint32_
 template <typename T>
 __device__ __forceinline__ void epilogue_dispatch(const IgemmArgs& a, const uint32_t (&acc)[32], T* ybase, int co0,
                                                   int co_end, float noise, const float* s_scale, const float* s_bias,
-                                                  bool has_scale) {
-  if (a.act == 0) epilogue_store<T, -1>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
-  else if (a.act == VCN_ACT_LRELU) epilogue_store<T, VCN_ACT_LRELU>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
-  else if (a.act == VCN_ACT_LINEAR) epilogue_store<T, VCN_ACT_LINEAR>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
-  else epilogue_store<T, 0>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale);
+                                                  bool has_scale, unsigned char* stg_row, int stg_xor, int c_tile) {
+  if (a.act == 0) epilogue_store<T, -1>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale, stg_row, stg_xor, c_tile);
+  else if (a.act == VCN_ACT_LRELU) epilogue_store<T, VCN_ACT_LRELU>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale, stg_row, stg_xor, c_tile);
+  else if (a.act == VCN_ACT_LINEAR) epilogue_store<T, VCN_ACT_LINEAR>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale, stg_row, stg_xor, c_tile);
+  else epilogue_store<T, 0>(a, acc, ybase, co0, co_end, noise, s_scale, s_bias, has_scale, stg_row, stg_xor, c_tile);
 }
+
+// Profiling aid (VCN_CONV_PROFILE=1): cycle counters summed over CTAs, read back with vcn_conv_profile_counters().
+//  [0] epilogue busy  [1] epilogue waiting for an accumulator  [2] MMA warp waiting for a drained accumulator
+//  [3] MMA warp waiting for operands  [4] tiles  [5] TMA producer waiting for a free stage  [6] k-blocks
+__device__ unsigned long long g_conv_prof[8];
+
+struct alignas(64) OutMaps {
+  CUtensorMap m[kMaxPhases];  // per output phase: the strided view y[n, g_oy::o_mul, g_ox::o_mul, :]
+};
 
 struct TileCoord {
   int x0, y0, n0, co0, phase;
@@ -127,19 +158,99 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmArgs& a, int tile) {
   return t;
 }
 
+// Swapped-operand epilogue: this thread owns ONE output channel (TMEM lane) and 32 consecutive tile pixels (columns
+// m0..m0+31).  The 32 lanes of the warp hold 32 consecutive channels of the same pixel, so each store instruction of
+// the warp writes one contiguous run of channels (y is channels-fastest).  Pixel coordinates are warp-uniform.
+template <typename T, int ACT>
+__device__ __forceinline__ void swap_store(const IgemmArgs& a, const uint32_t (&acc)[32], T* __restrict__ ybase,
+                                           const float* __restrict__ noise_n, int m0, int x0, int y0, int g_oy, int g_ox,
+                                           bool co_ok, float sc, float bi) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const int m = m0 + j;
+    const int px = x0 + (m & (a.tw - 1)), py = y0 + ((m >> a.log_tw) & (a.th - 1));
+    const int oy = py * a.o_mul + g_oy, ox = px * a.o_mul + g_ox;
+    if (!(py < a.grid_h && px < a.grid_w && oy < a.out_h && ox < a.out_w)) continue;  // warp-uniform
+    float r = __uint_as_float(acc[j]) * sc;
+    if (noise_n) r += __ldg(noise_n + (int64_t)oy * a.out_w + ox);
+    if (ACT != -1) r = act_eval<float, (ACT > 0 ? ACT : 0)>(r + bi, 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+    if (co_ok) ybase[(int64_t)oy * a.ys[2] + (int64_t)ox * a.ys[3]] = cvt_out<T>(r);
+  }
+}
+
+// Fast variant for tiles at least 32 pixels wide: the 32 columns are consecutive x of ONE output row, so the row
+// pointer, the bounds (nvalid leading pixels exist) and the noise (lane j holds pixel j's value) are hoisted out.
+template <typename T, int ACT>
+__device__ __forceinline__ void swap_store_row(const IgemmArgs& a, const uint32_t (&acc)[32], T* __restrict__ yrow,
+                                               int64_t xstride, int nvalid, float nz_lane, bool has_noise, bool co_ok,
+                                               float sc, float bi) {
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    float r = __uint_as_float(acc[j]) * sc;
+    if (has_noise) r += __shfl_sync(0xffffffffu, nz_lane, j);
+    if (ACT != -1) r = act_eval<float, (ACT > 0 ? ACT : 0)>(r + bi, 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+    if (co_ok && j < nvalid) yrow[j * xstride] = cvt_out<T>(r);
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void swap_row_dispatch(const IgemmArgs& a, const uint32_t (&acc)[32], T* yrow, int64_t xstride,
+                                                  int nvalid, float nz_lane, bool has_noise, bool co_ok, float sc, float bi) {
+  if (a.act == 0) swap_store_row<T, -1>(a, acc, yrow, xstride, nvalid, nz_lane, has_noise, co_ok, sc, bi);
+  else if (a.act == VCN_ACT_LRELU) swap_store_row<T, VCN_ACT_LRELU>(a, acc, yrow, xstride, nvalid, nz_lane, has_noise, co_ok, sc, bi);
+  else if (a.act == VCN_ACT_LINEAR) swap_store_row<T, VCN_ACT_LINEAR>(a, acc, yrow, xstride, nvalid, nz_lane, has_noise, co_ok, sc, bi);
+  else swap_store_row<T, 0>(a, acc, yrow, xstride, nvalid, nz_lane, has_noise, co_ok, sc, bi);
+}
+
+// Swapped operands, staged output: this thread's channel goes to byte (cl & 7) * 2 of 16-byte chunk (cl >> 3) ^ (row & 7)
+// of staging row `row` (= tile pixel), cl = channel inside its 64-channel block.  row0 is a multiple of 32.
+template <typename T, int ACT>
+__device__ __forceinline__ void swap_stage(const IgemmArgs& a, const uint32_t (&acc)[32], unsigned char* __restrict__ blk,
+                                           int cl, int row0, float nz_lane, bool has_noise, float sc, float bi) {
+  if constexpr (sizeof(T) == 2) {
+    unsigned char* base = blk + (size_t)row0 * 128 + (cl & 7) * 2;
+    const int chunk = cl >> 3;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      float r = __uint_as_float(acc[j]) * sc;
+      if (has_noise) r += __shfl_sync(0xffffffffu, nz_lane, j);
+      if (ACT != -1) r = act_eval<float, (ACT > 0 ? ACT : 0)>(r + bi, 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+      *reinterpret_cast<T*>(base + j * 128 + ((chunk ^ (j & 7)) << 4)) = cvt_out<T>(r);
+    }
+  }
+}
+
+template <typename T>
+__device__ __forceinline__ void swap_stage_dispatch(const IgemmArgs& a, const uint32_t (&acc)[32], unsigned char* blk, int cl,
+                                                    int row0, float nz_lane, bool has_noise, float sc, float bi) {
+  if (a.act == 0) swap_stage<T, -1>(a, acc, blk, cl, row0, nz_lane, has_noise, sc, bi);
+  else if (a.act == VCN_ACT_LRELU) swap_stage<T, VCN_ACT_LRELU>(a, acc, blk, cl, row0, nz_lane, has_noise, sc, bi);
+  else if (a.act == VCN_ACT_LINEAR) swap_stage<T, VCN_ACT_LINEAR>(a, acc, blk, cl, row0, nz_lane, has_noise, sc, bi);
+  else swap_stage<T, 0>(a, acc, blk, cl, row0, nz_lane, has_noise, sc, bi);
+}
+
+template <typename T>
+__device__ __forceinline__ void swap_dispatch(const IgemmArgs& a, const uint32_t (&acc)[32], T* ybase, const float* noise_n,
+                                              int m0, int x0, int y0, int g_oy, int g_ox, bool co_ok, float sc, float bi) {
+  if (a.act == 0) swap_store<T, -1>(a, acc, ybase, noise_n, m0, x0, y0, g_oy, g_ox, co_ok, sc, bi);
+  else if (a.act == VCN_ACT_LRELU) swap_store<T, VCN_ACT_LRELU>(a, acc, ybase, noise_n, m0, x0, y0, g_oy, g_ox, co_ok, sc, bi);
+  else if (a.act == VCN_ACT_LINEAR) swap_store<T, VCN_ACT_LINEAR>(a, acc, ybase, noise_n, m0, x0, y0, g_oy, g_ox, co_ok, sc, bi);
+  else swap_store<T, 0>(a, acc, ybase, noise_n, m0, x0, y0, g_oy, g_ox, co_ok, sc, bi);
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                  const __grid_constant__ IgemmArgs a) {
+                  const __grid_constant__ OutMaps om, const __grid_constant__ IgemmArgs a) {
   extern __shared__ unsigned char smem_raw[];
   // 1024-byte alignment: the 128B swizzle pattern repeats every 8 rows = 1024 bytes
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const uint32_t b_bytes = (uint32_t)a.n_tile * kBlockK * 2;
-  const uint32_t stage_bytes = kABytes + b_bytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)a.stages * stage_bytes);
+  const uint32_t stage_bytes = a.pix_bytes + a.w_bytes;
+  unsigned char* stg = smem + (size_t)a.stages * stage_bytes;  // output staging tile (1024-byte aligned), may be empty
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg + a.stage_bytes_out);
   uint64_t* empty_bar = full_bar + a.stages;
   uint64_t* tmem_full_bar = empty_bar + a.stages;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;     // [2]
@@ -172,6 +283,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
+      long long prof_wait = 0;
       for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x) {
         const TileCoord tc = decode_tile(a, tile);
         const int nw = a.w_per_sample ? tc.n0 : 0;
@@ -179,36 +291,46 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const ConvTap tap = a.taps[t];
           const int ax = tc.x0 * a.a_mul + tap.dx, ay = tc.y0 * a.a_mul + tap.dy;
           for (int cb = 0; cb < a.kblocks_c; ++cb) {
+            const long long t0 = a.prof ? clock64() : 0;
             mbar_wait(empty_bar + s, ph ^ 1u);
+            if (a.prof) prof_wait += clock64() - t0;
             unsigned char* sa = smem + (size_t)s * stage_bytes;
             mbar_expect_tx(full_bar + s, stage_bytes);
             tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, ax, ay, tc.n0);
-            tma_load_4d(sa + kABytes, &tmap_b, full_bar + s, cb * kBlockK, tc.co0, tap.wtap, nw);
+            tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * kBlockK, tc.co0, tap.wtap, nw);
             if (++s == a.stages) { s = 0; ph ^= 1u; }
           }
         }
       }
+      if (a.prof) atomicAdd(&g_conv_prof[5], (unsigned long long)prof_wait);
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16_f32(kBlockM, a.n_tile);
+      const int acc_cols = a.swap ? 256 : a.n_tile;
+      const uint32_t idesc = umma_idesc_bf16_f32(kBlockM, acc_cols);
       int s = 0;
       uint32_t ph = 0;
       int tile_iter = 0;
+      long long prof_acc = 0, prof_ops = 0, prof_kb = 0;
       for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
         const TileCoord tc = decode_tile(a, tile);
         const int num_kb = (a.phase_first[tc.phase + 1] - a.phase_first[tc.phase]) * a.kblocks_c;
         const int as = tile_iter & 1;
         const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
+        long long t0 = a.prof ? clock64() : 0;
         mbar_wait(tmem_empty_bar + as, aph ^ 1u);  // epilogue has drained this accumulator stage
+        if (a.prof) prof_acc += clock64() - t0;
         tcgen05_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(as * a.n_tile);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * acc_cols);
         for (int kb = 0; kb < num_kb; ++kb) {
+          if (a.prof) t0 = clock64();
           mbar_wait(full_bar + s, ph);
+          if (a.prof) { prof_ops += clock64() - t0; ++prof_kb; }
           tcgen05_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
-          const uint64_t da = umma_desc_k_sw128(sa), db = umma_desc_k_sw128(sa + kABytes);
+          const uint64_t dpix = umma_desc_k_sw128(sa), dwt = umma_desc_k_sw128(sa + a.pix_bytes);
+          const uint64_t da = a.swap ? dwt : dpix, db = a.swap ? dpix : dwt;
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
@@ -218,6 +340,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
         umma_commit(tmem_full_bar + as);
+      }
+      if (a.prof) {
+        atomicAdd(&g_conv_prof[2], (unsigned long long)prof_acc);
+        atomicAdd(&g_conv_prof[3], (unsigned long long)prof_ops);
+        atomicAdd(&g_conv_prof[6], (unsigned long long)prof_kb);
       }
     }
   } else {
@@ -230,6 +357,82 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int tn_i = m / (a.tw * a.th);
     const bool stage_scale = a.scale != nullptr && a.tn == 1;
     int tile_iter = 0;
+    long long prof_busy = 0, prof_wait = 0;
+    if (a.swap) {
+      // lane = out channel, columns = the 256 pixels of the tile (one sample per tile: tn == 1)
+      for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
+        const TileCoord tc = decode_tile(a, tile);
+        const int as = tile_iter & 1;
+        const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
+        const int co = tc.co0 + m;
+        const bool co_ok = co < a.cout;
+        const float sc = (a.scale && co_ok) ? a.scale[(int64_t)tc.n0 * a.cout + co] : 1.f;
+        const float bi = (a.bias && co_ok) ? a.bias[co] : 0.f;
+        const float* noise_n = a.noise ? a.noise + (int64_t)tc.n0 * a.noise_stride_n : nullptr;
+        const int64_t yoff = (int64_t)tc.n0 * a.ys[0] + (co_ok ? co : 0);
+        const int g_oy = a.g_oy[tc.phase], g_ox = a.g_ox[tc.phase];
+        if (a.stage_out) {  // the previous tile's TMA stores must have read the staging tile before it is rewritten
+          if (et == 0) tma_store_wait_read();
+          named_bar_sync(1, kEpilogueWarps * 32);
+        }
+        long long t0 = a.prof ? clock64() : 0;
+        mbar_wait(tmem_full_bar + as, aph);
+        if (a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
+        tcgen05_fence_after();
+        for (int c = 0; c < 256; c += 32) {
+          uint32_t acc[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 256 + c);
+          if (a.stage_out) {
+            tmem_ld_32x32(taddr, acc);
+            float nz_lane = 0.f;
+            if (noise_n) {  // lane j fetches the noise of tile pixel c + j
+              const int ml = c + lane;
+              const int px = tc.x0 + (ml & (a.tw - 1)), py = tc.y0 + ((ml >> a.log_tw) & (a.th - 1));
+              const int oy = py * a.o_mul + g_oy, ox = px * a.o_mul + g_ox;
+              if (py < a.grid_h && px < a.grid_w && oy < a.out_h && ox < a.out_w) nz_lane = __ldg(noise_n + (int64_t)oy * a.out_w + ox);
+            }
+            unsigned char* blk = stg + (size_t)(m >> 6) * a.stage_blk_bytes;
+            tmem_ld_wait();
+            if (a.y_dtype == VCN_BF16) swap_stage_dispatch<__nv_bfloat16>(a, acc, blk, m & 63, c, nz_lane, noise_n != nullptr, sc, bi);
+            else if (a.y_dtype == VCN_F16) swap_stage_dispatch<__half>(a, acc, blk, m & 63, c, nz_lane, noise_n != nullptr, sc, bi);
+            continue;
+          }
+          if (a.tw >= 32) {
+            const int px0 = tc.x0 + (c & (a.tw - 1)), py = tc.y0 + ((c >> a.log_tw) & (a.th - 1));
+            const int oy = py * a.o_mul + g_oy, ox0 = px0 * a.o_mul + g_ox;
+            int nvalid = min(32, min(a.grid_w - px0, (a.out_w - ox0 + a.o_mul - 1) / a.o_mul));
+            if (!(py < a.grid_h && oy < a.out_h)) nvalid = 0;
+            if (nvalid <= 0) continue;  // warp-uniform
+            tmem_ld_32x32(taddr, acc);
+            const float nz_lane = (noise_n && lane < nvalid) ? __ldg(noise_n + (int64_t)oy * a.out_w + ox0 + lane * a.o_mul) : 0.f;
+            const int64_t roff = yoff + (int64_t)oy * a.ys[2] + (int64_t)ox0 * a.ys[3], xs = (int64_t)a.o_mul * a.ys[3];
+            tmem_ld_wait();
+            if (a.y_dtype == VCN_F32) swap_row_dispatch<float>(a, acc, static_cast<float*>(a.y) + roff, xs, nvalid, nz_lane, noise_n != nullptr, co_ok, sc, bi);
+            else if (a.y_dtype == VCN_BF16) swap_row_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + roff, xs, nvalid, nz_lane, noise_n != nullptr, co_ok, sc, bi);
+            else if (a.y_dtype == VCN_F16) swap_row_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + roff, xs, nvalid, nz_lane, noise_n != nullptr, co_ok, sc, bi);
+            continue;
+          }
+          tmem_ld_32x32(taddr, acc);
+          tmem_ld_wait();
+          if (a.y_dtype == VCN_F32) swap_dispatch<float>(a, acc, static_cast<float*>(a.y) + yoff, noise_n, c, tc.x0, tc.y0, g_oy, g_ox, co_ok, sc, bi);
+          else if (a.y_dtype == VCN_BF16) swap_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + yoff, noise_n, c, tc.x0, tc.y0, g_oy, g_ox, co_ok, sc, bi);
+          else swap_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, noise_n, c, tc.x0, tc.y0, g_oy, g_ox, co_ok, sc, bi);
+        }
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar + as);
+        if (a.prof) prof_busy += clock64() - t0;
+        if (a.stage_out) {
+          fence_proxy_async();  // generic-proxy writes of the staging tile -> visible to TMA
+          named_bar_sync(2, kEpilogueWarps * 32);
+          if (et == 0) {
+            for (int b = 0; b < a.out_blocks; ++b)
+              if (tc.co0 + 64 * b < a.cout) tma_store_4d(&om.m[tc.phase], stg + (size_t)b * a.stage_blk_bytes, tc.co0 + 64 * b, tc.x0, tc.y0, tc.n0);
+            tma_store_commit();
+          }
+        }
+      }
+    } else
     for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
       const TileCoord tc = decode_tile(a, tile);
       const int as = tile_iter & 1;
@@ -254,8 +457,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int64_t yoff = ok ? (int64_t)n * a.ys[0] + (int64_t)oy * a.ys[2] + (int64_t)ox * a.ys[3] : 0;
       const float* gscale = (a.scale && !stage_scale && ok) ? a.scale + (int64_t)n * a.cout : nullptr;
       const int co_end = min(a.cout, tc.co0 + a.n_tile);  // channels past the tile belong to another CTA
+      if (a.stage_out && et == 0) tma_store_wait_read();  // previous tile's TMA stores have read the staging tile
       named_bar_sync(1, kEpilogueWarps * 32);
+      long long t0 = a.prof ? clock64() : 0;
       mbar_wait(tmem_full_bar + as, aph);
+      if (a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
       tcgen05_fence_after();
       for (int c = 0; c < a.n_tile; c += 32) {
         if (tc.co0 + c >= a.cout) break;  // warp-uniform
@@ -270,7 +476,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int j = 0; j < 16; ++j) { acc[j] = h16[j]; acc[16 + j] = 0u; }
         }
         tmem_ld_wait();
-        if (ok) {
+        if (ok || a.stage_out) {  // staged: every row is written, TMA clips the pixels that do not exist
+          unsigned char* stg_row = a.stage_out ? stg + (size_t)m * 128 : nullptr;
           float lsc[32];
           const float* scp = sp + c;
           bool has_scale = stage_scale;
@@ -281,15 +488,31 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             has_scale = true;
           }
           const float* bip = sp + a.n_tile + c;
-          if (a.y_dtype == VCN_F32) epilogue_dispatch<float>(a, acc, static_cast<float*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale);
-          else if (a.y_dtype == VCN_BF16) epilogue_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale);
-          else epilogue_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale);
+          if (a.y_dtype == VCN_F32) epilogue_dispatch<float>(a, acc, static_cast<float*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale, stg_row, m & 7, c);
+          else if (a.y_dtype == VCN_BF16) epilogue_dispatch<__nv_bfloat16>(a, acc, static_cast<__nv_bfloat16*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale, stg_row, m & 7, c);
+          else if (a.y_dtype == VCN_F16) epilogue_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale, stg_row, m & 7, c);
         }
       }
       // hand the accumulator stage back to the MMA warp
       tcgen05_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tmem_empty_bar + as);
+      if (a.prof) prof_busy += clock64() - t0;
+      if (a.stage_out) {
+        fence_proxy_async();
+        named_bar_sync(2, kEpilogueWarps * 32);
+        if (et == 0) {
+          for (int b = 0; b < a.out_blocks; ++b)
+            if (tc.co0 + 64 * b < a.cout) tma_store_4d(&om.m[tc.phase], stg + (size_t)b * a.stage_blk_bytes, tc.co0 + 64 * b, tc.x0, tc.y0, tc.n0);
+          tma_store_commit();
+        }
+      }
+    }
+    if (a.stage_out && et == 0) tma_store_wait_all();
+    if (a.prof && et == 0) {
+      atomicAdd(&g_conv_prof[0], (unsigned long long)prof_busy);
+      atomicAdd(&g_conv_prof[1], (unsigned long long)prof_wait);
+      atomicAdd(&g_conv_prof[4], (unsigned long long)tile_iter);
     }
   }
   tcgen05_fence_before();
@@ -306,12 +529,12 @@ inline int pow2_ceil(int v) {
   return p;
 }
 
-// (tw, th, tn) with tw*th*tn = 128 minimising the number of CTA tiles; ties -> wider rows
-void choose_tile(int gw, int gh, int n, int one_sample, int* tw, int* th, int* tn) {
+// (tw, th, tn) with tw*th*tn = pixels (128, or 256 with swapped operands) minimising the number of CTA tiles; ties -> wider rows
+void choose_tile(int gw, int gh, int n, int one_sample, int pixels, int max_w, int min_w, int* tw, int* th, int* tn) {
   int64_t best = -1;
-  for (int w = 128; w >= 1; w >>= 1) {
-    for (int h = 1; w * h <= 128; h <<= 1) {
-      const int nn = 128 / (w * h);
+  for (int w = pixels < max_w ? pixels : max_w; w >= min_w; w >>= 1) {
+    for (int h = 1; w * h <= pixels; h <<= 1) {
+      const int nn = pixels / (w * h);
       if (one_sample && nn != 1) continue;  // per-sample weights: a tile must not straddle samples
       const int64_t tiles = (int64_t)((gw + w - 1) / w) * ((gh + h - 1) / h) * ((n + nn - 1) / nn);
       if (best < 0 || tiles < best) { best = tiles; *tw = w; *th = h; *tn = nn; }
@@ -384,7 +607,15 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   a.a_mul = d->kind == VCN_CONV_SCONV2 ? 2 : 1;
   a.w_per_sample = d->w_per_sample ? 1 : 0;
   a.n = d->n; a.cout = d->cout; a.out_h = d->out_h; a.out_w = d->out_w;
-  choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample, &a.tw, &a.th, &a.tn);
+  // Operand swap (UMMA M = out channels, N = 256 pixels) for 65..128 out channels and a channels-fastest output: a
+  // 128 x 128 tile pulls 1/64 byte of operands per flop through TMA, a 128 x 256 tile 1/85 - and the measured ceiling
+  // of this kernel is the ~50 B/clk an SM ingests from L2, not the tensor pipe.
+  a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256;
+  if (const char* e = getenv("VCN_CONV_SWAP")) a.swap = a.swap && atoi(e) != 0;
+  choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample || a.swap, a.swap ? 256 : 128, 256 / a.a_mul,
+              (a.swap && a.grid_w > 16) ? 32 : 1 /* swapped epilogue: 32 consecutive x per TMEM chunk */, &a.tw, &a.th, &a.tn);
+  for (a.log_tw = 0; (1 << a.log_tw) < a.tw; ++a.log_tw) {}
+  for (a.log_th = 0; (1 << a.log_th) < a.th; ++a.log_th) {}
   a.tiles_w = (a.grid_w + a.tw - 1) / a.tw;
   a.tiles_h = (a.grid_h + a.th - 1) / a.th;
   const int tiles_n = (d->n + a.tn - 1) / a.tn;
@@ -392,9 +623,10 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   // two accumulator stages of n_tile fp32 columns each must fit the 512 TMEM columns
   a.n_tile = (d->cout + 15) / 16 * 16;
   if (a.n_tile > 256) a.n_tile = 256;
+  if (a.swap) a.n_tile = 128;  // out channels per tile = the 128 UMMA rows (TMA zero-fills rows past cout)
   // few M tiles (tiny resolutions): narrower out-channel tiles spread the weight stream over more SMs - one CTA
   // ingests only ~75 GB/s through TMA, so a 4.7 MB weight tensor on 2 CTAs is latency/bandwidth bound
-  while (a.n_tile > 32 && a.n_tile % 32 == 0 &&
+  while (!a.swap && a.n_tile > 32 && a.n_tile % 32 == 0 &&
          (int64_t)a.tiles_m * a.num_phases * ((d->cout + a.n_tile - 1) / a.n_tile) < sm_count() / 2)
     a.n_tile /= 2;
   const int tiles_co = (d->cout + a.n_tile - 1) / a.n_tile;
@@ -402,28 +634,42 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   VCN_REQUIRE(total <= 0x7fffffffLL, "conv_igemm: too many tiles");
   a.tiles_total = (int)total;
   a.kblocks_c = (d->cin_pad + kBlockK - 1) / kBlockK;
-  a.tmem_cols = pow2_ceil(2 * a.n_tile);
+  a.tmem_cols = a.swap ? 512 : pow2_ceil(2 * a.n_tile);
   if (a.tmem_cols < 32) a.tmem_cols = 32;
-  const size_t stage_bytes = kABytes + (size_t)a.n_tile * kBlockK * 2;
+  a.pix_bytes = (a.swap ? 2u : 1u) * kABytes;
+  a.w_bytes = (uint32_t)a.n_tile * kBlockK * 2;
+  const size_t stage_bytes = (size_t)a.pix_bytes + a.w_bytes;
   const size_t tail_bytes = (2 * (size_t)8 + 4) * 8 + 16 + 4 * (size_t)a.n_tile * sizeof(float) + 64;
-  a.stages = (int)((220 * 1024 - 1024 - tail_bytes) / stage_bytes);
-  if (a.stages > 8) a.stages = 8;
-  if (a.stages < 1) a.stages = 1;
-  // one CTA per SM (launch bounds); TMEM allocations above 256 columns additionally rely on it
-  size_t smem = 1024 + (size_t)a.stages * stage_bytes + tail_bytes;
-  if (smem < 120 * 1024) smem = 120 * 1024;
 
   a.y = y; a.y_dtype = d->y_dtype;
   for (int i = 0; i < 4; ++i) a.ys[i] = d->ys[i];
   const size_t oe = dtype_size(d->y_dtype);
   const int64_t vq = 16 / (int64_t)oe;
   a.vec_store = d->ys[1] == 1 && aligned16(y) && d->ys[0] % vq == 0 && d->ys[2] % vq == 0 && d->ys[3] % vq == 0;
+  // staged TMA-store epilogue: 16-bit channels-fastest output whose 64-channel blocks fill whole staging rows
+  a.stage_out = a.vec_store && oe == 2 && (a.swap || a.n_tile % 64 == 0);
+  if (const char* e = getenv("VCN_CONV_STAGE")) a.stage_out = a.stage_out && atoi(e) != 0;
+  if (a.stage_out) {
+    a.out_blocks = a.n_tile / 64;
+    a.stage_blk_bytes = (a.swap ? 256u : 128u) * 128u;
+    a.stage_bytes_out = (uint32_t)a.out_blocks * a.stage_blk_bytes;
+  }
+  a.stages = (int)((232448 - 1024 - (int64_t)tail_bytes - (int64_t)a.stage_bytes_out) / (int64_t)stage_bytes);
+  if (a.stages > 8) a.stages = 8;
+  if (a.stages < 1) a.stages = 1;
+  // one CTA per SM (launch bounds); TMEM allocations above 256 columns additionally rely on it
+  size_t smem = 1024 + (size_t)a.stages * stage_bytes + a.stage_bytes_out + tail_bytes;
+  if (smem < 120 * 1024) smem = 120 * 1024;
   if (epi) {
     a.scale = epi->scale; a.noise = epi->noise; a.noise_stride_n = epi->noise_stride_n; a.bias = epi->bias;
     a.act = epi->act; a.alpha = epi->alpha; a.act_gain = epi->act_gain; a.clamp = epi->clamp;
     VCN_REQUIRE(a.act == 0 || (a.act >= VCN_ACT_LINEAR && a.act <= VCN_ACT_SWISH), "conv_igemm: bad epilogue act %d", a.act);
   }
 
+  if (const char* e = getenv("VCN_CONV_PROFILE")) a.prof = atoi(e) != 0;
+  if (const char* e = getenv("VCN_CONV_DEBUG_NOSTORE")) {  // profiling aid: the epilogue drains TMEM but stores nothing
+    if (atoi(e) != 0) a.y_dtype = -1;
+  }
   CUtensorMap tmap_a, tmap_b;
   {
     const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
@@ -445,10 +691,37 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
     const int rc = make_tensor_map(&tmap_b, VCN_BF16, 4, wt, dims, strides, box, nullptr, 1);
     if (rc) return rc;
   }
+  OutMaps om;
+  memset(&om, 0, sizeof(om));
+  if (a.stage_out) {
+    for (int g = 0; g < a.num_phases; ++g) {
+      // phase view: pixel (py, px) of the M grid is output pixel (py * o_mul + g_oy, px * o_mul + g_ox)
+      const int64_t vw = (d->out_w - a.g_ox[g] + a.o_mul - 1) / a.o_mul, vh = (d->out_h - a.g_oy[g] + a.o_mul - 1) / a.o_mul;
+      const char* base = static_cast<const char*>(y) + ((int64_t)a.g_oy[g] * d->ys[2] + (int64_t)a.g_ox[g] * d->ys[3]) * 2;
+      const uint64_t dims[4] = {(uint64_t)d->cout, (uint64_t)vw, (uint64_t)vh, (uint64_t)d->n};
+      const uint64_t strides[3] = {(uint64_t)(d->ys[3] * a.o_mul * 2), (uint64_t)(d->ys[2] * a.o_mul * 2), (uint64_t)(d->ys[0] * 2)};
+      const uint32_t box[4] = {64u, (uint32_t)a.tw, (uint32_t)a.th, (uint32_t)a.tn};
+      const int rc = make_tensor_map(&om.m[g], d->y_dtype, 4, base, dims, strides, box, nullptr, 1);
+      if (rc) return rc;
+    }
+  }
   VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = sm_count();
   if (grid > a.tiles_total) grid = a.tiles_total;
-  conv_igemm_kernel<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, a);
+  conv_igemm_kernel<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, om, a);
   VCN_LAUNCH_CHECK("conv_igemm_kernel");
+  return VCN_OK;
+}
+
+extern "C" int vcn_conv_profile_counters(uint64_t out[8], int reset) {
+  using namespace vcn;
+  VCN_REQUIRE(out != nullptr, "conv_profile_counters: out must not be NULL");
+  unsigned long long h[8];
+  VCN_CUDA(cudaMemcpyFromSymbol(h, g_conv_prof, sizeof(h)));
+  for (int i = 0; i < 8; ++i) out[i] = h[i];
+  if (reset) {
+    memset(h, 0, sizeof(h));
+    VCN_CUDA(cudaMemcpyToSymbol(g_conv_prof, h, sizeof(h)));
+  }
   return VCN_OK;
 }

@@ -56,7 +56,7 @@ __device__ __forceinline__ void group_reduce_add(float (*red)[8], const float (&
 }
 
 template <typename T, bool FINISH>
-__global__ void __launch_bounds__(256) modconv_bwd_cl_kernel(const BwdClArgs a) {
+__global__ void __launch_bounds__(256, 2) modconv_bwd_cl_kernel(const BwdClArgs a) {
   __shared__ float red[256][8];
   const int tid = threadIdx.x, n = blockIdx.y;
   const int groups = a.c_pad >> 3;        // <= 256
@@ -83,7 +83,69 @@ __global__ void __launch_bounds__(256) modconv_bwd_cl_kernel(const BwdClArgs a) 
   const T* pb = a.y ? static_cast<const T*>(a.y) + (int64_t)n * a.bs[0] + c : nullptr;
   const bool va = valid == 8 && ((a.as[0] | a.as[2] | a.as[3]) & 7) == 0 && aligned16_dev(a.dy);
   const bool vb = valid == 8 && ((a.bs[0] | a.bs[2] | a.bs[3]) & 7) == 0 && aligned16_dev(a.y);
-  if (active) {
+  // one pixel of this thread's 8 channels: u = dy (or dxhat), v = y (or x); off_a = element offset of the pixel in dy
+  auto pixel = [&](const float (&u)[8], const float (&v)[8], float nz, int64_t off_a, int p) {
+    Vec16<__nv_bfloat16> o;
+    if (FINISH) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        acc0[k] = fmaf(u[k], v[k], acc0[k]);
+        o.v[k] = __float2bfloat16_rn(u[k] * sc[k]);
+      }
+      // in place: dxhat is a dense [n,h,w,c_pad] bf16 buffer
+      *reinterpret_cast<Vec16<__nv_bfloat16>*>(const_cast<T*>(pa) + off_a) = o;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float dz = u[k], r = v[k];
+        if (a.act) {  // first derivative of bias_act keyed on the stored output (bias_act.cu:48,72,141)
+          const float yy = v[k] * a.inv_gain;
+          const bool neg = a.act == VCN_ACT_LRELU && !(yy > 0.f);
+          dz = (neg ? u[k] * a.alpha : u[k]) * a.gain;
+          if (a.clamp >= 0.f && !(v[k] > -a.clamp && v[k] < a.clamp)) dz = 0.f;
+          r = (neg ? yy * a.inv_alpha : yy) - bi[k];
+        }
+        r -= nz;
+        acc0[k] = fmaf(dz, r, acc0[k]);
+        acc1[k] += dz;
+        o.v[k] = __float2bfloat16_rn(k < valid ? dz * sc[k] : 0.f);
+      }
+      *reinterpret_cast<Vec16<__nv_bfloat16>*>(a.out + ((int64_t)n * hw + p) * a.c_pad + c) = o;
+    }
+  };
+  const float* noise_n = (!FINISH && a.noise) ? a.noise + (int64_t)n * a.noise_stride_n : nullptr;
+  // dense rows (stride_h == w * stride_w) of full, aligned channel groups: the pixel offset is p * stride_w and the
+  // loads of kBatch pixels are issued before the first one is consumed (the pass is latency-bound otherwise: at 77
+  // registers three CTAs per SM keep only 24 KB in flight, HBM needs ~50 KB per SM)
+  constexpr int kBatch = 4;
+  const bool fast = va && (!pb || vb) && a.as[2] == (int64_t)a.w * a.as[3] && (!pb || a.bs[2] == (int64_t)a.w * a.bs[3]);
+  if (active && fast) {
+    const int64_t sa = a.as[3], sb = a.bs[3];
+    for (int p = blockIdx.x * a.chunk + row; p < p_end; p += kBatch * rows) {
+      Vec16<T> ru[kBatch], rv[kBatch];
+      float nz[kBatch];
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b) {
+        const int pp = p + b * rows;
+        if (pp < p_end) {
+          // finish rewrites dxhat in place: a plain load there, the non-coherent streaming path for read-only data
+          ru[b] = FINISH ? *reinterpret_cast<const Vec16<T>*>(pa + pp * sa) : ld_stream<T>(pa + pp * sa);
+          if (pb) rv[b] = ld_stream<T>(pb + pp * sb);
+          nz[b] = noise_n ? __ldg(noise_n + pp) : 0.f;
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < kBatch; ++b) {
+        const int pp = p + b * rows;
+        if (pp < p_end) {
+          float u[8], v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { u[k] = to_acc<T>(ru[b].v[k]); v[k] = pb ? to_acc<T>(rv[b].v[k]) : 0.f; }
+          pixel(u, v, nz[b], pp * sa, pp);
+        }
+      }
+    }
+  } else if (active) {
     for (int p = blockIdx.x * a.chunk + row; p < p_end; p += rows) {
       const int py = p / a.w, px = p - py * a.w;
       float u[8], v[8];
@@ -93,35 +155,7 @@ __global__ void __launch_bounds__(256) modconv_bwd_cl_kernel(const BwdClArgs a) 
 #pragma unroll
         for (int k = 0; k < 8; ++k) v[k] = 0.f;
       }
-      Vec16<__nv_bfloat16> o;
-      if (FINISH) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          acc0[k] = fmaf(u[k], v[k], acc0[k]);
-          o.v[k] = __float2bfloat16_rn(u[k] * sc[k]);
-        }
-        // in place: dxhat is a dense [n,h,w,c_pad] bf16 buffer
-        *reinterpret_cast<Vec16<__nv_bfloat16>*>(const_cast<T*>(pa) + py * a.as[2] + px * a.as[3]) = o;
-      } else {
-        float nz = 0.f;
-        if (a.noise) nz = a.noise[(int64_t)n * a.noise_stride_n + p];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          float dz = u[k], r = v[k];
-          if (a.act) {  // first derivative of bias_act keyed on the stored output (bias_act.cu:48,72,141)
-            const float yy = v[k] * a.inv_gain;
-            const bool neg = a.act == VCN_ACT_LRELU && !(yy > 0.f);
-            dz = (neg ? u[k] * a.alpha : u[k]) * a.gain;
-            if (a.clamp >= 0.f && !(v[k] > -a.clamp && v[k] < a.clamp)) dz = 0.f;
-            r = (neg ? yy * a.inv_alpha : yy) - bi[k];
-          }
-          r -= nz;
-          acc0[k] = fmaf(dz, r, acc0[k]);
-          acc1[k] += dz;
-          o.v[k] = __float2bfloat16_rn(k < valid ? dz * sc[k] : 0.f);
-        }
-        *reinterpret_cast<Vec16<__nv_bfloat16>*>(a.out + ((int64_t)n * hw + p) * a.c_pad + c) = o;
-      }
+      pixel(u, v, noise_n ? noise_n[p] : 0.f, py * a.as[2] + px * a.as[3], p);
     }
   }
   if (!active) {

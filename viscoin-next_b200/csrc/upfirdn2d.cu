@@ -409,136 +409,121 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
 // is read once from shared memory per 2x2 block (25 LDS.128 for 4 outputs) - the 8 threads of a quarter warp read the
 // 128 contiguous bytes of one pixel, so the reads are bank-conflict free.
 // ---------------------------------------------------------------------------------------------
-constexpr int kClTx = 16, kClTy = 16, kClCb = 64;
+constexpr int kClTx = 32, kClTy = 16, kClCb = 64;
 
-// Persistent: CTA walks tiles (x tile, y tile, sample, channel block) blockIdx.x, + gridDim.x, ...; two halo buffers, the
-// TMA box of the next tile is in flight while this one is filtered.
 template <typename T, typename TO>
 __global__ void __launch_bounds__(256, 2)
-upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y,
-                    const int cblocks, const int total_tiles) {
+upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int HX = kClTx + kF - 1, HY = kClTy + kF - 1;
-  constexpr uint32_t kTileBytes = HY * HX * kClCb * sizeof(T);
-  constexpr uint32_t kBufBytes = (kTileBytes + 127u) & ~127u;
-  float* s_flt = reinterpret_cast<float*>(smem_raw + 2 * kBufBytes);     // flt[16]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(s_flt + kF * kF);           // [2]
+  T* tile = reinterpret_cast<T*>(smem_raw);                                   // [HY][HX][64]
+  float* s_par = reinterpret_cast<float*>(smem_raw + (size_t)HY * HX * kClCb * sizeof(T));  // scale[64] | bias[64] | flt[16]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_par + 2 * kClCb + kF * kF);
 
   const int tid = threadIdx.x;
-  auto decode = [&](int t, int& ox0, int& oy0, int& n, int& c0) {
-    const int bx = t % tiles_x; t /= tiles_x;
-    const int by = t % tiles_y; t /= tiles_y;
-    c0 = (t % cblocks) * kClCb;
-    n = t / cblocks;
-    ox0 = bx * kClTx; oy0 = by * kClTy;
-  };
-  auto issue = [&](int t, int b) {
-    int ox0, oy0, n, c0;
-    decode(t, ox0, oy0, n, c0);
-    mbar_expect_tx(bar + b, kTileBytes);
-    tma_load_4d(smem_raw + b * kBufBytes, &tmap, bar + b, c0, ox0 - a.padx0, oy0 - a.pady0, n);
-  };
+  int bid = blockIdx.x;
+  const int bx = bid % tiles_x; bid /= tiles_x;
+  const int by = bid % tiles_y;
+  const int n = bid / tiles_y;
+  const int c0 = blockIdx.y * kClCb;
+  const int ox0 = bx * kClTx, oy0 = by * kClTy;
 
   if (tid == 0) {
     mbar_init(bar, 1);
-    mbar_init(bar + 1, 1);
     fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    mbar_expect_tx(bar, (uint32_t)(HY * HX * kClCb * sizeof(T)));
+    tma_load_4d(tile, &tmap, bar, c0, ox0 - a.padx0, oy0 - a.pady0, n);
   }
   if (tid < kF * kF) {
     const int fy = tid / kF, fx = tid % kF;
     float w = 0.f;
     if (fy < a.fh && fx < a.fw) w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
-    s_flt[tid] = w * a.gain;
+    s_par[2 * kClCb + tid] = w * a.gain;
+  } else if (tid >= 64 && tid < 64 + kClCb) {
+    const int c = c0 + tid - 64;
+    s_par[tid - 64] = (a.scale && c < a.c) ? a.scale[(int64_t)n * a.c + c] : 1.f;
+  } else if (tid >= 128 && tid < 128 + kClCb) {
+    const int c = c0 + tid - 128;
+    s_par[kClCb + tid - 128] = (a.bias && a.act && c < a.c) ? a.bias[c] : 0.f;
   }
   __syncthreads();
-  if (tid == 0) issue(blockIdx.x, 0);
+  mbar_wait(bar, 0);
 
   float flt[kF][kF];
 #pragma unroll
   for (int i = 0; i < kF; ++i)
 #pragma unroll
-    for (int j = 0; j < kF; ++j) flt[i][j] = s_flt[i * kF + j];
+    for (int j = 0; j < kF; ++j) flt[i][j] = s_par[2 * kClCb + i * kF + j];
 
   const int cg = tid & 7;          // channel group: channels c0 + cg*8 .. +7
   const int pb = tid >> 3;         // 0..31
-  int it = 0;
-  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-    const int b = it & 1;
-    if (tid == 0 && t + (int)gridDim.x < total_tiles) issue(t + gridDim.x, b ^ 1);
-    int ox0, oy0, n, c0;
-    decode(t, ox0, oy0, n, c0);
-    const int c = c0 + cg * 8;
-    float sc[8], bi[8];
+  const int c = c0 + cg * 8;
+  if (c >= a.c) return;
+  float sc[8], bi[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const bool ok = c + k < a.c;
-      sc[k] = (a.scale && ok) ? a.scale[(int64_t)n * a.c + c + k] : 1.f;
-      bi[k] = (a.bias && a.act && ok) ? a.bias[c + k] : 0.f;
-    }
-    mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
-    const T* tile = reinterpret_cast<const T*>(smem_raw + b * kBufBytes);
-    if (c < a.c) {
+  for (int k = 0; k < 8; ++k) { sc[k] = s_par[cg * 8 + k]; bi[k] = s_par[kClCb + cg * 8 + k]; }
+
 #pragma unroll 1
-      for (int rep = 0; rep < (kClTx / 2) * (kClTy / 2) / 32; ++rep) {
-        const int blk = pb + rep * 32;               // 2x2-pixel blocks of the tile
-        const int bxx = blk % (kClTx / 2), byy = blk / (kClTx / 2);
-        const int oy = oy0 + 2 * byy, ox = ox0 + 2 * bxx;
-        if (oy >= a.out_h || ox >= a.out_w) continue;
-        float acc[2][2][8];
+  for (int it = 0; it < 4; ++it) {
+    const int blk = pb + it * 32;               // 128 blocks of 2x2 pixels: 16 wide x 8 high
+    const int bxx = blk % (kClTx / 2), byy = blk / (kClTx / 2);
+    const int oy = oy0 + 2 * byy, ox = ox0 + 2 * bxx;
+    if (oy >= a.out_h || ox >= a.out_w) continue;
+    float acc[2][2][8];
 #pragma unroll
-        for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < 2; ++i)
 #pragma unroll
-          for (int j = 0; j < 2; ++j)
+      for (int j = 0; j < 2; ++j)
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[i][j][k] = 0.f;
+        for (int k = 0; k < 8; ++k) acc[i][j][k] = 0.f;
 #pragma unroll
-        for (int wy = 0; wy < kF + 1; ++wy) {
+    for (int wy = 0; wy < kF + 1; ++wy) {
 #pragma unroll
-          for (int wx = 0; wx < kF + 1; ++wx) {
-            const Vec16<T> v = *reinterpret_cast<const Vec16<T>*>(tile + ((size_t)(2 * byy + wy) * HX + (2 * bxx + wx)) * kClCb + cg * 8);
-            float f[8];
+      for (int wx = 0; wx < kF + 1; ++wx) {
+        const Vec16<T> v = *reinterpret_cast<const Vec16<T>*>(tile + ((size_t)(2 * byy + wy) * HX + (2 * bxx + wx)) * kClCb + cg * 8);
+        float f[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) f[k] = to_acc<T>(v.v[k]);
-#pragma unroll
-            for (int dy = 0; dy < 2; ++dy) {
-              const int fy = wy - dy;
-              if (fy < 0 || fy >= kF) continue;
-#pragma unroll
-              for (int dx = 0; dx < 2; ++dx) {
-                const int fx = wx - dx;
-                if (fx < 0 || fx >= kF) continue;
-#pragma unroll
-                for (int k = 0; k < 8; ++k) acc[dy][dx][k] = fmaf(f[k], flt[fy][fx], acc[dy][dx][k]);
-              }
-            }
-          }
-        }
+        for (int k = 0; k < 8; ++k) f[k] = to_acc<T>(v.v[k]);
 #pragma unroll
         for (int dy = 0; dy < 2; ++dy) {
+          const int fy = wy - dy;
+          if (fy < 0 || fy >= kF) continue;
 #pragma unroll
           for (int dx = 0; dx < 2; ++dx) {
-            const int yy = oy + dy, xx = ox + dx;
-            if (yy >= a.out_h || xx >= a.out_w) continue;
-            float nz = 0.f;
-            if (a.noise) nz = a.noise[(int64_t)n * a.noise_stride_n + (int64_t)yy * a.out_w + xx];
-            TO* dst = static_cast<TO*>(a.y) + n * a.ys[0] + yy * a.ys[2] + xx * a.ys[3] + c;
-            constexpr int VO = 16 / sizeof(TO);
+            const int fx = wx - dx;
+            if (fx < 0 || fx >= kF) continue;
 #pragma unroll
-            for (int h = 0; h < 8 / VO; ++h) {
-              Vec16<TO> o;
-#pragma unroll
-              for (int k = 0; k < VO; ++k) {
-                float r = acc[dy][dx][h * VO + k] * sc[h * VO + k] + nz;
-                if (a.act) r = act_eval<float, 0>(r + bi[h * VO + k], 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
-                o.v[k] = from_acc<TO>(r);
-              }
-              *reinterpret_cast<Vec16<TO>*>(dst + h * VO) = o;
-            }
+            for (int k = 0; k < 8; ++k) acc[dy][dx][k] = fmaf(f[k], flt[fy][fx], acc[dy][dx][k]);
           }
         }
       }
     }
-    __syncthreads();  // buffer b may be refilled by the issue of the next iteration
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int yy = oy + dy, xx = ox + dx;
+        if (yy >= a.out_h || xx >= a.out_w) continue;
+        float nz = 0.f;
+        if (a.noise) nz = a.noise[(int64_t)n * a.noise_stride_n + (int64_t)yy * a.out_w + xx];
+        TO* dst = static_cast<TO*>(a.y) + n * a.ys[0] + yy * a.ys[2] + xx * a.ys[3] + c;
+        constexpr int VO = 16 / sizeof(TO);
+#pragma unroll
+        for (int h = 0; h < 8 / VO; ++h) {
+          Vec16<TO> o;
+#pragma unroll
+          for (int k = 0; k < VO; ++k) {
+            float r = acc[dy][dx][h * VO + k] * sc[h * VO + k] + nz;
+            if (a.act) r = act_eval<float, 0>(r + bi[h * VO + k], 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+            o.v[k] = from_acc<TO>(r);
+          }
+          *reinterpret_cast<Vec16<TO>*>(dst + h * VO) = o;
+        }
+      }
+    }
   }
 }
 
@@ -559,21 +544,16 @@ int try_launch_cl(const UpfirdnArgs& a, int dtype, int y_dtype, cudaStream_t st)
   const int rc = make_tensor_map(&tmap, dtype, 4, a.x, dims, strides, box, nullptr, 0);
   if (rc) return rc;
   const int tiles_x = (a.out_w + kClTx - 1) / kClTx, tiles_y = (a.out_h + kClTy - 1) / kClTy;
-  const int cblocks = (a.c + kClCb - 1) / kClCb;
-  const size_t buf = (((size_t)(kClTy + kF - 1) * (kClTx + kF - 1) * kClCb * 2) + 127) & ~(size_t)127;
-  const size_t smem = 2 * buf + kF * kF * sizeof(float) + 16;
-  const int64_t total = (int64_t)tiles_x * tiles_y * a.n * cblocks;
-  if (total > 0x7fffffffLL) { set_error("upfirdn2d: too many tiles"); return VCN_ERR_INVALID; }
-  int64_t grid = (int64_t)sm_count() * 2;
-  if (grid > total) grid = total;
+  const size_t smem = (size_t)(kClTy + kF - 1) * (kClTx + kF - 1) * kClCb * 2 + (2 * kClCb + kF * kF) * sizeof(float) + 16;
+  dim3 grid((unsigned)((int64_t)tiles_x * tiles_y * a.n), (unsigned)((a.c + kClCb - 1) / kClCb));
   if (y_dtype == VCN_F32) {
     auto kern = upfirdn2d_cl_kernel<T, float>;
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y, cblocks, (int)total);
+    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
   } else {
     auto kern = upfirdn2d_cl_kernel<T, T>;
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y, cblocks, (int)total);
+    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
   }
   VCN_LAUNCH_CHECK("upfirdn2d_cl_kernel");
   return VCN_OK;
