@@ -174,3 +174,35 @@ def test_channels_last_16bit_fast_path(dtype, shape, pat):
     y = U.upfirdn2d(xc, f4.cuda(), impl="cuda", **kw)
     assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
     assert _rel(y, y_ref) <= 2 * torch.finfo(dtype).eps
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("act,alpha,gain,clamp", [(None, None, None, None), ("lrelu", None, None, None), ("lrelu", 0.2, 1.7, 0.9),
+                                                  ("linear", None, 0.5, 0.4), ("lrelu", 1.5, 1.0, None), ("tanh", None, None, None),
+                                                  ("lrelu", 0.2, -1.0, 0.5)])
+@pytest.mark.parametrize("sep", [True, False])
+def test_channels_last_fused_epilogue(dtype, act, alpha, gain, clamp, sep):
+    """Channels-last 16-bit FIR with the fused epilogue y = bias_act(fir(x) * scale[n,c] + noise[n,:,y,x], bias) - the second
+    half of an up=2 SynthesisLayer (networks.py:299-304 after conv2d_resample.py:125-142) - for the packed
+    (lrelu / linear, gain > 0, 0 <= alpha <= 1) and generic epilogues, with a separable filter (the in-kernel rank-1
+    factorisation + sliding-window path) and a non-separable one (direct path).  fp32 oracle on the rounded inputs;
+    <= 2 ulp of the storage type relative to the output range."""
+    from viscoin_next_b200 import modconv as M
+    U = _ops()
+    g = torch.Generator().manual_seed(11)
+    n, c, h, w = 2, 72, 37, 45
+    x = torch.randn(n, c, h, w, generator=g).to(dtype)
+    f = R.setup_filter([1, 3, 3, 1])
+    if not sep:
+        f = f + 0.05 * torch.randn(4, 4, generator=g)
+    scale = torch.rand(n, c, generator=g) + 0.5
+    noise = torch.randn(n, 1, h - 1, w - 1, generator=g) * 0.3
+    bias = torch.randn(c, generator=g) * 0.3
+    z = R.upfirdn2d(x.float(), f, padding=[1, 1, 1, 1], gain=4) * scale[:, :, None, None] + noise
+    y_ref = R.bias_act(z, bias, act=act, alpha=alpha, gain=gain, clamp=clamp) if act is not None else z
+    epi, hold = M.make_epilogue(scale=scale.cuda(), noise=noise.cuda(), bias=bias.cuda() if act else None, act=act, alpha=alpha,
+                                gain=gain, clamp=clamp)
+    xc = x.cuda().contiguous(memory_format=torch.channels_last)
+    y = U.launch(xc, f.cuda(), 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi)
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, y_ref) <= 2 * torch.finfo(dtype).eps

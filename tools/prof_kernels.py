@@ -28,18 +28,43 @@ def conv_counters(reset):
     return list(out)
 
 
+GRAPH = os.environ.get("VCN_PROF_GRAPH", "1") != "0" and not quick  # replay the launches from one CUDA graph: device time only
+
+
 def timed(name, fn, work, unit):
+    global iters
     fn()
     torch.cuda.synchronize()
     if PROF:
         conv_counters(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(iters):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / iters
+    if GRAPH and not PROF:
+        # python + ctypes + cuTensorMapEncode cost 20-40 us per call - as much as the short kernels themselves; a graph of
+        # `reps` back-to-back launches takes the host out of the measurement (the ABI is capture-safe)
+        reps = 10
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for _ in range(reps):
+                    fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g.replay()
+        torch.cuda.synchronize()
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+    else:
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
     print("%-46s %.4f ms  %.1f %s" % (name, ms, work / ms / 1e9 * (1e3 if unit == "GB/s" else 1), unit), flush=True)
     if PROF and name.startswith("conv"):
         c = conv_counters(True)

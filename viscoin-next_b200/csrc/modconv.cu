@@ -610,7 +610,9 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   // Operand swap (UMMA M = out channels, N = 256 pixels) for 65..128 out channels and a channels-fastest output: a
   // 128 x 128 tile pulls 1/64 byte of operands per flop through TMA, a 128 x 256 tile 1/85 - and the measured ceiling
   // of this kernel is the ~50 B/clk an SM ingests from L2, not the tensor pipe.
-  a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256;
+  // Not for the transposed conv: its phase tiles carry 1..4 taps only (9 k-blocks per tile on average at 256 channels), the
+  // tile is epilogue-bound either way and the swapped epilogue costs 1.7x per pixel (measured: 0.168 ms vs 0.131 ms).
+  a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256 && d->kind != VCN_CONV_TCONV2;
   if (const char* e = getenv("VCN_CONV_SWAP")) a.swap = a.swap && atoi(e) != 0;
   choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample || a.swap, a.swap ? 256 : 128, 256 / a.a_mul,
               (a.swap && a.grid_w > 16) ? 32 : 1 /* swapped epilogue: 32 consecutive x per TMEM chunk */, &a.tw, &a.th, &a.tn);

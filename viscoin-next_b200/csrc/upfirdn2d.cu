@@ -527,6 +527,282 @@ upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tma
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// channels-last kernel, separable form.  Same tile, TMA box and thread/channel mapping as upfirdn2d_cl_kernel, but the
+// 4x4 filter is factored inside the kernel into gy (x) gx (every filter setup_filter() builds from a 1-D kernel is an
+// outer product; the factorisation is checked against all 16 taps and a non-separable filter takes the direct loop at the
+// end).  Thread = 8 channels x 2 columns x 8 rows, walked as a sliding window over 11 staged rows: per row 5 LDS.128, a
+// 4-tap horizontal pass into two column sums and a 4-tap vertical pass into a ring of four output-row accumulators -
+// 8 FMAs per output instead of 16, issued as packed fma.rn.f32x2 (FFMA2: the two channels of one bf16x2 word), i.e.
+// ~10 issue slots per output instead of ~23.  The direct kernel was issue-bound (ncu: issue-active 70+ %).
+// EPI: 0 = plain FIR, 1 = scale / noise / bias with linear or lrelu, 2 = any activation (run-time dispatch).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t pack_f2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack_f2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul_f2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+template <typename T> __device__ __forceinline__ uint64_t widen_f2(uint32_t w);
+template <> __device__ __forceinline__ uint64_t widen_f2<__nv_bfloat16>(uint32_t w) {
+  return pack_f2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+template <> __device__ __forceinline__ uint64_t widen_f2<__half>(uint32_t w) {
+  const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+  return pack_f2(f.x, f.y);
+}
+
+// one output pixel x 8 channels: epilogue + 16-byte stores
+template <typename TO, int EPI>
+__device__ __forceinline__ void cl_emit(const UpfirdnArgs& a, const float (&v)[8], const float* s_par, int cg, int n, int c,
+                                        int yy, int xx) {
+  if (yy >= a.out_h || xx >= a.out_w) return;
+  float r[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) r[k] = v[k];
+  if constexpr (EPI != 0) {
+    const float nz = a.noise ? __ldg(a.noise + (int64_t)n * a.noise_stride_n + (int64_t)yy * a.out_w + xx) : 0.f;
+    const float4 s0 = *reinterpret_cast<const float4*>(s_par + cg * 8), s1 = *reinterpret_cast<const float4*>(s_par + cg * 8 + 4);
+    const float4 b0 = *reinterpret_cast<const float4*>(s_par + kClCb + cg * 8), b1 = *reinterpret_cast<const float4*>(s_par + kClCb + cg * 8 + 4);
+    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float bi[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float t = fmaf(r[k], sc[k], nz);
+      if (a.act) t = act_eval<float, 0>(t + bi[k], 0.f, 0.f, 1.f, a.act, 0, a.alpha, a.act_gain, a.clamp);
+      r[k] = t;
+    }
+  }
+  TO* dst = static_cast<TO*>(a.y) + n * a.ys[0] + yy * a.ys[2] + xx * a.ys[3] + c;
+  constexpr int VO = 16 / sizeof(TO);
+#pragma unroll
+  for (int h = 0; h < 8 / VO; ++h) {
+    Vec16<TO> o;
+#pragma unroll
+    for (int k = 0; k < VO; ++k) o.v[k] = from_acc<TO>(r[h * VO + k]);
+    *reinterpret_cast<Vec16<TO>*>(dst + h * VO) = o;
+  }
+}
+
+// EPI = 1, packed: lrelu / linear are positively homogeneous, so with g = act_gain > 0 and 0 <= alpha <= 1
+//   clamp(lrelu(acc*sc + nz + b) * g) = clamp(max(t, alpha*t)),  t = acc*(sc*g) + (nz*g + b*g)
+// (sc*g and b*g are staged per channel, alpha = 1 for linear / no activation): add2 + fma2 + mul2 per channel pair.
+template <typename TO>
+__device__ __forceinline__ void cl_emit_packed(const UpfirdnArgs& a, const uint64_t (&v)[4], const float* s_par, int cg, int n,
+                                               int c, int yy, int xx, float g, uint64_t alpha2, bool has_clamp) {
+  if (yy >= a.out_h || xx >= a.out_w) return;
+  float nz = 0.f;
+  if (a.noise) nz = __ldg(a.noise + (int64_t)n * a.noise_stride_n + (int64_t)yy * a.out_w + xx) * g;
+  const uint64_t nz2 = pack_f2(nz, nz);
+  const ulonglong2 s0 = *reinterpret_cast<const ulonglong2*>(s_par + cg * 8), s1 = *reinterpret_cast<const ulonglong2*>(s_par + cg * 8 + 4);
+  const ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(s_par + kClCb + cg * 8), b1 = *reinterpret_cast<const ulonglong2*>(s_par + kClCb + cg * 8 + 4);
+  const uint64_t sc[4] = {s0.x, s0.y, s1.x, s1.y}, bi[4] = {b0.x, b0.y, b1.x, b1.y};
+  float r[8];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    uint64_t off;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(off) : "l"(nz2), "l"(bi[p]));
+    const uint64_t t = fma_f2(v[p], sc[p], off);
+    const uint64_t u = mul_f2(t, alpha2);
+    float t0, t1, u0, u1;
+    unpack_f2(t, t0, t1);
+    unpack_f2(u, u0, u1);
+    r[2 * p] = fmaxf(t0, u0);
+    r[2 * p + 1] = fmaxf(t1, u1);
+  }
+  if (has_clamp) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r[k] = fminf(fmaxf(r[k], -a.clamp), a.clamp);
+  }
+  TO* dst = static_cast<TO*>(a.y) + n * a.ys[0] + yy * a.ys[2] + xx * a.ys[3] + c;
+  constexpr int VO = 16 / sizeof(TO);
+#pragma unroll
+  for (int h = 0; h < 8 / VO; ++h) {
+    Vec16<TO> o;
+#pragma unroll
+    for (int k = 0; k < VO; ++k) o.v[k] = from_acc<TO>(r[h * VO + k]);
+    *reinterpret_cast<Vec16<TO>*>(dst + h * VO) = o;
+  }
+}
+
+template <typename T, typename TO, int EPI>
+__global__ void __launch_bounds__(256, 2)
+upfirdn2d_cl_sep_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int HX = kClTx + kF - 1, HY = kClTy + kF - 1;
+  constexpr int RT = kClTy / 2;  // output rows per thread
+  T* tile = reinterpret_cast<T*>(smem_raw);                                   // [HY][HX][64]
+  float* s_par = reinterpret_cast<float*>(smem_raw + (size_t)HY * HX * kClCb * sizeof(T));  // scale[64] | bias[64] | flt[16]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_par + 2 * kClCb + kF * kF);
+
+  const int tid = threadIdx.x;
+  int bid = blockIdx.x;
+  const int bx = bid % tiles_x; bid /= tiles_x;
+  const int by = bid % tiles_y;
+  const int n = bid / tiles_y;
+  const int c0 = blockIdx.y * kClCb;
+  const int ox0 = bx * kClTx, oy0 = by * kClTy;
+
+  const float epi_g = (EPI == 1 && a.act) ? a.act_gain : 1.f;  // EPI 1 folds the activation gain into scale / bias / noise
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    mbar_expect_tx(bar, (uint32_t)(HY * HX * kClCb * sizeof(T)));
+    tma_load_4d(tile, &tmap, bar, c0, ox0 - a.padx0, oy0 - a.pady0, n);
+  }
+  if (tid < kF * kF) {
+    const int fy = tid / kF, fx = tid % kF;
+    float w = 0.f;
+    if (fy < a.fh && fx < a.fw) w = a.flip ? a.f[fy * a.fw + fx] : a.f[(a.fh - 1 - fy) * a.fw + (a.fw - 1 - fx)];
+    s_par[2 * kClCb + tid] = w * a.gain;
+  } else if (tid >= 64 && tid < 64 + kClCb) {
+    const int c = c0 + tid - 64;
+    s_par[tid - 64] = ((a.scale && c < a.c) ? a.scale[(int64_t)n * a.c + c] : 1.f) * epi_g;
+  } else if (tid >= 128 && tid < 128 + kClCb) {
+    const int c = c0 + tid - 128;
+    s_par[kClCb + tid - 128] = ((a.bias && a.act && c < a.c) ? a.bias[c] : 0.f) * epi_g;
+  }
+  __syncthreads();
+
+  // rank-1 factorisation flt[i][j] = gy[i] * gx[j] around the largest tap (while the TMA load is in flight)
+  float gx[kF], gy[kF];
+  bool sep = true;
+  {
+    float flt[kF * kF];
+    int piv = 0;
+    float pv = 0.f;
+#pragma unroll
+    for (int i = 0; i < kF * kF; ++i) {
+      flt[i] = s_par[2 * kClCb + i];
+      if (fabsf(flt[i]) > fabsf(pv)) { pv = flt[i]; piv = i; }
+    }
+    const int pr = piv / kF, pc = piv % kF;
+    const float inv = pv != 0.f ? 1.f / pv : 0.f;
+#pragma unroll
+    for (int j = 0; j < kF; ++j) {
+      gx[j] = 0.f; gy[j] = 0.f;
+#pragma unroll
+      for (int i = 0; i < kF; ++i) {
+        if (i == pr) gx[j] = flt[i * kF + j];
+        if (i == pc) gy[j] = flt[j * kF + i] * inv;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kF; ++i)
+#pragma unroll
+      for (int j = 0; j < kF; ++j) sep = sep && fabsf(flt[i * kF + j] - gy[i] * gx[j]) <= 1e-6f * fabsf(pv);
+  }
+
+  const int cg = tid & 7;           // channel group: channels c0 + cg*8 .. +7
+  const int cp = (tid >> 3) & 15;   // column pair: tile columns 2cp, 2cp+1
+  const int rh = tid >> 7;          // row half: tile rows 8rh .. 8rh+7
+  const int c = c0 + cg * 8;
+  mbar_wait(bar, 0);
+  if (c >= a.c) return;
+  const T* base = tile + ((size_t)(RT * rh) * HX + 2 * cp) * kClCb + cg * 8;
+  const int oyb = oy0 + RT * rh, oxb = ox0 + 2 * cp;
+
+  if (sep) {
+    uint64_t gx2[kF], gy2[kF];
+#pragma unroll
+    for (int j = 0; j < kF; ++j) { gx2[j] = pack_f2(gx[j], gx[j]); gy2[j] = pack_f2(gy[j], gy[j]); }
+    uint64_t acc[4][2][4];  // [output row & 3][column][channel pair]
+    const float alpha = a.act == VCN_ACT_LRELU ? a.alpha : 1.f;
+    const uint64_t alpha2 = pack_f2(alpha, alpha);
+    const bool has_clamp = a.act != 0 && a.clamp >= 0.f;
+#pragma unroll
+    for (int r = 0; r < RT + kF - 1; ++r) {
+      uint64_t h[2][4];
+#pragma unroll
+      for (int j = 0; j < kF + 1; ++j) {
+        const uint4 v = *reinterpret_cast<const uint4*>(base + ((size_t)r * HX + j) * kClCb);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const uint64_t f = widen_f2<T>(w[p]);
+          if (j < kF) h[0][p] = (j == 0) ? mul_f2(f, gx2[0]) : fma_f2(f, gx2[j], h[0][p]);
+          if (j >= 1) h[1][p] = (j == 1) ? mul_f2(f, gx2[0]) : fma_f2(f, gx2[j - 1], h[1][p]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < kF; ++i) {
+        const int o = r - i;  // staged row r is tap i of output row o
+        if (o < 0 || o >= RT) continue;
+#pragma unroll
+        for (int col = 0; col < 2; ++col)
+#pragma unroll
+          for (int p = 0; p < 4; ++p)
+            acc[o & 3][col][p] = (i == 0) ? mul_f2(h[col][p], gy2[0]) : fma_f2(h[col][p], gy2[i], acc[o & 3][col][p]);
+      }
+      if (r >= kF - 1) {
+        const int o = r - (kF - 1);
+#pragma unroll
+        for (int col = 0; col < 2; ++col) {
+          if constexpr (EPI == 1) {
+            cl_emit_packed<TO>(a, acc[o & 3][col], s_par, cg, n, c, oyb + o, oxb + col, epi_g, alpha2, has_clamp);
+          } else {
+            float v[8];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) unpack_f2(acc[o & 3][col][p], v[2 * p], v[2 * p + 1]);
+            cl_emit<TO, EPI>(a, v, s_par, cg, n, c, oyb + o, oxb + col);
+          }
+        }
+      }
+    }
+  } else {
+    // non-separable filter: direct 16-tap accumulation, one pixel at a time (correctness path)
+#pragma unroll 1
+    for (int o = 0; o < RT; ++o) {
+#pragma unroll 1
+      for (int col = 0; col < 2; ++col) {
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = 0.f;
+#pragma unroll 1
+        for (int t = 0; t < kF * kF; ++t) {
+          const float w = s_par[2 * kClCb + t];
+          const Vec16<T> in = *reinterpret_cast<const Vec16<T>*>(base + ((size_t)(o + t / kF) * HX + col + t % kF) * kClCb);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) v[k] = fmaf(to_acc<T>(in.v[k]), w, v[k]);
+        }
+        if constexpr (EPI == 1) {
+          uint64_t vp[4];
+#pragma unroll
+          for (int p = 0; p < 4; ++p) vp[p] = pack_f2(v[2 * p], v[2 * p + 1]);
+          const float alpha = a.act == VCN_ACT_LRELU ? a.alpha : 1.f;
+          cl_emit_packed<TO>(a, vp, s_par, cg, n, c, oyb + o, oxb + col, epi_g, pack_f2(alpha, alpha), a.act != 0 && a.clamp >= 0.f);
+        } else {
+          cl_emit<TO, EPI>(a, v, s_par, cg, n, c, oyb + o, oxb + col);
+        }
+      }
+    }
+  }
+}
+
+template <typename T, typename TO, int EPI>
+int launch_cl_sep(const UpfirdnArgs& a, const CUtensorMap& tmap, dim3 grid, size_t smem, int tiles_x, int tiles_y, cudaStream_t st) {
+  auto kern = upfirdn2d_cl_sep_kernel<T, TO, EPI>;
+  VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
+  VCN_LAUNCH_CHECK("upfirdn2d_cl_sep_kernel");
+  return VCN_OK;
+}
+
 // Eligibility + launch of the channels-last kernel.  Returns -1 when the configuration is not covered.
 template <typename T>
 int try_launch_cl(const UpfirdnArgs& a, int dtype, int y_dtype, cudaStream_t st) {
@@ -546,6 +822,15 @@ int try_launch_cl(const UpfirdnArgs& a, int dtype, int y_dtype, cudaStream_t st)
   const int tiles_x = (a.out_w + kClTx - 1) / kClTx, tiles_y = (a.out_h + kClTy - 1) / kClTy;
   const size_t smem = (size_t)(kClTy + kF - 1) * (kClTx + kF - 1) * kClCb * 2 + (2 * kClCb + kF * kF) * sizeof(float) + 16;
   dim3 grid((unsigned)((int64_t)tiles_x * tiles_y * a.n), (unsigned)((a.c + kClCb - 1) / kClCb));
+  static const bool use_sep = [] { const char* e = getenv("VCN_FIR_CL_SEP"); return !e || atoi(e) != 0; }();
+  if constexpr (sizeof(T) == 2) {
+    if (use_sep && y_dtype != VCN_F32) {
+      if (!a.scale && !a.noise && !a.act) return launch_cl_sep<T, T, 0>(a, tmap, grid, smem, tiles_x, tiles_y, st);
+      const bool homog = a.act == 0 || (a.act_gain > 0.f && (a.act == VCN_ACT_LINEAR || (a.act == VCN_ACT_LRELU && a.alpha >= 0.f && a.alpha <= 1.f)));
+      if (homog) return launch_cl_sep<T, T, 1>(a, tmap, grid, smem, tiles_x, tiles_y, st);
+      return launch_cl_sep<T, T, 2>(a, tmap, grid, smem, tiles_x, tiles_y, st);
+    }
+  }
   if (y_dtype == VCN_F32) {
     auto kern = upfirdn2d_cl_kernel<T, float>;
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
