@@ -8,7 +8,7 @@
 //       convolution's zero padding (negative coordinates included), TW*TH*TN = 128 rows.
 //   B = one TMA box (64ch, N_TILE, 1) of the packed weights [tap][cout][cin].
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, tcgen05.mma
-// cta_group::1 kind::f16, M=128), warps 2..5 = epilogue (tcgen05.ld of their TMEM lane quarter, then
+// cta_group::1 kind::f16, M=128), warps 2..9 = epilogue (two per lane quarter) (tcgen05.ld of their TMEM lane quarter, then
 // demodulation * d[n,co] + noise, bias + activation + gain + clamp, store).  smem ring of S stages with
 // full/empty mbarriers; tcgen05.commit releases a stage and, after the last k-block, hands TMEM to the epilogue.
 // A "plan" lists the taps; taps are partitioned into up to 4 accumulator groups (TMEM column ranges): the plain
@@ -28,8 +28,8 @@ constexpr int kBlockK = 64;   // bf16 channels per k-block = one 128-byte swizzl
 constexpr int kUmmaK = 16;
 constexpr int kMaxTaps = 9;
 constexpr int kMaxPhases = 4;
-constexpr int kEpilogueWarps = 4;
-constexpr int kThreads = 192;
+constexpr int kEpilogueWarps = 8;  // two warps per TMEM lane quarter, alternating 32-column chunks (the epilogue bounds the small-K tiles)
+constexpr int kThreads = 64 + kEpilogueWarps * 32;
 constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
 
 struct ConvTap {
@@ -348,9 +348,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
   } else {
-    // ===== epilogue: warps 2..5 own TMEM lane quarters (warp % 4) =====
+    // ===== epilogue: warps 2..9, two per TMEM lane quarter (warp % 4), alternating 32-column chunks =====
     const int q = warp & 3;
-    const int et = threadIdx.x - 64;  // 0..127
+    const int et = threadIdx.x - 64;  // 0..kEpilogueWarps*32-1
+    const int cg0 = ((warp - 2) >> 2) * 32, cg_step = (kEpilogueWarps / 4) * 32;  // this warp's 32-column chunks: cg0, cg0 + cg_step, ...
     const int m = q * 32 + lane;
     const int tw_i = m % a.tw;
     const int th_i = (m / a.tw) % a.th;
@@ -379,7 +380,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         mbar_wait(tmem_full_bar + as, aph);
         if (a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
         tcgen05_fence_after();
-        for (int c = 0; c < 256; c += 32) {
+        for (int c = cg0; c < 256; c += cg_step) {
           uint32_t acc[32];
           const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 256 + c);
           if (a.stage_out) {
@@ -463,7 +464,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       mbar_wait(tmem_full_bar + as, aph);
       if (a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
       tcgen05_fence_after();
-      for (int c = 0; c < a.n_tile; c += 32) {
+      for (int c = cg0; c < a.n_tile; c += cg_step) {
         if (tc.co0 + c >= a.cout) break;  // warp-uniform
         uint32_t acc[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * a.n_tile + c);
@@ -613,7 +614,10 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   // Not for the transposed conv: its phase tiles carry 1..4 taps only (9 k-blocks per tile on average at 256 channels), the
   // tile is epilogue-bound either way and the swapped epilogue costs 1.7x per pixel (measured: 0.168 ms vs 0.131 ms).
   a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256 && d->kind != VCN_CONV_TCONV2;
-  if (const char* e = getenv("VCN_CONV_SWAP")) a.swap = a.swap && atoi(e) != 0;
+  if (const char* e = getenv("VCN_CONV_SWAP")) {  // 0: never, 2: also for the transposed conv (experiments)
+    const bool base = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256;
+    a.swap = atoi(e) == 2 ? base : (a.swap && atoi(e) != 0);
+  }
   choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample || a.swap, a.swap ? 256 : 128, 256 / a.a_mul,
               (a.swap && a.grid_w > 16) ? 32 : 1 /* swapped epilogue: 32 consecutive x per TMEM chunk */, &a.tw, &a.th, &a.tn);
   for (a.log_tw = 0; (1 << a.log_tw) < a.tw; ++a.log_tw) {}
