@@ -297,3 +297,49 @@ def test_weight_gradient_vs_oracle(case):
     assert dw.shape == w.shape and dw.dtype == torch.float32
     e = _rel(dw, dw_ref)
     assert e <= TOL_GRAD, e
+
+
+def test_conv2d_resample_golden(golden):
+    """conv2d_resample(impl='cuda') - every branch networks.py uses (plain 3x3 / 1x1, up=2 3x3 = transposed conv + FIR, up=2 1x1,
+    down=2 3x3 = FIR + stride-2 conv, down=2 1x1) - against the outputs and gradients recorded from the reference
+    (conv2d_resample.py:59-154, CONV_CASES).  bf16 tensor-core operands: y <= 1e-2, dx / dw <= 2e-2 (rel-L-inf).  Grouped and
+    asymmetric-padding calls are not on the sm_100a path: loud VcnError, no library fallback."""
+    import viscoin_next_b200 as V
+    from oracle.make_golden import CONV_CASES
+    g = golden("conv_modconv")
+    f4 = g.t("f4", device="cuda")
+    worst = {}
+    for name, (xs, ws, kw, use_f) in CONV_CASES.items():
+        x = g.t(f"conv.{name}.x", device="cuda").requires_grad_(True)
+        w = g.t(f"conv.{name}.w", device="cuda").requires_grad_(True)
+        if name in ("grouped_up2", "asym_pad"):
+            with pytest.raises(V._lib.VcnError):
+                V.conv2d_resample.conv2d_resample(x, w, f=(f4 if use_f else None), **kw)
+            continue
+        y = V.conv2d_resample.conv2d_resample(x, w, f=(f4 if use_f else None), **kw)
+        dx, dw = torch.autograd.grad(y, [x, w], g.t(f"conv.{name}.dy", device="cuda"))
+        e = (_rel(y, g.t(f"conv.{name}.y")), _rel(dx, g.t(f"conv.{name}.dx")), _rel(dw, g.t(f"conv.{name}.dw")))
+        worst[name] = e
+        assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, (name, e)
+    print("conv2d_resample worst y/dx/dw:", {k: tuple("%.1e" % v for v in e) for k, e in worst.items()})
+
+
+@pytest.mark.parametrize("n,cin,cout,res", [(2, 64, 128, 32), (1, 24, 40, 18)])
+def test_conv2d_resample_down2_vs_oracle(n, cin, cout, res):
+    """DiscriminatorBlock-shaped down=2 3x3 convolution (networks.py:571 path: FIR, then the stride-2 tcgen05 GEMM; dx through the
+    transposed-conv kind, dw through the MN-major weight-gradient GEMM with exchanged operand roles) vs the fp32 oracle."""
+    import viscoin_next_b200 as V
+    from oracle import ref_ops as R
+    g = torch.Generator().manual_seed(n * 100 + cin)
+    x = torch.randn(n, cin, res, res, generator=g).requires_grad_(True)
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (3 * cin ** 0.5)).requires_grad_(True)
+    f = R.setup_filter([1, 3, 3, 1])
+    for flip_weight in (True, False):
+        y_ref = R.conv2d_resample(x, w, f=f, down=2, padding=1, flip_weight=flip_weight)
+        dy = torch.randn(y_ref.shape, generator=g)
+        dx_ref, dw_ref = torch.autograd.grad(y_ref, [x, w], dy)
+        xc, wc = x.detach().cuda().requires_grad_(True), w.detach().cuda().requires_grad_(True)
+        y = V.conv2d_resample.conv2d_resample(xc, wc, f=f.cuda(), down=2, padding=1, flip_weight=flip_weight)
+        dx, dw = torch.autograd.grad(y, [xc, wc], dy.cuda())
+        e = (_rel(y, y_ref), _rel(dx, dx_ref), _rel(dw, dw_ref))
+        assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, (flip_weight, e)

@@ -60,7 +60,7 @@ def test_network_mirrors_load_reference_state_dicts(golden):
 def test_patch_install_on_reference_modules():
     sys.path.insert(0, os.path.join(REF, "stylegan2_ada"))
     try:
-        from torch_utils.ops import bias_act as rb, upfirdn2d as ru, fma as rf  # noqa
+        from torch_utils.ops import bias_act as rb, upfirdn2d as ru, fma as rf, conv2d_resample as rc  # noqa
         from training import networks as rn
         import viscoin_next_b200 as V
         orig = rb.bias_act
@@ -69,6 +69,7 @@ def test_patch_install_on_reference_modules():
             assert "torch_utils.ops.bias_act.bias_act" in done and "training.networks.modulated_conv2d" in done
             assert rb.bias_act is V.bias_act.bias_act and ru.upsample2d is V.upfirdn2d.upsample2d
             assert rn.modulated_conv2d is V.modconv.modulated_conv2d and rf.fma is V.fma.fma
+            assert rc.conv2d_resample is V.conv2d_resample.conv2d_resample
             assert "lrelu" in rb.activation_funcs  # table kept
             # a reference layer now routes through the replacement: on CPU tensors that is a loud error, not a fallback
             layer = rn.SynthesisLayer(8, 8, w_dim=16, resolution=8)
@@ -79,3 +80,24 @@ def test_patch_install_on_reference_modules():
         assert rb.bias_act is orig
     finally:
         sys.path.remove(os.path.join(REF, "stylegan2_ada"))
+
+
+def test_conv2d_resample_ref_matches_reference_golden():
+    """The mirror's impl='ref' formulation of conv2d_resample (every branch: plain, 1x1/3x3 up and down, grouped, asymmetric
+    padding through the generic path) reproduces the outputs and gradients recorded from the reference
+    (tests/golden/conv_modconv.npz, oracle/make_golden.py CONV_CASES); impl='cuda' on CPU tensors is a loud error."""
+    import numpy as np
+    import viscoin_next_b200 as V
+    from oracle.make_golden import CONV_CASES
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "conv_modconv.npz"))
+    f4 = torch.from_numpy(g["f4"])
+    for name, (xs, ws, kw, use_f) in CONV_CASES.items():
+        x = torch.from_numpy(g[f"conv.{name}.x"]).requires_grad_(True)
+        w = torch.from_numpy(g[f"conv.{name}.w"]).requires_grad_(True)
+        y = V.conv2d_resample.conv2d_resample(x, w, f=(f4 if use_f else None), impl="ref", **kw)
+        dx, dw = torch.autograd.grad(y, [x, w], torch.from_numpy(g[f"conv.{name}.dy"]))
+        for got, key in ((y, "y"), (dx, "dx"), (dw, "dw")):
+            want = torch.from_numpy(g[f"conv.{name}.{key}"])
+            assert got.shape == want.shape and (got.detach() - want).abs().max() <= 1e-5 * want.abs().max().clamp_min(1), (name, key)
+    with pytest.raises(V._lib.VcnError):
+        V.conv2d_resample.conv2d_resample(torch.randn(1, 4, 8, 8), torch.randn(4, 4, 3, 3), padding=1)

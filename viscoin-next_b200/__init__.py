@@ -7,7 +7,7 @@ installer).  Import as ``viscoin_next_b200`` (the hyphenated directory is not an
 """
 
 from . import _lib  # noqa: F401
-from .host import bias_act, dp, fma, lpips_tap, modconv, networks, upfirdn2d, viscoin_models, viscoin_step  # noqa: F401
+from .host import bias_act, conv2d_resample, dp, fma, lpips_tap, modconv, networks, upfirdn2d, viscoin_models, viscoin_step  # noqa: F401
 from . import patch  # noqa: F401
 
-__all__ = ["_lib", "bias_act", "dp", "fma", "lpips_tap", "modconv", "networks", "patch", "upfirdn2d", "viscoin_models", "viscoin_step"]
+__all__ = ["_lib", "bias_act", "conv2d_resample", "dp", "fma", "lpips_tap", "modconv", "networks", "patch", "upfirdn2d", "viscoin_models", "viscoin_step"]

@@ -8,6 +8,7 @@ first).  ``uninstall()`` restores the originals."""
 import sys
 
 from .host import bias_act as _bias_act
+from .host import conv2d_resample as _conv2d_resample
 from .host import fma as _fma
 from .host import modconv as _modconv
 from .host import upfirdn2d as _upfirdn2d
@@ -18,6 +19,7 @@ _TARGETS = {
     "bias_act": (_bias_act, ["bias_act"]),
     "upfirdn2d": (_upfirdn2d, ["upfirdn2d", "filter2d", "upsample2d", "downsample2d", "setup_filter"]),
     "fma": (_fma, ["fma"]),
+    "conv2d_resample": (_conv2d_resample, ["conv2d_resample"]),
 }
 
 
