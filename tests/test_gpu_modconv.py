@@ -174,8 +174,9 @@ def test_errors():
     x = torch.zeros(1, 8, 4, 4)
     with pytest.raises(_lib.VcnError):
         M.modulated_conv2d(x, torch.zeros(8, 8, 3, 3), torch.ones(1, 8), padding=1)  # CPU tensor: no fallback
-    with pytest.raises(_lib.VcnError):
-        M.modulated_conv2d(x.cuda(), torch.zeros(8, 8, 3, 3).cuda(), torch.ones(1, 8).cuda(), down=2, padding=1)
+    with pytest.raises(_lib.VcnError):  # down = 3 has no sm_100a counterpart (down = 2 is covered, see the down2 tests)
+        M.modulated_conv2d(x.cuda(), torch.zeros(8, 8, 3, 3).cuda(), torch.ones(1, 8).cuda(), down=3, padding=1,
+                           resample_filter=torch.ones(4, 4).cuda())
     w = torch.zeros(8, 8, 3, 3, device="cuda", requires_grad=True)
     y = M.modulated_conv2d(x.cuda(), w, torch.ones(1, 8, device="cuda"), padding=1)
     y.sum().backward()  # weight gradient (vcn_conv_wgrad): x = 0 gives exactly 0
@@ -343,3 +344,27 @@ def test_conv2d_resample_down2_vs_oracle(n, cin, cout, res):
         dx, dw = torch.autograd.grad(y, [xc, wc], dy.cuda())
         e = (_rel(y, y_ref), _rel(dx, dx_ref), _rel(dw, dw_ref))
         assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, (flip_weight, e)
+
+
+@pytest.mark.parametrize("demod,use_noise", [(True, True), (True, False), (False, True)])
+def test_modulated_conv2d_down2_vs_oracle(demod, use_noise):
+    """modulated_conv2d(down=2) (networks.py:27-84 with down>1; not used by the synthesis network, kept for API parity):
+    x*s -> FIR + stride-2 GEMM -> fma(dcoefs, noise), forward and dx / dstyles against the fp32 oracle."""
+    import viscoin_next_b200 as V
+    from oracle import ref_ops as R
+    g = torch.Generator().manual_seed(5)
+    n, cin, cout, res = 2, 32, 48, 16
+    x = torch.randn(n, cin, res, res, generator=g).requires_grad_(True)
+    w = torch.randn(cout, cin, 3, 3, generator=g)
+    s = (torch.randn(n, cin, generator=g) * 0.5 + 1).requires_grad_(True)
+    noise = torch.randn(n, 1, res // 2, res // 2, generator=g) * 0.2 if use_noise else None
+    f = R.setup_filter([1, 3, 3, 1])
+    y_ref = R.modulated_conv2d(x, w, s, noise=noise, down=2, padding=1, resample_filter=f, demodulate=demod, fused_modconv=False)
+    dy = torch.randn(y_ref.shape, generator=g)
+    dx_ref, ds_ref = torch.autograd.grad(y_ref, [x, s], dy)
+    xc, sc = x.detach().cuda().requires_grad_(True), s.detach().cuda().requires_grad_(True)
+    y = V.modconv.modulated_conv2d(xc, w.cuda(), sc, noise=noise.cuda() if use_noise else None, down=2, padding=1,
+                                   resample_filter=f.cuda(), demodulate=demod)
+    dx, ds = torch.autograd.grad(y, [xc, sc], dy.cuda())
+    e = (_rel(y, y_ref), _rel(dx, dx_ref), _rel(ds, ds_ref))
+    assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, e

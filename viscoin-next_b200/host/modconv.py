@@ -426,7 +426,26 @@ def modulated_conv2d(x, weight, styles, noise=None, up=1, down=1, padding=0, res
                                      fused_modconv)
     _check_cuda(x, "modulated_conv2d")
     if down != 1:
-        raise _lib.VcnError("modulated_conv2d(impl='cuda'): down != 1 is not on the synthesis path and is not implemented")
+        # not on the synthesis path: the reference's non-fused branch (networks.py:63-72) composed from this package's
+        # operators - x*s -> conv2d_resample(down) [FIR + stride-2 tcgen05 GEMM] -> fma(y, dcoefs, noise)
+        from . import conv2d_resample as _c2r
+        from . import fma as _fma
+        n, cin = int(x.shape[0]), int(x.shape[1])
+        dcoefs = None
+        if demodulate:
+            wmod = weight.unsqueeze(0) * styles.reshape(n, 1, cin, 1, 1)
+            dcoefs = (wmod.square().sum(dim=[2, 3, 4]) + 1e-8).rsqrt()
+        y = _c2r.conv2d_resample(x * styles.to(x.dtype).reshape(n, cin, 1, 1), weight.to(x.dtype), f=resample_filter, up=up,
+                                 down=down, padding=padding, flip_weight=flip_weight)
+        nz = None
+        if noise is not None:
+            nz = noise.to(y.dtype)
+            nz = nz.reshape(1, 1, *nz.shape) if nz.ndim == 2 else nz
+        if demodulate and nz is not None:
+            return _fma.fma(y, dcoefs.to(y.dtype).reshape(n, -1, 1, 1), nz)
+        if demodulate:
+            return y * dcoefs.to(y.dtype).reshape(n, -1, 1, 1)
+        return y + nz if nz is not None else y
     return modconv_layer(x, weight, styles, noise=noise, bias=None, up=up, padding=padding, resample_filter=resample_filter,
                          demodulate=demodulate, flip_weight=flip_weight, act=None)
 
