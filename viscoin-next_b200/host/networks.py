@@ -64,11 +64,12 @@ class SynthesisLayer(torch.nn.Module):
             self.noise_strength = torch.nn.Parameter(torch.zeros([]))
         self.bias = torch.nn.Parameter(torch.zeros([out_channels]))
 
-    def forward(self, x, w, noise_mode="random", fused_modconv=True, gain=1):
+    def forward(self, x, w, noise_mode="random", fused_modconv=True, gain=1, styles=None):
         assert noise_mode in ["random", "const", "none"]
         in_res = self.resolution // self.up
         assert tuple(x.shape[1:]) == (self.weight.shape[1], in_res, in_res)
-        styles = self.affine(w)
+        if styles is None:  # else: precomputed by SynthesisNetwork._batched_styles (all affine FCs in one batched GEMM)
+            styles = self.affine(w)
         noise = None
         if self.use_noise and noise_mode == "random":
             noise = torch.randn([x.shape[0], 1, self.resolution, self.resolution], device=x.device) * self.noise_strength
@@ -79,9 +80,10 @@ class SynthesisLayer(torch.nn.Module):
                                       resample_filter=self.resample_filter, flip_weight=(self.up == 1),
                                       act=self.activation, gain=self.act_gain * gain, clamp=act_clamp)
 
-    def forward_nhwc(self, act, w, noise_mode="random", gain=1):
+    def forward_nhwc(self, act, w, noise_mode="random", gain=1, styles=None):
         """Resident-activation (bf16 NHWC) variant of forward(); inference only."""
-        styles = self.affine(w)
+        if styles is None:
+            styles = self.affine(w)
         noise = None
         if self.use_noise and noise_mode == "random":
             noise = torch.randn([act.shape[0], 1, self.resolution, self.resolution], device=act.device) * self.noise_strength
@@ -102,14 +104,16 @@ class ToRGBLayer(torch.nn.Module):
         self.bias = torch.nn.Parameter(torch.zeros([out_channels]))
         self.weight_gain = 1 / math.sqrt(in_channels * (kernel_size ** 2))
 
-    def forward(self, x, w, fused_modconv=True):
-        styles = self.affine(w) * self.weight_gain
+    def forward(self, x, w, fused_modconv=True, styles=None):
+        if styles is None:
+            styles = self.affine(w) * self.weight_gain
         return _modconv.modconv_layer(x, self.weight, styles, bias=self.bias, demodulate=False, act="linear",
                                       clamp=self.conv_clamp)
 
-    def forward_nhwc(self, act, w):
+    def forward_nhwc(self, act, w, styles=None):
         """bf16 NHWC activation -> fp32 NCHW RGB: per-sample 1x1 weights, no pass over the activation besides the GEMM."""
-        styles = self.affine(w) * self.weight_gain
+        if styles is None:
+            styles = self.affine(w) * self.weight_gain
         return _modconv.layer_nhwc(act, self.weight, styles, bias=self.bias, demodulate=False, act_name="linear",
                                    clamp=self.conv_clamp, per_sample=True, out_nchw_f32=True)
 
@@ -166,23 +170,24 @@ class SynthesisBlock(torch.nn.Module):
         if in_channels != 0 and architecture == "resnet":
             self.skip = Conv2dLayer(in_channels, out_channels, kernel_size=1, bias=False, up=2, resample_filter=resample_filter)
 
-    def forward_nhwc(self, act, img, ws, noise_mode="random"):
+    def forward_nhwc(self, act, img, ws, noise_mode="random", styles=None):
         """Resident-activation block ('skip' / 'orig' architectures): act stays bf16 NHWC, img fp32 NCHW."""
         w_iter = iter(ws.unbind(dim=1))
+        st = styles or {}
         if self.in_channels == 0:
             act = self.const.to(torch.bfloat16).permute(1, 2, 0).unsqueeze(0).repeat([ws.shape[0], 1, 1, 1]).contiguous()
-            act = self.conv1.forward_nhwc(act, next(w_iter), noise_mode=noise_mode)
+            act = self.conv1.forward_nhwc(act, next(w_iter), noise_mode=noise_mode, styles=st.get(self.conv1))
         else:
-            act = self.conv0.forward_nhwc(act, next(w_iter), noise_mode=noise_mode)
-            act = self.conv1.forward_nhwc(act, next(w_iter), noise_mode=noise_mode)
+            act = self.conv0.forward_nhwc(act, next(w_iter), noise_mode=noise_mode, styles=st.get(self.conv0))
+            act = self.conv1.forward_nhwc(act, next(w_iter), noise_mode=noise_mode, styles=st.get(self.conv1))
         if img is not None:
             img = _upfirdn2d.upsample2d(img, self.resample_filter)
         if self.is_last or self.architecture == "skip":
-            y = self.torgb.forward_nhwc(act, next(w_iter))
+            y = self.torgb.forward_nhwc(act, next(w_iter), styles=st.get(self.torgb))
             img = img.add_(y) if img is not None else y
         return act, img
 
-    def forward(self, x, img, ws, force_fp32=False, fused_modconv=None, resident=False, **layer_kwargs):
+    def forward(self, x, img, ws, force_fp32=False, fused_modconv=None, resident=False, styles=None, **layer_kwargs):
         """resident=True (training on the 'skip' / 'orig' architectures): activations are bf16 channels_last tensors from
         block to block, forward and backward (modconv._ModConvLayer keeps them that way); img stays fp32 NCHW."""
         assert tuple(ws.shape[1:]) == (self.num_conv + self.num_torgb, self.w_dim)
@@ -194,20 +199,21 @@ class SynthesisBlock(torch.nn.Module):
                 x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         elif not resident:
             x = x.to(torch.float32)
+        st = styles or {}
         if self.in_channels == 0:
-            x = self.conv1(x, next(w_iter), **layer_kwargs)
+            x = self.conv1(x, next(w_iter), styles=st.get(self.conv1), **layer_kwargs)
         elif self.architecture == "resnet":
             y = self.skip(x, gain=math.sqrt(0.5))
-            x = self.conv0(x, next(w_iter), **layer_kwargs)
-            x = self.conv1(x, next(w_iter), gain=math.sqrt(0.5), **layer_kwargs)
+            x = self.conv0(x, next(w_iter), styles=st.get(self.conv0), **layer_kwargs)
+            x = self.conv1(x, next(w_iter), gain=math.sqrt(0.5), styles=st.get(self.conv1), **layer_kwargs)
             x = y + x
         else:
-            x = self.conv0(x, next(w_iter), **layer_kwargs)
-            x = self.conv1(x, next(w_iter), **layer_kwargs)
+            x = self.conv0(x, next(w_iter), styles=st.get(self.conv0), **layer_kwargs)
+            x = self.conv1(x, next(w_iter), styles=st.get(self.conv1), **layer_kwargs)
         if img is not None:
             img = _upfirdn2d.upsample2d(img, self.resample_filter)
         if self.is_last or self.architecture == "skip":
-            y = self.torgb(x, next(w_iter)).to(torch.float32)
+            y = self.torgb(x, next(w_iter), styles=st.get(self.torgb)).to(torch.float32)
             img = img.add_(y) if img is not None else y
         return x, img
 
@@ -222,6 +228,7 @@ class SynthesisNetwork(torch.nn.Module):
         # differentiable forward with bf16 channels_last activations between layers (see SynthesisBlock.forward); off by
         # default: the reference's configurations store fp32 (networks.py:382-383 with num_fp16_res = 0)
         self.resident_bf16 = False
+        self.batch_affine = True  # all style FCs of a forward in one batched GEMM while their parameters are frozen
         self.block_resolutions = [2 ** i for i in range(2, self.img_resolution_log2 + 1)]
         channels_dict = {res: min(channel_base // res, channel_max) for res in self.block_resolutions}
         self.num_ws = 0
@@ -234,9 +241,54 @@ class SynthesisNetwork(torch.nn.Module):
                 self.num_ws += block.num_torgb
             setattr(self, f"b{res}", block)
 
+    def _affine_plan(self):
+        """(layer, index into ws, extra gain) of every style FC in forward order (networks.py:463-466 ws split; ToRGB
+        multiplies its styles by weight_gain, networks.py:321)."""
+        plan, w_idx = [], 0
+        for res in self.block_resolutions:
+            b = getattr(self, f"b{res}")
+            k = w_idx
+            if b.in_channels != 0:
+                plan.append((b.conv0, k, 1.0)); k += 1
+            plan.append((b.conv1, k, 1.0)); k += 1
+            if b.is_last or b.architecture == "skip":
+                plan.append((b.torgb, k, b.torgb.weight_gain))
+            w_idx += b.num_conv
+        return plan
+
+    def _batched_styles(self, ws):
+        """All style FCs of one forward (20 at 256^2: `affine` of every SynthesisLayer / ToRGBLayer, networks.py:290,321) as ONE
+        batched GEMM  S[l] = ws[:, idx_l] @ (W_l g_l)^T + b_l g_l  over zero-padded [L, w_dim, Cmax] weights (SURVEY 8(f) N1:
+        ~45 tiny launches per forward become 3).  Only while the affine parameters are frozen (VisCoIN's shared synthesis
+        network, inference): the padded stack is cached per parameter version; ws may require grad (baddbmm's autograd).
+        Returns {layer: styles [N, Cin_l]} or None when the per-layer path must run."""
+        plan = self._affine_plan()
+        params = [p for layer, _, _ in plan for p in (layer.affine.weight, layer.affine.bias)]
+        if not ws.is_cuda or (torch.is_grad_enabled() and any(p.requires_grad for p in params)):
+            return None
+        key = tuple((p.data_ptr(), p._version) for p in params) + (ws.device,)
+        cache = getattr(self, "_affine_cache", None)
+        if cache is None or cache[0] != key:
+            with torch.no_grad():
+                cmax = max(layer.affine.weight.shape[0] for layer, _, _ in plan)
+                wt = torch.zeros([len(plan), self.w_dim, cmax], dtype=torch.float32, device=ws.device)
+                bs = torch.zeros([len(plan), 1, cmax], dtype=torch.float32, device=ws.device)
+                for l, (layer, _, g) in enumerate(plan):
+                    a = layer.affine
+                    c = a.weight.shape[0]
+                    wt[l, :, :c] = (a.weight.float() * (a.weight_gain * g)).t()
+                    bs[l, 0, :c] = a.bias.float() * (a.bias_gain * g)
+                idx = torch.tensor([k for _, k, _ in plan], dtype=torch.long, device=ws.device)
+            cache = (key, wt, bs, idx)
+            self._affine_cache = cache
+        _, wt, bs, idx = cache
+        s_all = torch.baddbmm(bs, ws.index_select(1, idx).transpose(0, 1), wt)  # [L, N, Cmax]
+        return {layer: s_all[l, :, :layer.affine.weight.shape[0]] for l, (layer, _, _) in enumerate(plan)}
+
     def forward(self, ws, **block_kwargs):
         assert tuple(ws.shape[1:]) == (self.num_ws, self.w_dim)
         ws = ws.to(torch.float32)
+        styles = self._batched_styles(ws) if self.batch_affine else None
         block_ws, w_idx = [], 0
         for res in self.block_resolutions:
             block = getattr(self, f"b{res}")
@@ -249,9 +301,9 @@ class SynthesisNetwork(torch.nn.Module):
             and all(getattr(self, f"b{res}").architecture in ("skip", "orig") for res in self.block_resolutions)
         for res, cur_ws in zip(self.block_resolutions, block_ws):
             if fast:  # inference: activations stay resident as bf16 NHWC, no per-layer layout / modulation passes
-                x, img = getattr(self, f"b{res}").forward_nhwc(x, img, cur_ws, **block_kwargs)
+                x, img = getattr(self, f"b{res}").forward_nhwc(x, img, cur_ws, styles=styles, **block_kwargs)
             else:
-                x, img = getattr(self, f"b{res}")(x, img, cur_ws, resident=self.resident_bf16, **block_kwargs)
+                x, img = getattr(self, f"b{res}")(x, img, cur_ws, resident=self.resident_bf16, styles=styles, **block_kwargs)
         return img
 
 
