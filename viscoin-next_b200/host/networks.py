@@ -64,6 +64,21 @@ class SynthesisLayer(torch.nn.Module):
             self.noise_strength = torch.nn.Parameter(torch.zeros([]))
         self.bias = torch.nn.Parameter(torch.zeros([out_channels]))
 
+    def _const_noise(self):
+        """noise_const * noise_strength (networks.py:296); cached per (buffer, parameter) version while the strength is frozen."""
+        ns = self.noise_strength
+        if ns.requires_grad and torch.is_grad_enabled():
+            return self.noise_const * ns
+        key = (self.noise_const.data_ptr(), self.noise_const._version, ns.data_ptr(), ns._version)
+        hit = getattr(self, "_noise_cache", None)
+        if hit is None or hit[0] != key:
+            if ns.is_cuda and torch.cuda.is_current_stream_capturing():
+                return self.noise_const * ns  # a tensor born inside a capture belongs to that graph's pool: do not keep it
+            with torch.no_grad():
+                hit = (key, self.noise_const * ns)
+            self._noise_cache = hit
+        return hit[1]
+
     def forward(self, x, w, noise_mode="random", fused_modconv=True, gain=1, styles=None):
         assert noise_mode in ["random", "const", "none"]
         in_res = self.resolution // self.up
@@ -74,7 +89,7 @@ class SynthesisLayer(torch.nn.Module):
         if self.use_noise and noise_mode == "random":
             noise = torch.randn([x.shape[0], 1, self.resolution, self.resolution], device=x.device) * self.noise_strength
         if self.use_noise and noise_mode == "const":
-            noise = self.noise_const * self.noise_strength
+            noise = self._const_noise()
         act_clamp = self.conv_clamp * gain if self.conv_clamp is not None else None
         return _modconv.modconv_layer(x, self.weight, styles, noise=noise, bias=self.bias, up=self.up, padding=self.padding,
                                       resample_filter=self.resample_filter, flip_weight=(self.up == 1),
@@ -88,7 +103,7 @@ class SynthesisLayer(torch.nn.Module):
         if self.use_noise and noise_mode == "random":
             noise = torch.randn([act.shape[0], 1, self.resolution, self.resolution], device=act.device) * self.noise_strength
         if self.use_noise and noise_mode == "const":
-            noise = self.noise_const * self.noise_strength
+            noise = self._const_noise()
         act_clamp = self.conv_clamp * gain if self.conv_clamp is not None else None
         return _modconv.layer_nhwc(act, self.weight, styles, noise=noise, bias=self.bias, up=self.up,
                                    resample_filter=self.resample_filter, act_name=self.activation,
@@ -269,6 +284,8 @@ class SynthesisNetwork(torch.nn.Module):
         key = tuple((p.data_ptr(), p._version) for p in params) + (ws.device,)
         cache = getattr(self, "_affine_cache", None)
         if cache is None or cache[0] != key:
+            if torch.cuda.is_current_stream_capturing():
+                return None  # build the stack eagerly (warm-up), never inside a capture
             with torch.no_grad():
                 cmax = max(layer.affine.weight.shape[0] for layer, _, _ in plan)
                 wt = torch.zeros([len(plan), self.w_dim, cmax], dtype=torch.float32, device=ws.device)
