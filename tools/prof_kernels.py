@@ -125,6 +125,15 @@ if "bias" in what:
     timed("bias_act lrelu fwd f32 [8,128,256,256]", lambda: V.bias_act.bias_act(x, b, act="lrelu"), 2 * x.numel() * 4, "GB/s")
 
 if "bwdcl" in what:
+    for n, c, r in [(16, 512, 16), (16, 512, 32)]:  # low-resolution layers: latency-bound, few CTAs
+        y = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+        dy = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+        d = torch.rand(n, c, device=dev) + 0.5
+        b = torch.randn(c, device=dev)
+        epi, hold = M.make_epilogue(scale=d, bias=b, act="lrelu")
+        timed("bwd_pack_cl bf16 [%d,%d,%d,%d]" % (n, c, r, r), lambda: M.bwd_pack(dy, y, epi, True, True), 3 * y.numel() * 2, "GB/s")
+        dxh = dy.clone()
+        timed("bwd_finish_cl bf16 [%d,%d,%d,%d]" % (n, c, r, r), lambda: M.bwd_finish_cl(dxh, y, d, True), 3 * y.numel() * 2, "GB/s")
     n, c, r = 16, 128, 256
     y = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
     dy = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)

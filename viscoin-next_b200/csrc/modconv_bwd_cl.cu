@@ -211,6 +211,9 @@ int launch(BwdClArgs& a, int dtype, cudaStream_t st, const char* name) {
   // about 16 CTAs per SM in total, at least 32 pixel iterations each
   int chunk = hw;
   while (chunk > 32 * rows && (int64_t)a.n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 16) chunk = (chunk + 1) / 2;
+  // low resolutions (4^2..32^2 at 512 channels): 16-32 CTAs walking 64 dependent iterations each took 25-36 us for a
+  // few MB - shorter chunks until every SM has two CTAs
+  while (chunk > 8 * rows && (int64_t)a.n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 2) chunk = (chunk + 1) / 2;
   a.chunk = chunk;
   dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)a.n);
   if (!FINISH && a.fast_act) {
