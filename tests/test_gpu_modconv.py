@@ -368,3 +368,23 @@ def test_modulated_conv2d_down2_vs_oracle(demod, use_noise):
     dx, ds = torch.autograd.grad(y, [xc, sc], dy.cuda())
     e = (_rel(y, y_ref), _rel(dx, dx_ref), _rel(ds, ds_ref))
     assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, e
+
+
+@pytest.mark.parametrize("shape", [(3, 128, 37, 21), (2, 512, 4, 4), (2, 64, 16, 16), (2, 24, 9, 9), (1, 2048, 3, 5)])
+@pytest.mark.parametrize("with_styles", [True, False])
+def test_modulate_pack_channels_last_exact(shape, with_styles):
+    """vcn_modulate_pack on a resident bf16 channels_last activation (rows kernel for power-of-two channel counts, generic
+    kernel otherwise): xhat[n,h,w,c] = bf16(x * s[n,c]) - one fp32 multiply and one rounding, bit-exact against torch."""
+    M = _M()
+    g = torch.Generator().manual_seed(sum(shape))
+    n, c, h, w = shape
+    x = torch.randn(shape, generator=g).bfloat16().cuda().contiguous(memory_format=torch.channels_last)
+    s = (torch.randn(n, c, generator=g) + 1).cuda() if with_styles else None
+    got = M.modulate_pack(x, s)
+    want = x.float() * (s[:, :, None, None] if with_styles else 1.0)
+    want = want.bfloat16().permute(0, 2, 3, 1).contiguous()
+    c_pad = (c + 7) // 8 * 8
+    assert got.shape == (n, h, w, c_pad)
+    assert torch.equal(got[..., :c], want)
+    if c_pad > c:
+        assert float(got[..., c:].abs().max()) == 0.0

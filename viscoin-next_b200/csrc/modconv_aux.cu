@@ -94,6 +94,41 @@ __global__ void __launch_bounds__(256) modulate_pack_cl_kernel(const T* __restri
   }
 }
 
+// Dense rows (stride_h == w * stride_w), 16-bit input, cin == cin_pad a power of two <= 2048, vector-aligned: a thread owns
+// ONE channel group for the whole launch (its 8 style factors stay in registers), walks pixels with a stride of
+// 256 / groups, four 16-byte loads in flight - no 64-bit divisions and no per-vector style loads (the generic kernel above
+// spends ~3 int64 div/mod and 8 scalar loads per 16-byte vector).  grid = (pixel chunks, n).
+template <typename T>
+__global__ void __launch_bounds__(256) modulate_pack_cl_rows_kernel(const T* __restrict__ x, int64_t xs_n, int64_t xs_w,
+                                                                    const float* __restrict__ styles,
+                                                                    __nv_bfloat16* __restrict__ xhat, int cin, int hw, int chunk) {
+  const int groups = cin >> 3, rows = 256 / groups;
+  const int g = threadIdx.x % groups, row = threadIdx.x / groups;
+  const int n = blockIdx.y, c = g * 8;
+  float sc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sc[k] = styles ? styles[(int64_t)n * cin + c + k] : 1.f;
+  const T* src = x + n * xs_n + c;
+  __nv_bfloat16* dst = xhat + (int64_t)n * hw * cin + c;
+  const int p_end = min(hw, (int)(blockIdx.x + 1) * chunk);
+  constexpr int kBatch = 4;
+  for (int p = blockIdx.x * chunk + row; p < p_end; p += kBatch * rows) {
+    Vec16<T> in[kBatch];
+#pragma unroll
+    for (int b = 0; b < kBatch; ++b)
+      if (p + b * rows < p_end) in[b] = ld_stream<T>(src + (int64_t)(p + b * rows) * xs_w);
+#pragma unroll
+    for (int b = 0; b < kBatch; ++b) {
+      if (p + b * rows < p_end) {
+        Vec16<__nv_bfloat16> o;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o.v[k] = __float2bfloat16_rn(to_acc<T>(in[b].v[k]) * sc[k]);
+        *reinterpret_cast<Vec16<__nv_bfloat16>*>(dst + (int64_t)(p + b * rows) * cin) = o;
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) pack_weights_kernel(const T* __restrict__ w, int cout, int cin, int taps,
                                                            int transpose_io, __nv_bfloat16* __restrict__ wt, int rows,
@@ -153,6 +188,7 @@ struct BwdPackArgs {
   __nv_bfloat16* dy0; float* gsum; float* db;
   int n, c, c_pad, h, w;
   int act; float alpha, gain, clamp;
+  int subs;  // 32-pixel sub-tiles per CTA
 };
 
 // dz = bias_act'(dy; y), r = act^-1(y) - bias - noise (= y0 * d), gsum[n,c] += sum_p dz*r, db[c] += sum_p dz,
@@ -169,8 +205,8 @@ __global__ void __launch_bounds__(256) modconv_bwd_pack_kernel(const BwdPackArgs
   float gacc[8], bacc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) gacc[i] = bacc[i] = 0.f;
-  for (int sub = 0; sub < 4; ++sub) {
-    const int p0 = (blockIdx.x * 4 + sub) * 32;
+  for (int sub = 0; sub < a.subs; ++sub) {
+    const int p0 = (blockIdx.x * a.subs + sub) * 32;
     if (p0 >= hw) break;  // block-uniform
     const int p = p0 + lane;
     const int py = p / a.w, px = p - py * a.w;
@@ -325,6 +361,19 @@ int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* 
     if (grid > cap) grid = cap;
     const int64_t vq = 16 / (int64_t)sizeof(T);
     const int vec_in = aligned16(x) && xs[0] % vq == 0 && xs[2] % vq == 0 && xs[3] % vq == 0;
+    if constexpr (sizeof(T) == 2) {
+      const int groups = cin_pad / 8;
+      const bool pow2 = (groups & (groups - 1)) == 0 && groups <= 256;
+      if (vec_in && cin == cin_pad && pow2 && xs[2] == (int64_t)w * xs[3] && (int64_t)h * w <= 0x7fffffff) {
+        const int hw = h * w, rows = 256 / groups;
+        int chunk = hw;  // about 16 CTAs per SM in total, at least 16 pixel iterations each
+        while (chunk > 16 * rows && (int64_t)n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 16) chunk = (chunk + 1) / 2;
+        dim3 g2((unsigned)((hw + chunk - 1) / chunk), (unsigned)n);
+        modulate_pack_cl_rows_kernel<T><<<g2, 256, 0, st>>>(px, xs[0], xs[3], styles, po, cin, hw, chunk);
+        VCN_LAUNCH_CHECK("modulate_pack_cl_rows_kernel");
+        return VCN_OK;
+      }
+    }
     modulate_pack_cl_kernel<T><<<(unsigned)grid, 256, 0, st>>>(px, xs[0], xs[2], xs[3], styles, po, n, cin, cin_pad, h, w, vec_in);
     VCN_LAUNCH_CHECK("modulate_pack_cl_kernel");
     return VCN_OK;
@@ -437,7 +486,11 @@ int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t
               "modconv_bwd_pack: fused backward supports no activation, linear, or lrelu with alpha != 0 (got act %d)", a.act);
   VCN_REQUIRE(a.act == 0 || a.gain != 0.f, "modconv_bwd_pack: gain must be non-zero");
   VCN_REQUIRE((a.act == 0 && !gsum) || y, "modconv_bwd_pack: y is required with an activation or when gsum is requested");
-  dim3 grid((unsigned)((h * w + 127) / 128), (unsigned)((c_pad + 63) / 64), (unsigned)n);
+  // 128 pixels per CTA; few channels (ToRGB: 3): every CTA ends in one atomicAdd per channel on the SAME c addresses of db
+  // (8192 CTAs on 3 addresses took 180 us at 256^2) - longer pixel runs per CTA while the machine stays covered
+  a.subs = 4;
+  while (a.subs < 64 && c <= 16 && (int64_t)n * ((h * w + 32 * a.subs - 1) / (32 * a.subs)) > (int64_t)sm_count() * 4) a.subs *= 2;
+  dim3 grid((unsigned)((h * w + 32 * a.subs - 1) / (32 * a.subs)), (unsigned)((c_pad + 63) / 64), (unsigned)n);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   {  // 16-bit channels-last operands: streaming kernel of modconv_bwd_cl.cu
     const int rc = bwd_pack_cl_try(dy, y, dtype, a.dys, a.ys, epi, dy0, gsum, db, n, c, c_pad, h, w, a.act, a.alpha, a.gain,
