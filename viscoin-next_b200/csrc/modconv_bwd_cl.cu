@@ -61,8 +61,10 @@ __device__ __forceinline__ void group_reduce_add(float (*red)[8], const float (&
   }
 }
 
+// Occupancy is what these passes run on (ncu: long_scoreboard stalls at 16 warps per SM; the same loop without
+// accumulators - modulate_pack_cl_rows_kernel, 8 CTAs per SM - streams at the HBM peak): small batches, 3-4 CTAs per SM.
 template <typename T, bool FINISH, bool FAST>
-__global__ void __launch_bounds__(256, 2) modconv_bwd_cl_kernel(const BwdClArgs a) {
+__global__ void __launch_bounds__(256, FINISH ? 4 : (FAST ? 3 : 2)) modconv_bwd_cl_kernel(const BwdClArgs a) {
   __shared__ float red[256][8];
   const int tid = threadIdx.x, n = blockIdx.y;
   const int groups = a.c_pad >> 3;        // <= 256
@@ -141,47 +143,30 @@ __global__ void __launch_bounds__(256, 2) modconv_bwd_cl_kernel(const BwdClArgs 
   constexpr int kBatch = 2;
   const bool fast = va && (!pb || vb) && a.as[2] == (int64_t)a.w * a.as[3] && (!pb || a.bs[2] == (int64_t)a.w * a.bs[3]);
   if (active && fast) {
-    // software pipeline: the loads of the next kBatch pixels are in flight while this batch is processed (a burst of loads
-    // followed by a burst of math left HBM idle half of the time: 0.41 / 0.60 of the peak at 16 warps per SM)
     const int64_t sa = a.as[3], sb = a.bs[3];
-    const int step = kBatch * rows;
-    Vec16<T> ru[2][kBatch], rv[2][kBatch];
-    float nz[2][kBatch];
-    auto load = [&](auto B, int p) {
-      constexpr int bf = decltype(B)::value;
+    for (int p = blockIdx.x * a.chunk + row; p < p_end; p += kBatch * rows) {
+      Vec16<T> ru[kBatch], rv[kBatch];
+      float nz[kBatch];
 #pragma unroll
       for (int b = 0; b < kBatch; ++b) {
         const int pp = p + b * rows;
         if (pp < p_end) {
           // finish rewrites dxhat in place: a plain load there, the non-coherent streaming path for read-only data
-          ru[bf][b] = FINISH ? *reinterpret_cast<const Vec16<T>*>(pa + pp * sa) : ld_stream<T>(pa + pp * sa);
-          if (pb) rv[bf][b] = ld_stream<T>(pb + pp * sb);
-          nz[bf][b] = noise_n ? __ldg(noise_n + pp) : 0.f;
+          ru[b] = FINISH ? *reinterpret_cast<const Vec16<T>*>(pa + pp * sa) : ld_stream<T>(pa + pp * sa);
+          if (pb) rv[b] = ld_stream<T>(pb + pp * sb);
+          nz[b] = noise_n ? __ldg(noise_n + pp) : 0.f;
         }
       }
-    };
-    auto proc = [&](auto B, int p) {
-      constexpr int bf = decltype(B)::value;
 #pragma unroll
       for (int b = 0; b < kBatch; ++b) {
         const int pp = p + b * rows;
         if (pp < p_end) {
           float u[8], v[8];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) { u[k] = to_acc<T>(ru[bf][b].v[k]); v[k] = pb ? to_acc<T>(rv[bf][b].v[k]) : 0.f; }
-          pixel(u, v, nz[bf][b], pp * sa, pp);
+          for (int k = 0; k < 8; ++k) { u[k] = to_acc<T>(ru[b].v[k]); v[k] = pb ? to_acc<T>(rv[b].v[k]) : 0.f; }
+          pixel(u, v, nz[b], pp * sa, pp);
         }
       }
-    };
-    using I0 = std::integral_constant<int, 0>;
-    using I1 = std::integral_constant<int, 1>;
-    int p = blockIdx.x * a.chunk + row;
-    if (p < p_end) load(I0{}, p);
-    for (; p < p_end; p += 2 * step) {
-      if (p + step < p_end) load(I1{}, p + step);
-      proc(I0{}, p);
-      if (p + 2 * step < p_end) load(I0{}, p + 2 * step);
-      if (p + step < p_end) proc(I1{}, p + step);
     }
   } else if (active) {
     for (int p = blockIdx.x * a.chunk + row; p < p_end; p += rows) {
