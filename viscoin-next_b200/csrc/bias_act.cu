@@ -337,6 +337,7 @@ int run(BiasActArgs a, void* db, void* ws, size_t ws_bytes, cudaStream_t st) {
   if (aligned) {
     if (a.act == VCN_ACT_LRELU) rc = launch_flat<T, VCN_ACT_LRELU>(a, st);
     else if (a.act == VCN_ACT_LINEAR) rc = launch_flat<T, VCN_ACT_LINEAR>(a, st);
+    else if (a.act == VCN_ACT_RELU) rc = launch_flat<T, VCN_ACT_RELU>(a, st);  // conv + bias + ReLU of the frozen f / VGG
     else rc = launch_flat<T, 0>(a, st);
     if (rc) return rc;
   } else {

@@ -71,6 +71,45 @@ def fold_batchnorm(model):
     return n
 
 
+class ConvBiasAct(nn.Conv2d):
+    """nn.Conv2d whose bias add and ReLU run as ONE ``vcn_bias_act`` pass over the convolution output (cuDNN adds the bias
+    with a separate elementwise kernel and the ReLU is a third one: two extra read+write passes over every activation of
+    the frozen ResNet-50 / VGG-16).  Same parameters and ``state_dict`` names as the Conv2d it replaces (the instance's
+    class is swapped in place by ``fuse_conv_bias_relu``); CPU tensors take the plain torch path."""
+    vcn_act = "relu"
+
+    def forward(self, x):
+        if not x.is_cuda or self.bias is None or self.padding_mode != "zeros":
+            y = super().forward(x)
+            return torch.relu(y) if self.vcn_act == "relu" else y
+        from . import bias_act as _bias_act
+        y = torch.nn.functional.conv2d(x, self.weight, None, self.stride, self.padding, self.dilation, self.groups)
+        return _bias_act.bias_act(y, self.bias.to(y.dtype), act=self.vcn_act)
+
+
+def fuse_conv_bias_relu(model):
+    """Frozen eval-mode networks only.  torchvision VGG (`Conv2d, ReLU` neighbours in a Sequential) and the HF ResNet after
+    ``fold_batchnorm`` (`ResNetConvLayer.convolution / .activation`): the Conv2d becomes a ``ConvBiasAct`` and the ReLU module
+    an Identity.  Returns the number of fused pairs."""
+    n = 0
+    for m in model.modules():
+        if isinstance(m, nn.Sequential):
+            names = list(m._modules.keys())
+            for a, b in zip(names, names[1:]):
+                ca, rb = m._modules[a], m._modules[b]
+                if type(ca) is nn.Conv2d and ca.bias is not None and isinstance(rb, nn.ReLU):
+                    ca.__class__ = ConvBiasAct
+                    m._modules[b] = nn.Identity()
+                    n += 1
+        conv, act = getattr(m, "convolution", None), getattr(m, "activation", None)
+        if type(conv) is nn.Conv2d and conv.bias is not None and isinstance(act, nn.ReLU) \
+                and isinstance(getattr(m, "normalization", None), nn.Identity):
+            conv.__class__ = ConvBiasAct
+            m.activation = nn.Identity()
+            n += 1
+    return n
+
+
 class ConceptExtractor(nn.Module):
     def __init__(self, n_concepts=256, latent_channels=512, input_channels1=512, input_channels2=1024, input_channels3=2048):
         super().__init__()

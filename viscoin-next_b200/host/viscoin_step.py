@@ -16,6 +16,7 @@ is frozen and in eval mode (:114-115).  Data parallelism = batch sharding only: 
 """
 
 import itertools
+import os
 
 import torch
 import torch.nn.functional as F
@@ -134,6 +135,11 @@ class VisCoINTrainer:
             _models.fold_batchnorm(self.classifier)
             if self.channels_last:
                 self.classifier.to(memory_format=torch.channels_last)
+        if self.device.type == "cuda" and os.environ.get("VCN_FUSE_BIAS_RELU", "0") == "1":
+            # frozen f (after the BN fold) and VGG-16: conv bias + ReLU in one vcn_bias_act pass instead of two torch kernels
+            if self.fold_bn:
+                _models.fuse_conv_bias_relu(self.classifier)
+            _models.fuse_conv_bias_relu(self.lpips)
         self.deterministic = deterministic
         self.viscoin_gan.synthesis.resident_bf16 = self.amp is not None  # bf16 run: activations stay bf16 NHWC
         self.synthesis_kwargs = {}  # e.g. {'noise_mode': 'const'} for parity runs; the reference passes none (:193)
