@@ -1,15 +1,18 @@
 #!/usr/bin/env python
 """bench.py - the measurement contract of this repo (see DESIGN.md "Measurement").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload opsweep|synthesis] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload trainstep|synthesis|opsweep] [--impl ours|reference|reference-gpu]
 
 One "step" = one pass of the hot path over one batch of synthetic input.  Prints ONE JSON line (rank 0).
   value     whole-job throughput with inputs resident in HBM (device-timed, CUDA events, max over ranks)
   e2e       same metric through the public operator API with HOST (pinned) buffers: H2D + op + D2H timed
   roofline  dominant kernel: algorithmic bytes per launch / CUDA-event duration vs MEASURED_PEAKS.json
   cpu_baseline  the oracle (CPU restatement of the reference ref path) timed on a bounded sample, rank 0, N=1
+  roofline_others  every other hand-written kernel alone at its BASELINE shape (+ the cuDNN kernel of the same layer)
 `--impl reference` times the reference's CPU implementation (the oracle port; /root/reference does not exist on
-the GPU box) on the same workload with all host threads.
+the GPU box) on the same workload - the FULL batch, both Adam updates included - with all host threads.
+`--impl reference-gpu` (secondary baseline) runs the UNMODIFIED reference modules staged in the
+git-ignored oracle/_ref (its own CUDA plugins JIT-built for sm_100a + cuDNN convolutions, fp32/TF32, eager) on the GPU.
 """
 
 import argparse
@@ -32,7 +35,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-gpu"])
     ap.add_argument("--workload", default=os.environ.get("VCN_BENCH_WORKLOAD", "auto"))
     ap.add_argument("--batch", type=int, default=8, help="images per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -258,6 +261,16 @@ class OpSweep:
                 "peak_source": peaks["src"] + " (burst copy)", "traffic": None, "alg_bytes_per_launch": alg,
                 "avg_launch_ms": round(ms, 5)}
 
+    def reference_gpu_setup(self, device, seed):
+        """The reference's own plugins (bias_act.cu:23-147, upfirdn2d.cu:97-200) through its operator API, impl='cuda'."""
+        from oracle import stage_ref
+        import types
+        ref = stage_ref.load_plugins()
+        self.setup(device, seed)
+        self.V = types.SimpleNamespace(upfirdn2d=ref.upfirdn2d, bias_act=ref.bias_act)
+        self.f = ref.upfirdn2d.setup_filter([1, 3, 3, 1], device=device)
+        return "reference plugins bias_act.cu / upfirdn2d.cu (oracle/_ref, unmodified, sm_100a JIT) through torch_utils.ops, impl='cuda'"
+
     # --- CPU (oracle) -------------------------------------------------------------------------------
     def cpu_step(self, n_sample, seed=0):
         """The oracle's restatement of the reference ref path on a sample of n_sample images per tensor."""
@@ -288,7 +301,7 @@ class Synthesis:
 
     def __init__(self, batch):
         self.n = batch
-        self.name = "SynthesisNetwork forward %dx%d batch %d/GPU, random-init, noise const 0.1, fp32 I/O + bf16 MMA operands" % (self.RES, self.RES, batch)
+        self.name = "SynthesisNetwork forward %dx%d batch %d/GPU, random-init, noise const 0.1, fp32 I/O, bf16-resident activations + bf16 MMA operands" % (self.RES, self.RES, batch)
 
     def units_per_step(self):
         return float(self.n)
@@ -300,7 +313,9 @@ class Synthesis:
             for name, p in S.named_parameters():
                 if name.endswith("noise_strength"):
                     p.fill_(0.1)
-        return S.to(device).eval().requires_grad_(False)
+        S = S.to(device).eval().requires_grad_(False)
+        S.resident_bf16 = device.type == "cuda"  # bf16 NHWC activations between layers (stated in `config.workload`)
+        return S
 
     def setup(self, device, seed):
         import viscoin_next_b200 as V
@@ -352,6 +367,21 @@ class Synthesis:
                 "peak_source": peaks["src"] + " (burst cuBLAS bf16)", "traffic": None, "alg_flop_per_launch": flop,
                 "avg_launch_ms": round(ms, 5)}
 
+    def reference_gpu_setup(self, device, seed):
+        """Unmodified reference SynthesisNetwork (oracle/_ref) with its plugins + cuDNN, fp32, eval mode (fused grouped
+        convolution branch, networks.py:74-84), same weights as `_build`."""
+        from oracle import stage_ref
+        import viscoin_next_b200 as V
+        ref = stage_ref.load_plugins()
+        mine = self._build(torch.device("cpu"), V.networks)
+        S = ref.networks.SynthesisNetwork(w_dim=512, img_resolution=self.RES, img_channels=3)
+        S.load_state_dict(mine.state_dict(), strict=True)
+        self.S = S.to(device).eval().requires_grad_(False)
+        g = torch.Generator(device=device).manual_seed(seed)
+        self.ws = torch.randn(self.n, self.S.num_ws, 512, device=device, generator=g)
+        self.graphed = None
+        return "reference SynthesisNetwork (oracle/_ref, unmodified) + reference CUDA plugins (sm_100a JIT) + cuDNN, fp32/TF32, eval mode, eager"
+
     def cpu_step(self, n_sample, seed=0):
         from oracle import ref_net as RN
         if not hasattr(self, "_cpu_sd"):
@@ -375,6 +405,9 @@ class TrainStep:
     unit = "steps/s (x GPUs: one step = 8 real + 8 fake images on each GPU)"
     dtype = "bf16"
     l2_note = "activations per step (GBs) far exceed L2; no flush needed"
+    arithmetic_note = ("bf16 operands + bf16 NHWC storage with fp32 accumulation (synthesis tensor-core GEMMs; f / Psi / VGG-16 under "
+                       "bf16 autocast), fp32 master weights, losses and Adam; the reference runs fp32 (TF32 convolutions on a GPU)")
+    step_flop = None  # set in __init__ (6.3 TFLOP at 8 + 8 images)
 
     parallelism_note = "dp%d (batch-sharded replicas; one NCCL mean all-reduce of the 96.1 M trainable gradients per step, bucketed and overlapped with backward)"
 
@@ -382,6 +415,10 @@ class TrainStep:
         self.n = batch
         self.name = ("VisCoIN ensemble train step (ResNet-50 f + Psi + Theta + G reconstruction losses + LPIPS-VGG16, Adam), "
                      "%d real + %d fake images/GPU at 256x256, random-init, i > cd_fid_iteration (all six losses)" % (batch, batch))
+
+        # synthesis 90.24 GF/img x (n fake fwd + 2n fwd + 2n dgrad), ResNet-50 10.68 x (4n fwd + 2n bwd),
+        # VGG-16 40.09 x (4n + 2n), Psi 5.49 x 2n x 3  ->  6.3 TFLOP at n = 8
+        self.step_flop = (90.24 * 5 * batch + 10.68 * 6 * batch + 40.09 * 6 * batch + 5.49 * 6 * batch) * 1e9
 
     def units_per_step(self):
         return 1.0
@@ -429,7 +466,8 @@ class TrainStep:
     RES = 256
 
     def cpu_step(self, n_sample, seed=0):
-        """Oracle port of the same step on the host cores: n_sample real + n_sample fake images, forward + backward."""
+        """Oracle port of the same step on the host cores: n_sample real + n_sample fake images, forward + backward + BOTH
+        Adam updates (viscoin/training/viscoin.py:163-223) - like for like with the GPU step."""
         from oracle import ref_step as RS
         if not hasattr(self, "_cpu_state"):
             import viscoin_next_b200 as V
@@ -444,14 +482,16 @@ class TrainStep:
             st["lpips_convs"] = [(l.weight.detach(), l.bias.detach()) for s in lp.slices for l in s if isinstance(l, torch.nn.Conv2d)]
             st["lpips_lins"] = [p.detach() for p in lp.lins]
             st["_f"] = RS.make_classifier(st["classifier"])
+            main, gan = [], []
             for grp in ("concept_extractor", "explainer"):
                 for v in st[grp].values():
                     if v.is_floating_point():
-                        v.requires_grad_(True)
+                        main.append(v.requires_grad_(True))
             for k, v in st["viscoin_gan"].items():
                 if k.startswith("mapping."):
-                    v.requires_grad_(True)
+                    gan.append(v.requires_grad_(True))
             self._cpu_state = st
+            self._cpu_opts = (torch.optim.Adam(main, lr=1e-4), torch.optim.Adam(gan, lr=1e-4))  # viscoin.py:130-134
         st = self._cpu_state
         from oracle import ref_net as RN
         g = torch.Generator().manual_seed(seed)
@@ -463,11 +503,63 @@ class TrainStep:
         out = RS.step_losses(st, real, labels, fake, noise_mode="random")
         out.pop("_rebuilt")
         sum(out.values()).backward()
-        dt = time.perf_counter() - t0
-        for grp in ("concept_extractor", "explainer", "viscoin_gan"):
-            for v in st[grp].values():
-                v.grad = None
-        return dt
+        for opt in self._cpu_opts:
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+        return time.perf_counter() - t0
+
+    # --- the reference's own modules on the GPU (secondary baseline) ------------------------------------
+    def reference_gpu_setup(self, device, seed):
+        """The UNMODIFIED reference modules (oracle/_ref: Generator / GeneratorAdapted / ConceptExtractor / Explainer with
+        their CUDA plugins + cuDNN) in the restated iteration, fp32 parameters, torch's default TF32 convolutions, eager -
+        the way `python main.py train viscoin` runs them.  f = HF ResNet-50 and LPIPS-VGG16 (torch formulation) as in the
+        reference; none of this repo's kernels is on the path."""
+        from oracle import stage_ref
+        import viscoin_next_b200 as V
+        ref = stage_ref.load_plugins()
+        VM = V.viscoin_models
+        torch.manual_seed(0)
+        cls = VM.Classifier(200)
+        psi = ref.concept_extractors.ConceptExtractor()
+        theta = ref.explainers.Explainer(n_classes=200)
+        G = ref.networks.Generator(z_dim=512, c_dim=0, w_dim=512, img_resolution=256, img_channels=3, mapping_kwargs={"num_layers": 2})
+        GA = ref.gan.GeneratorAdapted.from_gan(G)
+        lp = VM.LPIPS()
+        lp.fused = False
+        cls = cls.to(device)
+        with torch.no_grad():
+            fakes = G.to(device)(torch.randn(4, 512, generator=torch.Generator().manual_seed(0)).to(device), None).float()
+        VM.calibrate_batchnorm(cls, torch.cat([torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(1)).to(device), fakes]))
+        self.tr = V.viscoin_step.VisCoINTrainer(device, amp=None, channels_last=False, fold_bn=False, fused_adam=False,
+                                                models=(cls, psi, theta, G, GA, lp))
+        g = torch.Generator(device=device).manual_seed(seed)
+        self.real = torch.randn(self.n, 3, 256, 256, device=device, generator=g)
+        self.labels = torch.randint(0, 200, (self.n,), device=device, generator=g)
+        self.zgen = torch.Generator().manual_seed(seed)
+        self.graph = False
+        return "reference modules (oracle/_ref, unmodified) + reference CUDA plugins (sm_100a JIT) + cuDNN, fp32 parameters, TF32 convolutions (torch default), eager"
+
+
+def parity_summary(rep):
+    """Worst measured errors of the BENCHMARKED trainer configuration against the CPU oracle (profiles/parity_r2.json,
+    written by tests/test_gpu_step.py on a B200)."""
+    out = {"source": "profiles/parity_r2.json (tests/test_gpu_step.py on a B200: bf16 autocast + channels_last + folded BN + bf16-resident synthesis vs the fp32 CPU oracle)"}
+    for sec in ("bench_l1l2", "bench_all"):
+        r = rep.get(sec)
+        if not r:
+            continue
+        groups = {k: v for k, v in r["grads"].items() if "(all" in k}
+        out[sec] = {"worst_loss_rel": max(v["rel"] for v in r["losses"].values()),
+                    "worst_group_grad_rel_l2": max(v["rel_l2"] for v in groups.values()),
+                    "worst_group_grad_cos": min(v["cos"] for v in groups.values()),
+                    "worst_adam_update_cos": min((v["update_cos"] for v in r.get("adam", {}).values()), default=None)}
+    if "graphed_vs_eager" in rep:
+        out["graphed_vs_eager"] = {"worst_loss_rel": rep["graphed_vs_eager"]["worst_loss_rel"],
+                                   "params_rel_l2": rep["graphed_vs_eager"]["params"]["rel_l2"],
+                                   "bitwise_equal": rep["graphed_vs_eager"]["bitwise_equal"]}
+    if "dp" in rep:
+        out["dp_2rank_vs_1rank"] = {k: v["rel_l2"] for k, v in rep["dp"]["grads"].items()}
+    return out
 
 
 WORKLOADS = {"opsweep": OpSweep, "synthesis": Synthesis, "trainstep": TrainStep}
@@ -486,25 +578,67 @@ DEFAULT_WORKLOAD = "trainstep"
 
 
 def run_reference(args, world, rank):
-    """The reference's own CPU implementation of the path (oracle port of its impl='ref' code) on host cores."""
+    """The reference's own CPU implementation of the path (oracle port of its impl='ref' code) on the host cores: the FULL
+    batch of the workload per step (for the train step: forward + backward + both Adam updates), --warmup / --steps honoured
+    while the whole run fits ~4 minutes (fewer timed steps otherwise; `steps` reports what ran)."""
     if rank != 0:
         return
     wl = pick_workload(args)
     cores = len(os.sched_getaffinity(0))
     torch.set_num_threads(cores)
-    n_sample = 1
-    for _ in range(max(1, min(args.warmup, 1))):
-        wl.cpu_step(n_sample)
-    t = [wl.cpu_step(n_sample) for _ in range(max(1, min(args.steps, 5)))]
-    sec = sum(t) / len(t)
-    value = wl.units_per_step() * (n_sample / wl.n) / sec
+    t_first = wl.cpu_step(wl.n)
+    budget = 240.0
+    warm = max(0, min(args.warmup, int(budget * 0.2 / max(t_first, 1e-3))) - 1)
+    for _ in range(warm):
+        wl.cpu_step(wl.n)
+    steps = max(1, min(args.steps, int((budget - (warm + 1) * t_first) / max(t_first, 1e-3))))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        wl.cpu_step(wl.n)
+    sec = (time.perf_counter() - t0) / steps
+    value = wl.units_per_step() / sec
     line = {"impl": "reference", "metric": wl.metric, "value": round(value, 4), "unit": wl.unit, "n_gpus": args.gpus,
-            "steps": len(t), "warmup": 1, "ms_per_step": round(sec * 1e3 * wl.n / n_sample, 3), "higher_is_better": True,
+            "steps": steps, "warmup": warm + 1, "ms_per_step": round(sec * 1e3, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl.name, "device": "host CPU"},
-            "cpu_baseline": {"value": round(value, 4), "unit": wl.unit, "cores": cores, "kind": "port",
-                             "sample": "%d of the %d images of a step, oracle/ (torch CPU restatement of the reference impl='ref' path)" % (n_sample, wl.n)},
+            "config": {"workload": wl.name, "batch_per_gpu": wl.n, "device": "host CPU"},
+            "cpu_baseline": {"value": round(value, 4), "unit": wl.unit, "cores": cores, "kind": "port", "extrapolated": False,
+                             "sample": "the full batch (%d images/GPU) per step%s, oracle/ (torch CPU restatement of the reference impl='ref' path); "
+                                       "%d timed steps of %d requested" % (wl.n, ", both Adam updates included" if isinstance(wl, TrainStep) else "", steps, args.steps)},
             "e2e": {"value": round(value, 4), "unit": wl.unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_reference_gpu(args, world, rank, local):
+    """Secondary baseline: the unmodified reference modules on this B200 - its two CUDA plugins JIT-built for
+    sm_100a and cuDNN convolutions - timed like our own arm (CUDA events, W warm-up + K steps).  Rank 0 only."""
+    if rank != 0:
+        return
+    from oracle import stage_ref
+    if not stage_ref.available() or not torch.cuda.is_available():
+        print(json.dumps({"impl": "reference-gpu", "unavailable": "oracle/_ref not staged (build container: python -m oracle.stage_ref) or no GPU"}), flush=True)
+        return
+    device = torch.device("cuda", local)
+    torch.cuda.set_device(device)
+    wl = pick_workload(args)
+    how = wl.reference_gpu_setup(device, seed=1000 * world + rank)
+    for _ in range(max(args.warmup, 3)):
+        wl.step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        wl.step()
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    value = wl.units_per_step() * args.steps / (ms * 1e-3)
+    line = {"impl": "reference-gpu", "metric": wl.metric, "value": round(value, 3), "unit": wl.unit, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 (TF32 convolutions)", "data": "synthetic",
+            "config": {"workload": wl.name, "batch_per_gpu": wl.n, "how": how}, "clocks": clocks}
     print(json.dumps(line), flush=True)
 
 
@@ -513,6 +647,9 @@ def main():
     world, rank, local = dist_setup(args)
     if args.impl == "reference":
         run_reference(args, world, rank)
+        return
+    if args.impl == "reference-gpu":
+        run_reference_gpu(args, world, rank, local)
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
@@ -563,7 +700,7 @@ def main():
     ms_e2e = max_over_ranks(ms_e2e, world, device)
     e2e_value = wl.units_per_step() * world * k_e2e / (ms_e2e * 1e-3)
 
-    roof = cpu = None
+    roof = cpu = others = None
     if rank == 0:
         roof = wl.roofline(device, peaks)
         prof = os.path.join(ROOT, "profiles", "traffic.json")
@@ -572,26 +709,48 @@ def main():
                 roof["traffic"] = json.load(open(prof)).get(roof["kernel"].split("<")[0].split(" ")[0])
             except Exception:
                 pass
+        if os.environ.get("VCN_BENCH_KERNELS", "1") == "1":
+            # every other hand-written kernel alone at its BASELINE shape (the "upfirdn2d/bias_act HBM GB/s vs peak" half of
+            # BASELINE.json's metric) and, for the convolutions, the cuDNN kernel of the same layer on this box
+            from tools import kernel_rooflines
+            try:
+                others = kernel_rooflines.collect(device, peaks, time_kernel_flushed, iters=10, n=wl.n)
+            except Exception as e:  # pragma: no cover - a failing side measurement must not lose the headline line
+                others = [{"error": "%s: %s" % (type(e).__name__, str(e)[:200])}]
         if world == 1 and not args.no_cpu_baseline:
             cores = len(os.sched_getaffinity(0))
             torch.set_num_threads(cores)
-            wl.cpu_step(1)
-            sec = min(wl.cpu_step(1) for _ in range(2))
-            cpu = {"value": round(wl.units_per_step() / wl.n / sec, 4), "unit": wl.unit, "cores": cores, "kind": "port",
-                   "sample": "1 of the %d images of a step, oracle/ (torch CPU restatement of the reference impl='ref' path)" % wl.n}
+            wl.cpu_step(wl.n)
+            sec = wl.cpu_step(wl.n)
+            cpu = {"value": round(wl.units_per_step() / sec, 4), "unit": wl.unit, "cores": cores, "kind": "port", "extrapolated": False,
+                   "sample": "one full step (%d images/GPU%s) after one warm-up step, oracle/ (torch CPU restatement of the reference impl='ref' path)"
+                             % (wl.n, ", forward + backward + both Adam updates" if isinstance(wl, TrainStep) else "")}
     barrier(world)
     if rank == 0:
         line = {"metric": wl.metric, "value": round(value, 3), "unit": wl.unit, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
                 "config": {"workload": wl.name, "batch_per_gpu": wl.n, "l2": getattr(wl, "l2_note", "working set per step larger than L2 (activations >= 67 MB per layer at 64^2 and above)"),
-                           "parallelism": getattr(wl, "parallelism_note", "dp%d (independent shards, no data-path collective)") % world},
+                           "parallelism": getattr(wl, "parallelism_note", "dp%d (independent shards, no data-path collective)") % world,
+                           "arithmetic": getattr(wl, "arithmetic_note", "fp32 storage and accumulation")},
                 "clocks": clocks,
                 "e2e": {"value": round(e2e_value, 3), "unit": wl.unit, "h2d_bytes_per_step": wl.h2d, "d2h_bytes_per_step": wl.d2h,
                         "steps": k_e2e},
                 "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu}
-        if getattr(wl, "other_rooflines", None):
-            line["roofline_others"] = wl.other_rooflines
+        flop = getattr(wl, "step_flop", None)
+        if flop:  # whole-step arithmetic rate against the SUSTAINED bf16 peak (the step runs for seconds under the power cap)
+            tf = flop / (ms / args.steps * 1e-3) / 1e12
+            line["step_tflops"] = round(tf, 1)
+            line["step_frac_of_sustained"] = round(tf / peaks["bf16_sus"], 4)
+        others = others or getattr(wl, "other_rooflines", None)
+        if others:
+            line["roofline_others"] = others
+        par = os.path.join(ROOT, "profiles", "parity_r2.json")
+        if os.path.exists(par):  # measured errors of the benchmarked configuration vs the oracle (tests/test_gpu_step.py)
+            try:
+                line["parity"] = parity_summary(json.load(open(par)))
+            except Exception:
+                pass
         print(json.dumps(line), flush=True)
     if world > 1:
         # CUDA graphs that captured NCCL collectives keep the communicator busy: tearing the process group down under them

@@ -40,7 +40,11 @@ def _worker(rank, world, port, out_dir):
         with torch.no_grad():
             for p in m.parameters():
                 p.add_(1.0)
+    versions = [p._version for p in m.parameters()]
     dp.broadcast_parameters([m])
+    # the in-place broadcast must bump every tensor's version counter: the synthesis path's packed-weight / style / noise
+    # caches are keyed on (data_ptr, _version) and may have been filled before the broadcast (dp.py)
+    assert rank == 0 or all(p._version > v for p, v in zip(m.parameters(), versions)), "broadcast did not bump tensor versions"
     buckets = dp.GradBuckets(m.parameters(), bucket_bytes=512)  # several small buckets
     assert len(buckets.buckets) >= 3
     g = torch.Generator().manual_seed(100)

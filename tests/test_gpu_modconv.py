@@ -388,3 +388,27 @@ def test_modulate_pack_channels_last_exact(shape, with_styles):
     assert torch.equal(got[..., :c], want)
     if c_pad > c:
         assert float(got[..., c:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("g,cin,cout,res,k,up,flip_weight", [(3, 64, 48, 16, 3, 1, True), (2, 128, 3, 32, 1, 1, True),
+                                                            (2, 64, 64, 8, 3, 2, False), (4, 24, 40, 9, 3, 1, False)])
+def test_conv2d_resample_grouped_per_sample(g, cin, cout, res, k, up, flip_weight):
+    """conv2d_resample(groups=N) in the call pattern of the reference's FUSED modconv branch (networks.py:78-81:
+    x = [1, N*Cin, H, W], w = [N*Cout, Cin, k, k]) -> the per-sample-weight mode of the implicit GEMM; y, dx and dw vs the
+    reference formulation in plain torch (grouped F.conv2d / F.conv_transpose2d + FIR)."""
+    import viscoin_next_b200 as V
+    C = V.conv2d_resample
+    gen = torch.Generator().manual_seed(g * 100 + cin + up)
+    x = torch.randn(1, g * cin, res, res, generator=gen)
+    w = torch.randn(g * cout, cin, k, k, generator=gen) / math.sqrt(cin * k * k)
+    f = R.setup_filter([1, 3, 3, 1])
+    xr, wr = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    y_ref = C.conv2d_resample(xr, wr, f=f, up=up, padding=k // 2, groups=g, flip_weight=flip_weight, impl="ref")
+    dy = torch.randn(y_ref.shape, generator=gen)
+    dx_ref, dw_ref = torch.autograd.grad(y_ref, [xr, wr], dy)
+    xc, wc = x.cuda().requires_grad_(True), w.cuda().requires_grad_(True)
+    y = C.conv2d_resample(xc, wc, f=f.cuda(), up=up, padding=k // 2, groups=g, flip_weight=flip_weight)
+    dx, dw = torch.autograd.grad(y, [xc, wc], dy.cuda())
+    e = (_rel(y, y_ref), _rel(dx, dx_ref), _rel(dw, dw_ref))
+    print("grouped", (g, cin, cout, res, k, up), "y/dx/dw", e)
+    assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, e

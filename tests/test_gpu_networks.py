@@ -46,9 +46,14 @@ def test_generator_golden(golden):
     G.eval()
     z = g.t("G.z", device="cuda")
     assert _rel(G(z, None, noise_mode="const"), g.t("G.full.img")) <= 2e-2
+    with torch.no_grad():  # without the flag: the same fp32-storage path as in grad mode (bit-identical numerics)
+        assert torch.equal(G(z, None, noise_mode="const"), G(z, None, noise_mode="const").clone())
+        assert _rel(G(z, None, noise_mode="const"), g.t("G.full.img")) <= 2e-2
+    G.synthesis.resident_bf16 = True
     with torch.no_grad():  # resident bf16-NHWC inference pipeline (per-sample weights / channels-last FIR)
         assert _rel(G(z, None, noise_mode="const"), g.t("G.full.img")) <= 3e-2
         assert _rel(G.synthesis(g.t("G.eval.ws", device="cuda"), noise_mode="const"), g.t("G.eval.img")) <= 3e-2
+    G.synthesis.resident_bf16 = False
     assert _rel(G(z, None, truncation_psi=0.7, noise_mode="none"), g.t("G.trunc.img")) <= 2e-2
     # noise_mode='random' consumes torch.randn exactly like the reference (same shapes, same order)
     torch.manual_seed(5)
@@ -123,8 +128,12 @@ def test_full_size_synthesis_runs():
     ws = torch.randn(8, S.num_ws, 512, device="cuda")
     img = S(ws, noise_mode="const")
     assert img.shape == (8, 3, 256, 256) and torch.isfinite(img).all()
+    with torch.no_grad():  # no flag: grad mode and no_grad run the same path (no silent numerics switch)
+        assert torch.equal(S(ws, noise_mode="const"), img)
+    S.resident_bf16 = True
     with torch.no_grad():  # the resident-activation pipeline agrees with the per-op path (both bf16 operands)
         fast = S(ws, noise_mode="const")
+    S.resident_bf16 = False
     assert _rel(fast, img) <= 3e-2
     one = S(ws[5:6], noise_mode="const")
     # the style FCs are library GEMMs whose batch-8 and batch-1 algorithms differ in the last fp32 bit; the bf16 rounding
@@ -132,12 +141,14 @@ def test_full_size_synthesis_runs():
     assert _rel(img[5:6], one) <= 1e-2
 
 
-def test_cuda_graph_replay_equals_eager():
+@pytest.mark.parametrize("resident", [True, False])
+def test_cuda_graph_replay_equals_eager(resident):
     """GraphedSynthesis (one captured graph of the whole forward) reproduces the eager inference path bit for bit on
-    new latents, and keeps doing so across replays."""
+    new latents, and keeps doing so across replays (bf16-resident pipeline and fp32-storage path)."""
     from viscoin_next_b200 import networks as N
     torch.manual_seed(1)
     S = N.SynthesisNetwork(w_dim=64, img_resolution=64, img_channels=3, channel_base=2048, channel_max=64).cuda().eval().requires_grad_(False)
+    S.resident_bf16 = resident
     for name, p in S.named_parameters():
         if name.endswith("noise_strength"):
             p.fill_(0.2)

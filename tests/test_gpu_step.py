@@ -1,102 +1,180 @@
-"""Full VisCoIN train step on the B200 vs the CPU oracle (oracle/ref_step.py) on the same weights and inputs.
+"""Full VisCoIN train step on the B200 vs the CPU oracle (oracle/ref_step.py) on the same weights and inputs
+(viscoin/training/viscoin.py:140-223): every loss term, every trainable gradient, and the parameters after both Adam
+updates - for the fp32-library configuration AND for exactly the configuration ``bench.py`` times (bf16 autocast,
+channels_last, folded BatchNorm, bf16-resident synthesis activations, whole-step CUDA graph).
 
-fp32 library networks with TF32 off, Theta's dropout off, noise_mode='const' with noise_strength 0.1, N = 1 real + 1
-fake image at 256x256 (the networks fix the resolution).  The synthesis path runs bf16 tensor-core operands with fp32
-accumulation, so tolerances are the bf16 gates of SURVEY 8(c): loss terms rel 2e-2, gradients rel-Linf 5e-2."""
+Theta's dropout is off and noise_mode='const' with noise_strength 0.1 (device RNG streams differ from the CPU's); the
+networks fix the resolution at 256x256.  The synthesis path computes on bf16 tensor-core operands with fp32 accumulation:
+tolerances are the bf16 gates of SURVEY 8(c).  Measured errors go to gpurun_out/parity_r2.json (-> profiles/)."""
+
+import os
+import subprocess
+import sys
 
 import pytest
 import torch
 
+from step_parity import ROOT, compare, make_inputs, metrics, record, set_noise_strength, summarize
+
 pytestmark = pytest.mark.gpu
 
-
-def _rel(a, ref):
-    a, ref = a.detach().double().cpu(), ref.detach().double().cpu()
-    return float((a - ref).abs().max() / ref.abs().max().clamp_min(1e-30))
+FP32_CONFIG = dict(amp=None, channels_last=False, fold_bn=False)  # library networks in fp32 (TF32 off below)
+BENCH_CONFIG = dict()                                             # VisCoINTrainer defaults = what bench.py builds
 
 
-def _compare(beta, gamma):
-    import viscoin_next_b200 as V
-    from oracle import ref_step as RS
-    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
-    torch.backends.cudnn.allow_tf32 = False
-    torch.backends.cuda.matmul.allow_tf32 = False
-    try:
-        dev = torch.device("cuda:0")
-        params = V.viscoin_step.VisCoINParams()
-        params.beta, params.gamma = beta, gamma
-        tr = V.viscoin_step.VisCoINTrainer(dev, seed=11, amp=None, channels_last=False, deterministic=True, params=params,
-                                           fold_bn=False)  # the oracle loads the unfolded HF state_dict
-        tr.synthesis_kwargs = {"noise_mode": "const"}
-        with torch.no_grad():
-            for name, p in tr.viscoin_gan.synthesis.named_parameters():
-                if name.endswith("noise_strength"):
-                    p.fill_(0.1)
-        cpu = lambda m: {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
-        state = {"classifier": cpu(tr.classifier), "concept_extractor": cpu(tr.concept_extractor),
-                 "explainer": cpu(tr.explainer), "viscoin_gan": cpu(tr.viscoin_gan)}
-        state["lpips_convs"] = [(l.weight.detach().cpu(), l.bias.detach().cpu()) for s in tr.lpips.slices for l in s
-                                if isinstance(l, torch.nn.Conv2d)]
-        state["lpips_lins"] = [p.detach().cpu() for p in tr.lpips.lins]
-        g = torch.Generator().manual_seed(5)
-        real = torch.randn(1, 3, 256, 256, generator=g)
-        labels = torch.randint(0, 200, (1,), generator=g)
-        with torch.no_grad():
-            fake = V.viscoin_step.synthetic_samples(tr.generator_gan, 1, dev, g).float()
-        assert fake.shape == (1, 3, 256, 256) and bool(torch.isfinite(fake).all())
+class _tf32_off:
+    def __enter__(self):
+        self.old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
 
-        # product: forward + backward only (the optimizer step would change the weights under comparison)
-        losses = tr.forward_losses(real.to(dev), labels.to(dev), 1000, fake_images=fake)
-        sum(losses.values()).backward()
-        tr.buckets.finish()
+    def __exit__(self, *exc):
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = self.old
 
-        # oracle
-        watch = {"concept_extractor": ["conv5.weight", "conv4.bias", "linear2.weight", "conv1.weight"],
-                 "explainer": ["linear.weight"], "viscoin_gan": ["mapping.s0.0.weight", "mapping.s5.0.weight", "mapping.s13.0.bias",
-                                                                 "mapping.fixed_w_avg"]}
-        for grp, names in watch.items():
-            for n in names:
-                state[grp][n].requires_grad_(True)
-        want = RS.step_losses(state, real, labels, fake.cpu(), noise_mode="const", beta=beta, gamma=gamma)
-        want.pop("_rebuilt")
-        sum(want.values()).backward()
 
-        for k in want:
-            r = abs(float(losses[k]) - float(want[k])) / max(abs(float(want[k])), 1e-6)
-            print("loss %-6s gpu %.6f cpu %.6f rel %.2e" % (k, float(losses[k]), float(want[k]), r))
-            assert r <= 2e-2, (k, float(losses[k]), float(want[k]))
-        errs = {}
-        mods = {"concept_extractor": tr.concept_extractor, "explainer": tr.explainer, "viscoin_gan": tr.viscoin_gan}
-        for grp, names in watch.items():
-            params = dict(mods[grp].named_parameters())
-            for n in names:
-                e = _rel(params[n].grad, state[grp][n].grad)
-                a_, b_ = params[n].grad.detach().double().cpu().flatten(), state[grp][n].grad.double().flatten()
-                cos = float(torch.dot(a_, b_) / (a_.norm() * b_.norm()).clamp_min(1e-300))
-                print("grad %s.%s rel-Linf %.2e cos %.6f" % (grp, n, e, cos))
-                errs[grp + "." + n] = (e, cos)
-        return errs
-    finally:
-        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+def _big(out):
+    """Per-tensor entries only (the '(all N tensors)' group rows are checked separately)."""
+    return {k: v for k, v in out["grads"].items() if "(all" not in k}
+
+
+def _groups(out):
+    return {k: v for k, v in out["grads"].items() if "(all" in k}
+
+
+# ---- fp32 library networks (TF32 off): isolates the synthesis kernels' bf16 operands ----------------------------------
 
 
 def test_train_step_matches_oracle_l1_l2_reconstruction():
     """beta = gamma = 0: the reconstruction term is L1 + L2 only, so the gradient that enters the synthesis backward is
-    smooth in the rebuilt image.  Every watched gradient (through the synthesis dgrad / dstyles kernels, the adapted
-    mapping and Psi) must match the fp32 oracle within the bf16 gate."""
-    errs = _compare(0.0, 0.0)
-    bad = {k: v for k, v in errs.items() if v[0] > 5e-2}
+    smooth in the rebuilt image.  Loss values <= 2e-2 (measured <= 1.2e-3); EVERY trainable gradient tensor (through the
+    synthesis dgrad / dstyles kernels, the adapted mapping and Psi) within the bf16 gate rel-Linf <= 5e-2; Adam update
+    direction of each parameter group cosine >= 0.9."""
+    with _tf32_off():
+        out = compare(FP32_CONFIG, 0.0, 0.0, n=1, label="fp32lib_l1l2")
+    summarize(out)
+    assert all(v["rel"] <= 2e-2 for v in out["losses"].values()), out["losses"]
+    bad = {k: v for k, v in _big(out).items() if v["rel_linf"] > 5e-2}
     assert not bad, bad
+    assert all(v["cos"] >= 0.999 for v in _groups(out).values()), _groups(out)
+    assert all(v["update_cos"] >= 0.9 for v in out["adam"].values()), out["adam"]
 
 
 def test_train_step_matches_oracle_all_losses():
-    """All six terms (beta = 3 LPIPS, gamma = 0.1 classifier agreement).  Loss VALUES must match at 2e-2.  With random-init
-    VGG / ResNet features the perceptual gradient is ill-conditioned in the rebuilt image (unit-normalisation of near-zero
-    feature vectors), so the bf16-operand rounding of the synthesis forward is amplified in d(rec)/d(image): gradients are
-    required to agree in direction (cosine >= 0.8), the tight per-element gate being the L1+L2 test above."""
-    errs = _compare(3.0, 0.1)
-    bad = {k: v for k, v in errs.items() if v[1] < 0.8}
+    """All six terms (beta = 3 LPIPS, gamma = 0.1 classifier agreement).  Loss VALUES <= 2e-2.  With random-init VGG /
+    ResNet features the perceptual gradient is ill-conditioned in the rebuilt image (unit-normalisation of near-zero
+    feature vectors): the bf16-operand rounding of the synthesis forward is amplified in d(rec)/d(image), so gradients
+    are gated on direction.  test_all_losses_fp32_reference_modules_conditioning shows what an fp32 GPU run of the
+    reference's own modules reaches on the same harness."""
+    with _tf32_off():
+        out = compare(FP32_CONFIG, 3.0, 0.1, n=1, label="fp32lib_all")
+    summarize(out)
+    assert all(v["rel"] <= 2e-2 for v in out["losses"].values()), out["losses"]
+    bad = {k: v for k, v in out["grads"].items() if v["cos"] < 0.8}
     assert not bad, bad
+
+
+# ---- the benchmarked configuration ------------------------------------------------------------------------------------
+
+
+def test_bench_config_matches_oracle_l1_l2_reconstruction():
+    """VisCoINTrainer defaults (bf16 autocast for f / Psi / VGG, channels_last, folded BN, bf16-resident synthesis), two
+    real + two fake images, L1+L2 reconstruction: loss values, all gradients, parameters after both Adam updates."""
+    out = compare(BENCH_CONFIG, 0.0, 0.0, n=2, label="bench_l1l2")
+    summarize(out)
+    assert all(v["rel"] <= 3e-2 for v in out["losses"].values()), out["losses"]
+    assert all(v["cos"] >= 0.99 and v["rel_l2"] <= 1.5e-1 for v in _groups(out).values()), _groups(out)
+    bad = {k: v for k, v in _big(out).items() if v["cos"] < 0.98}
+    assert not bad, bad
+    assert all(v["update_cos"] >= 0.8 for v in out["adam"].values()), out["adam"]
+
+
+def test_bench_config_matches_oracle_all_losses():
+    """Same with all six loss terms.  Loss values <= 3e-2; gradients directional (see the fp32 all-loss test)."""
+    out = compare(BENCH_CONFIG, 3.0, 0.1, n=2, label="bench_all")
+    summarize(out)
+    assert all(v["rel"] <= 3e-2 for v in out["losses"].values()), out["losses"]
+    bad = {k: v for k, v in _groups(out).items() if v["cos"] < 0.8}
+    assert not bad, bad
+
+
+def test_step_graphed_equals_eager_step():
+    """``step_graphed`` (what bench.py times: the whole iteration replayed from one CUDA graph) against the eager ``step``
+    on an identical replica: same z stream, noise_mode='const', dropout off, four iterations (two eager warm-ups, the
+    capture, one replay).  Every kernel of the step is deterministic except atomically accumulated reductions, so the loss
+    trajectories and the final parameters must agree to fp32 reduction-order noise."""
+    import viscoin_next_b200 as V
+    dev = torch.device("cuda:0")
+    trs = []
+    for _ in range(2):
+        tr = V.viscoin_step.VisCoINTrainer(dev, seed=3, deterministic=True)
+        tr.synthesis_kwargs = {"noise_mode": "const"}
+        set_noise_strength(tr, 0.1)
+        trs.append(tr)
+    eager, graphed = trs
+    g = torch.Generator().manual_seed(0)
+    real = torch.randn(2, 3, 256, 256, generator=g)
+    labels = torch.randint(0, 200, (2,), generator=g)
+    ze, zg = torch.Generator().manual_seed(9), torch.Generator().manual_seed(9)
+    worst, bitwise = 0.0, True
+    for it in range(4):
+        a = eager.step(real.to(dev), labels.to(dev), 1000, z_generator=ze)
+        a = {k: float(v) for k, v in a.items()}
+        b = graphed.step_graphed(real, labels, 1000, z_generator=zg)
+        b = {k: float(v) for k, v in b.items()}
+        for k in a:
+            worst = max(worst, abs(a[k] - b[k]) / max(abs(a[k]), 1e-6))
+            bitwise = bitwise and a[k] == b[k]
+    assert (2, True) in graphed._graphs, "the graph was never captured"
+    pe = torch.cat([p.detach().flatten() for p in eager.concept_extractor.parameters()] +
+                   [p.detach().flatten() for p in eager.viscoin_gan.mapping.parameters()])
+    pg = torch.cat([p.detach().flatten() for p in graphed.concept_extractor.parameters()] +
+                   [p.detach().flatten() for p in graphed.viscoin_gan.mapping.parameters()])
+    m = metrics(pg, pe)
+    bitwise = bitwise and bool(torch.equal(pe, pg))
+    print("graphed vs eager: worst loss rel diff %.2e, params rel-L2 %.2e max-abs %.2e, bitwise %s" % (worst, m["rel_l2"], m["max_abs"], bitwise))
+    record("graphed_vs_eager", {"worst_loss_rel": worst, "params": m, "bitwise_equal": bitwise, "iterations": 4})
+    assert worst <= 1e-3 and m["rel_l2"] <= 1e-5
+
+
+def test_all_losses_fp32_reference_modules_conditioning():
+    """Settles where the loose all-loss gradient gate comes from: the SAME harness with the synthesis
+    path run by the reference's own modules in fp32 on the GPU (its plugins / torch ops + cuDNN with TF32 off, no kernel of
+    this repo) against the same CPU oracle.  If this reaches cosine ~1 the 0.88..0.98 of the product path is bf16 operand
+    rounding amplified by the random-init perceptual loss; the measured values are recorded either way."""
+    from oracle import stage_ref
+    if not stage_ref.available():
+        pytest.skip("oracle/_ref not staged (build container only stages it when /root/reference is mounted)")
+    import viscoin_next_b200 as V
+    try:
+        ref = stage_ref.load_plugins()
+    except Exception as e:  # the reference itself would fall back to its torch ops here
+        print("reference plugins unavailable (%s): reference runs its impl='ref' path on the GPU" % e)
+        ref = stage_ref.import_reference()
+    torch.manual_seed(11)
+    VM, N = V.viscoin_models, V.networks
+    mine = (VM.Classifier(200), VM.ConceptExtractor(), VM.Explainer(n_classes=200),
+            N.Generator(z_dim=512, c_dim=0, w_dim=512, img_resolution=256, img_channels=3, mapping_kwargs={"num_layers": 2}))
+    lp = VM.LPIPS()
+    lp.fused = False
+    G = ref.networks.Generator(z_dim=512, c_dim=0, w_dim=512, img_resolution=256, img_channels=3, mapping_kwargs={"num_layers": 2})
+    G.load_state_dict(mine[3].state_dict(), strict=True)
+    GA = ref.gan.GeneratorAdapted.from_gan(G)
+    GA.mapping.load_state_dict(N.GeneratorAdapted.from_gan(mine[3]).mapping.state_dict(), strict=True)
+    psi = ref.concept_extractors.ConceptExtractor()
+    psi.load_state_dict(mine[1].state_dict(), strict=True)
+    theta = ref.explainers.Explainer(n_classes=200)
+    theta.load_state_dict(mine[2].state_dict(), strict=True)
+    # BatchNorm statistics of the random-init classifier (what VisCoINTrainer does when it builds the models itself)
+    cls = mine[0].cuda()
+    with torch.no_grad():
+        fakes = G.cuda()(torch.randn(4, 512, generator=torch.Generator().manual_seed(11)).cuda(), None).float()
+    VM.calibrate_batchnorm(cls, torch.cat([torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(12)).cuda(), fakes]))
+    with _tf32_off():
+        out = compare(FP32_CONFIG, 3.0, 0.1, n=1, label="fp32_reference_modules_all", with_adam=False,
+                      models=(cls, psi, theta, G, GA, lp))
+    summarize(out)
+    assert all(v["rel"] <= 1e-3 for v in out["losses"].values()), out["losses"]
+    assert all(v["cos"] >= 0.8 for v in _groups(out).values()), _groups(out)
 
 
 def test_train_step_updates_and_is_finite():
@@ -119,3 +197,17 @@ def test_train_step_updates_and_is_finite():
     assert torch.equal(w_syn, tr.viscoin_gan.synthesis.b64.conv1.weight)
     assert torch.equal(w_f, tr.classifier.linear.weight)
     assert tr.generator_gan.synthesis is tr.viscoin_gan.synthesis
+
+
+def test_data_parallel_two_ranks_equal_one_rank_on_concatenated_batch():
+    """SURVEY App. E 'DP' row on hardware: the real step on 2 NCCL ranks (each its own shard, bucketed all-reduce
+    overlapped with backward) gives the gradients of ONE rank on the concatenated batch.  Needs 2 GPUs (the round-end run
+    has one: run with `gpurun --gpus 2`; the measured errors are committed in profiles/parity_r2.json)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29533", os.path.join(ROOT, "tools", "dp_check.py")]
+    proc = subprocess.run(cmd, cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    print(proc.stdout[-4000:])
+    assert proc.returncode == 0, "dp_check.py failed"

@@ -1,0 +1,106 @@
+#!/usr/bin/env python
+"""Data-parallel parity on hardware (SURVEY App. E "DP" row): the real VisCoIN step on W NCCL ranks == one rank on the
+concatenated batch.  Launched under torchrun by tests/test_gpu_step.py (needs >= 2 GPUs):
+
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/dp_check.py
+
+Phase 1 (before the process group exists, world = 1): every rank computes the gradients of the concatenated batch
+(W*n real + W*n fake images) on its own GPU.  Phase 2 (NCCL): identical replica (same seed + broadcast; rank 1 is
+deliberately seeded differently first, so the broadcast - including the cache invalidation it must trigger - is what
+makes the replicas equal), each rank runs forward + backward on ITS shard, the bucketed all-reduce (AVG) runs under
+backward, and the averaged gradients are compared with phase 1.  Every loss term is a batch mean, the frozen f runs
+BatchNorm in eval mode and Psi has none, so mean-of-shard-gradients == concatenated-batch gradient up to fp32
+reduction order and the bf16 tiles' batch-size-dependent accumulation order.  Writes gpurun_out/parity_dp.json."""
+
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+
+def main():
+    import viscoin_next_b200 as V
+    from step_parity import metrics, set_noise_strength, trainer_named_params
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    n = 2
+
+    def build(seed):
+        tr = V.viscoin_step.VisCoINTrainer(dev, seed=seed, deterministic=True)
+        tr.synthesis_kwargs = {"noise_mode": "const"}
+        return tr
+
+    g = torch.Generator().manual_seed(77)
+    real = torch.randn(world * n, 3, 256, 256, generator=g)
+    labels = torch.randint(0, 200, (world * n,), generator=g)
+    z = torch.randn(world * n, 512, generator=g)
+
+    def grads_of(tr, sl):
+        with torch.no_grad():
+            fake = tr.generator_gan(z[sl].to(dev), None, noise_mode="const").float()
+        losses = tr.forward_losses(real[sl].to(dev), labels[sl].to(dev), 1000, fake_images=fake)
+        sum(losses.values()).backward()
+        tr.buckets.finish()
+        out = {k: p.grad.detach().float().clone() for k, p in trainer_named_params(tr).items()}
+        tr.buckets.reset()
+        return out, {k: float(v) for k, v in losses.items()}
+
+    # phase 1: single rank, concatenated batch
+    tr = build(0)
+    set_noise_strength(tr, 0.1)
+    want, want_losses = grads_of(tr, slice(0, world * n))
+    del tr
+    torch.cuda.empty_cache()
+
+    # phase 2: W ranks, one shard each
+    dist.init_process_group("nccl", device_id=dev)
+    tr = build(0 if rank == 0 else 1234 + rank)  # replicas become identical only through dp.broadcast_parameters
+    set_noise_strength(tr, 0.1)
+    assert tr.buckets.world == world
+    w0 = tr.viscoin_gan.synthesis.b32.conv1.weight.detach().clone()
+    dist.broadcast(w0, src=0)
+    assert torch.equal(w0, tr.viscoin_gan.synthesis.b32.conv1.weight), "replicas differ after broadcast_parameters"
+    # caches filled before the broadcast must not serve stale weights - the images must be equal too
+    with torch.no_grad():
+        img = tr.generator_gan(z[:2].to(dev), None, noise_mode="const").float()
+    ref_img = img.clone()
+    dist.broadcast(ref_img, src=0)
+    img_diff = float((img - ref_img).abs().max())
+    got, got_losses = grads_of(tr, slice(rank * n, (rank + 1) * n))
+    res = {"world": world, "n_per_rank": n, "replica_image_max_abs_diff": img_diff, "grads": {}}
+    cat = lambda d, keys: torch.cat([d[k].flatten() for k in keys])
+    for grp in ("concept_extractor", "explainer", "viscoin_gan"):
+        keys = [k for k in want if k.startswith(grp + ".")]
+        res["grads"][grp] = metrics(cat(got, keys), cat(want, keys))
+    lt = torch.tensor([got_losses[k] for k in sorted(got_losses)], device=dev, dtype=torch.float64)
+    dist.all_reduce(lt, op=dist.ReduceOp.AVG)
+    # 'ortho' depends on parameters only; the other terms are batch means: mean over ranks == concatenated batch
+    res["losses"] = {k: {"dp_mean": float(v), "single": want_losses[k]} for k, v in zip(sorted(got_losses), lt)}
+    ok = img_diff == 0.0 and all(v["rel_l2"] <= 2e-2 and v["cos"] >= 0.9995 for v in res["grads"].values()) and \
+        all(abs(v["dp_mean"] - v["single"]) <= 2e-3 * max(1e-3, abs(v["single"])) for v in res["losses"].values())
+    res["ok"] = bool(ok)
+    if rank == 0:
+        print(json.dumps(res, indent=1))
+        try:
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", "parity_dp.json"), "w") as fh:
+                json.dump(res, fh, indent=1)
+        except Exception as e:
+            print("not written:", e)
+    flag = torch.tensor([0 if ok else 1], device=dev)
+    dist.all_reduce(flag)
+    torch.cuda.synchronize()
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(1 if int(flag.item()) else 0)
+
+
+if __name__ == "__main__":
+    main()

@@ -15,9 +15,11 @@ with bf16 operands and fp32 accumulation, every FIR is ``vcn_upfirdn2d``), forwa
     kxk, up>1            (:119-142)  transposed conv -> FIR     TCONV2 -> upfirdn2d (3x3, up=2: the SynthesisLayer path)
     no resampling        (:145-147)  conv                       FPROP / DGRAD (flipped taps)
 
-Covered: groups == 1, 1x1 and 3x3 kernels, factors 1 and 2, symmetric padding k//2 - everything ``training/networks.py``
-asks for (SynthesisBlock, the 'resnet' skips, DiscriminatorBlock's down=2 convolutions).  Anything else (grouped
-convolutions, asymmetric padding, other factors / kernel sizes) raises ``VcnError``: the reference's generic fallback
+Covered: 1x1 and 3x3 kernels, factors 1 and 2, symmetric padding k//2, groups == 1 or the per-sample grouping of the
+fused-modconv branch (``groups = N`` with x = [1, N*Cin, H, W], networks.py:78-81 -> the GEMM's per-sample-weight mode) -
+everything ``training/networks.py`` asks for (SynthesisBlock in train and eval mode, the 'resnet' skips,
+DiscriminatorBlock's down=2 convolutions).  Anything else (other groupings, asymmetric padding, other factors / kernel
+sizes) raises ``VcnError``: the reference's generic fallback
 (:150-154) has no sm_100a counterpart here and there is no silent library path.  ``impl='ref'`` is the reference's
 formulation in plain torch (any device) - the checker, not a fallback."""
 
@@ -67,6 +69,76 @@ class _StridedConv3x3(torch.autograd.Function):
         return dz, dw
 
 
+class _GroupedConv(torch.autograd.Function):
+    """conv2d_resample(..., groups=G) as the reference's fused-modconv branch calls it (networks.py:78-81):
+    x = [1, G*Cin, H, W], w = [G*Cout, Cin, k, k] - G independent convolutions, one per sample.  That is exactly the
+    per-sample-weight mode of the implicit GEMM (``w_per_sample``: the weight tile's 4th TMA coordinate is the sample):
+    up=1 -> FPROP / DGRAD taps, up=2 -> TCONV2 + the 4x4 FIR.  Backward: dx = the per-sample transposed GEMM, dw = one
+    weight-gradient GEMM per group.  Unpickled generators keep their own ``modulated_conv2d`` (persistence.py:179-227) and
+    reach the sm_100a kernels through this entry in eval mode."""
+
+    @staticmethod
+    def _pack(w, groups, flip, transpose_io):
+        gco, cin, kh, kw = w.shape
+        cout = gco // groups
+        src = w.detach()
+        if flip:
+            src = src.flip([2, 3])
+        if transpose_io:  # [G,Cout,Cin,k,k] -> [G*Cin, Cout, k, k]: rows = in-channels of the forward
+            src = src.reshape(groups, cout, cin, kh, kw).transpose(1, 2).reshape(groups * cin, cout, kh, kw)
+        rows = src.shape[0] // groups
+        wt, _ = _modconv.pack_weights(src.contiguous())  # [taps, G*rows, cols_pad]
+        return wt.reshape(kh * kw, groups, rows, wt.shape[-1]).permute(1, 0, 2, 3).contiguous()  # [G, taps, rows, cols_pad]
+
+    @staticmethod
+    def forward(ctx, x, w, f, groups, up, flip_weight):
+        _, gc, h, wd = x.shape
+        cin, cout, k = gc // groups, w.shape[0] // groups, w.shape[-1]
+        xs = x.reshape(groups, cin, h, wd)
+        xhat = _modconv.modulate_pack(xs, None)
+        if up == 1:
+            wt = _GroupedConv._pack(w, groups, False, False)
+            kind = _lib.CONV_FPROP if flip_weight else _lib.CONV_DGRAD
+            y = _modconv.conv_igemm(xhat, wt, kind, cout, k, k, out_dtype=torch.float32, w_per_sample=True)
+        else:
+            wt = _GroupedConv._pack(w, groups, bool(flip_weight), False)
+            z = _modconv.conv_igemm(xhat, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=torch.float32, w_per_sample=True)
+            y = _upfirdn2d.launch(z, f.to(device=x.device, dtype=torch.float32), 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0)
+        ctx.save_for_backward(xhat if w.requires_grad else None, w, f)
+        ctx.cfg = (groups, up, bool(flip_weight), cin, cout, k, x.dtype)
+        return y.reshape(1, groups * cout, y.shape[2], y.shape[3]).to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xhat, w, f = ctx.saved_tensors
+        groups, up, flip_weight, cin, cout, k, xdtype = ctx.cfg
+        dy = dy.reshape(groups, cout, dy.shape[2], dy.shape[3])
+        dy0 = _modconv.modulate_pack(dy, None)
+        if up == 2:  # FIR^T: the same FIR with the flipped filter, padding fw-1-p = 2 (upfirdn2d.py:246-261)
+            dy0 = _upfirdn2d.launch(dy0.permute(0, 3, 1, 2), f.to(device=dy.device, dtype=torch.float32), 1, 1, 1, 1, 2, 2, 2, 2, True, 4.0)
+            dy0 = dy0.permute(0, 2, 3, 1)
+            assert dy0.is_contiguous()
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            if up == 1:
+                wt_t = _GroupedConv._pack(w, groups, False, True)
+                kind = _lib.CONV_DGRAD if flip_weight else _lib.CONV_FPROP
+                dx = _modconv.conv_igemm(dy0, wt_t, kind, cin, k, k, out_dtype=torch.float32, w_per_sample=True)
+            else:
+                wt_t = _GroupedConv._pack(w, groups, flip_weight, True)
+                dx = _modconv.conv_igemm(dy0, wt_t, _lib.CONV_SCONV2, cin, 3, 3, out_dtype=torch.float32, w_per_sample=True)
+            dx = dx.reshape(1, groups * cin, dx.shape[2], dx.shape[3]).to(xdtype)
+        if ctx.needs_input_grad[1]:
+            parts = []
+            for g in range(groups):
+                d = _modconv.conv_wgrad(dy0[g:g + 1], xhat[g:g + 1], cout, cin, k, k, transposed=(up == 2))
+                if (up == 1 and not flip_weight) or (up == 2 and flip_weight):
+                    d = d.flip([2, 3])
+                parts.append(d)
+            dw = torch.cat(parts).to(w.dtype)
+        return dx, dw, None, None, None, None
+
+
 def _conv(x, w, flip_weight=True):
     """Stride-1 convolution, padding k//2 (1x1 or 3x3), no modulation, through the fused layer op (dx, dw in its backward)."""
     return _modconv.modconv_layer(x, w, None, demodulate=False, flip_weight=flip_weight, act=None)
@@ -94,7 +166,13 @@ def conv2d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight
     fw, fh = _upfirdn2d._get_filter_size(f)
     px0, px1, py0, py1 = _upfirdn2d._parse_padding(padding)
     if groups != 1:
-        _unsupported("groups = %d" % groups)
+        # the fused-modconv call pattern (networks.py:78-81): one group per sample, no resampling except up=2 with the 4x4 filter
+        ok = x.shape[0] == 1 and x.shape[1] % groups == 0 and cout % groups == 0 and x.shape[1] // groups == cin_g \
+            and kh == kw and kh in (1, 3) and down == 1 and px0 == px1 == py0 == py1 == kh // 2 \
+            and (up == 1 or (up == 2 and kh == 3 and f is not None and tuple(f.shape) == (4, 4) and not flip_filter))
+        if not ok:
+            _unsupported("groups = %d outside the per-sample pattern x=[1,G*Cin,H,W], w=[G*Cout,Cin,k,k], k in {1,3}, up in {1,2}" % groups)
+        return _GroupedConv.apply(x, w, f, groups, up, flip_weight)
     if kh != kw or kh not in (1, 3):
         _unsupported("a %dx%d kernel" % (kh, kw))
     if up not in (1, 2) or down not in (1, 2) or (up == 2 and down == 2):

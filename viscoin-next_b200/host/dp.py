@@ -99,6 +99,17 @@ def broadcast_parameters(modules, src=0, group=None):
     """Identical initial replicas: rank `src`'s parameters and buffers to every rank."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
-    for m in modules:
-        for t in list(m.parameters()) + list(m.buffers()):
-            dist.broadcast(t.data, src=src, group=group)
+    # Receivers copy the broadcast value in with `copy_` on the tensor itself: that bumps `t._version` (a c10d collective
+    # writing through `.data` - or into the tensor directly - does not), and the packed-weight, batched-affine and const-noise
+    # caches of the synthesis path are keyed on (data_ptr, _version) and may already have been filled by a forward that ran
+    # before the broadcast (BatchNorm calibration in VisCoINTrainer.__init__).
+    rank = dist.get_rank(group)
+    with torch.no_grad():
+        for m in modules:
+            for t in list(m.parameters()) + list(m.buffers()):
+                if rank == src:
+                    dist.broadcast(t.detach(), src=src, group=group)
+                else:
+                    buf = torch.empty_like(t)
+                    dist.broadcast(buf, src=src, group=group)
+                    t.copy_(buf)

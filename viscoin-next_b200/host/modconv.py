@@ -85,15 +85,24 @@ def demod_coefs(styles, wsq):
     return d
 
 
-def make_epilogue(scale=None, noise=None, bias=None, act=None, alpha=None, gain=None, clamp=None, keep=None):
-    """vcn_upfirdn2d_epilogue from torch tensors.  noise: [N,1,H,W] / [H,W] fp32.  `keep` collects the tensors that
-    must outlive the launch call."""
+def make_epilogue(scale=None, noise=None, bias=None, act=None, alpha=None, gain=None, clamp=None, keep=None, out_shape=None):
+    """vcn_upfirdn2d_epilogue from torch tensors.  noise: anything the reference accepts, i.e. broadcastable to
+    [N,1,H,W] (networks.py:71,83 `x.add_(noise)`); the kernels index it as a dense [H,W] plane per sample (or one shared
+    plane), so with ``out_shape = (N, H, W)`` it is validated and expanded to one of those two forms first.  `keep`
+    collects the tensors that must outlive the launch call."""
     e = _lib.UpfirdnEpilogue()
     hold = []
     if scale is not None:
         scale = scale.to(torch.float32).contiguous(); hold.append(scale)
         e.scale = scale.data_ptr()
     if noise is not None:
+        if out_shape is not None:
+            n_, oh_, ow_ = out_shape
+            if noise.ndim == 4 and noise.shape[1] != 1:
+                raise ValueError("noise must broadcast to [N,1,H,W]: per-channel noise %s is not supported" % (tuple(noise.shape),))
+            if tuple(noise.shape[-2:]) != (oh_, ow_) or (noise.ndim == 4 and noise.shape[0] not in (1, n_)) or noise.ndim not in (2, 4):
+                per_sample = noise.ndim == 4 and noise.shape[0] != 1
+                noise = noise.expand([n_ if per_sample else 1, 1, oh_, ow_]) if noise.ndim == 4 else noise.expand([oh_, ow_])
         noise = noise.to(torch.float32).contiguous(); hold.append(noise)
         e.noise = noise.data_ptr()
         e.noise_stride_n = noise.shape[-1] * noise.shape[-2] if noise.ndim == 4 and noise.shape[0] > 1 else 0
@@ -292,7 +301,8 @@ class _ModConvLayer(torch.autograd.Function):
             wt, wsq = _packed(weight, False, bool(flip_weight), demodulate)
         d = demod_coefs(styles32, wsq) if demodulate else None
         xhat = modulate_pack(x, styles32)
-        epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
+        epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp,
+                                  out_shape=(n, h * up, w * up))
         # resident pipeline: 16-bit channels-last activations stay 16-bit channels-last (forward and backward); a ToRGB
         # layer (cout < 8) leaves it and writes fp32 NCHW for the image accumulation
         resident = x.dtype == torch.bfloat16 and x.stride(1) == 1 and cin % 8 == 0
@@ -329,7 +339,8 @@ class _ModConvLayer(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         elif not dy.is_contiguous():
             dy = dy.contiguous()
-        epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp)
+        epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp,
+                                  out_shape=(n, h * up, w * up))
         want_g = demodulate and (need_s or need_w)
         dy0, gsum, db = bwd_pack(dy, y if (act is not None or want_g) else None, epi, want_g, need_b and bias is not None)
         dx = ds = dnoise = dw = None
@@ -383,9 +394,8 @@ class _ModConvLayer(torch.autograd.Function):
                                       epi.alpha, epi.act_gain, epi.clamp, False)[0]
             else:
                 dzf = dy
-            dnoise = dzf.sum(dim=1, keepdim=True)
-            if noise.ndim == 2 or noise.shape[0] == 1:
-                dnoise = dnoise.sum(dim=0).reshape(noise.shape)
+            dnoise = dzf.sum(dim=1, keepdim=True)  # [N,1,H,W] -> un-broadcast to the shape the caller passed
+            dnoise = dnoise.sum_to_size(noise.shape) if noise.ndim == 4 else dnoise.sum(dim=[0, 1]).sum_to_size(noise.shape)
             dnoise = dnoise.to(noise.dtype)
         del hold
         return dx, dw, ds, dnoise, (db.to(bias.dtype) if db is not None else None), None, None
@@ -512,14 +522,16 @@ def layer_nhwc(act, weight, styles, noise=None, bias=None, up=1, resample_filter
         wt, _ = _packed(weight, False, False, demodulate)
         xin, scale = modulate_pack(act.permute(0, 3, 1, 2)[:, :cin], styles32), d
     if up == 1:
-        epi, hold = make_epilogue(scale=scale, noise=noise, bias=bias, act=act_name, alpha=alpha, gain=gain, clamp=clamp)
+        epi, hold = make_epilogue(scale=scale, noise=noise, bias=bias, act=act_name, alpha=alpha, gain=gain, clamp=clamp,
+                                  out_shape=(n, h, w))
         y = conv_igemm(xin, wt, _lib.CONV_FPROP, cout, kh, kw, out_dtype=torch.float32 if out_nchw_f32 else torch.bfloat16,
                        channels_last=not out_nchw_f32, epilogue=epi, w_per_sample=per_sample)
         del hold
         return y if out_nchw_f32 else y.permute(0, 2, 3, 1)
     assert up == 2 and kh == 3 and not out_nchw_f32
     z = conv_igemm(xin, wt, _lib.CONV_TCONV2, cout, 3, 3, out_dtype=torch.bfloat16, channels_last=True, w_per_sample=per_sample)
-    epi, hold = make_epilogue(scale=scale, noise=noise, bias=bias, act=act_name, alpha=alpha, gain=gain, clamp=clamp)
+    epi, hold = make_epilogue(scale=scale, noise=noise, bias=bias, act=act_name, alpha=alpha, gain=gain, clamp=clamp,
+                              out_shape=(n, 2 * h, 2 * w))
     f = resample_filter.to(device=act.device, dtype=torch.float32)
     y = _upfirdn2d.launch(z, f, 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi)
     del hold

@@ -168,6 +168,10 @@ class SynthesisBlock(torch.nn.Module):
         super().__init__()
         self.in_channels, self.w_dim, self.resolution, self.img_channels = in_channels, w_dim, resolution, img_channels
         self.is_last, self.architecture = is_last, architecture
+        # networks.py:382-383,394: a use_fp16 block stores its activations in 16 bits, channels_last.  Here that is the bf16
+        # resident pipeline (bf16 has fp32's exponent range: the fp16 pre-normalisation of networks.py:47-49 is not needed;
+        # conv_clamp is applied in the epilogue exactly as in the reference)
+        self.use_fp16 = bool(use_fp16)
         self.register_buffer("resample_filter", _upfirdn2d.setup_filter(resample_filter))
         self.num_conv = self.num_torgb = 0
         if in_channels == 0:
@@ -207,13 +211,15 @@ class SynthesisBlock(torch.nn.Module):
         block to block, forward and backward (modconv._ModConvLayer keeps them that way); img stays fp32 NCHW."""
         assert tuple(ws.shape[1:]) == (self.num_conv + self.num_torgb, self.w_dim)
         w_iter = iter(ws.unbind(dim=1))
-        resident = resident and self.architecture != "resnet"
+        resident = (resident or (self.use_fp16 and not force_fp32)) and self.architecture != "resnet"
         if self.in_channels == 0:
             x = self.const.to(torch.float32).unsqueeze(0).repeat([ws.shape[0], 1, 1, 1])
             if resident:
                 x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         elif not resident:
             x = x.to(torch.float32)
+        elif x.dtype != torch.bfloat16 or x.stride(1) != 1:  # first 16-bit block after fp32 ones (networks.py:394)
+            x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         st = styles or {}
         if self.in_channels == 0:
             x = self.conv1(x, next(w_iter), styles=st.get(self.conv1), **layer_kwargs)
@@ -240,17 +246,19 @@ class SynthesisNetwork(torch.nn.Module):
         super().__init__()
         self.w_dim, self.img_resolution, self.img_channels = w_dim, img_resolution, img_channels
         self.img_resolution_log2 = int(np.log2(img_resolution))
+        self.num_fp16_res = num_fp16_res
         # differentiable forward with bf16 channels_last activations between layers (see SynthesisBlock.forward); off by
         # default: the reference's configurations store fp32 (networks.py:382-383 with num_fp16_res = 0)
         self.resident_bf16 = False
         self.batch_affine = True  # all style FCs of a forward in one batched GEMM while their parameters are frozen
         self.block_resolutions = [2 ** i for i in range(2, self.img_resolution_log2 + 1)]
         channels_dict = {res: min(channel_base // res, channel_max) for res in self.block_resolutions}
+        fp16_resolution = max(2 ** (self.img_resolution_log2 + 1 - num_fp16_res), 8)  # networks.py:442
         self.num_ws = 0
         for res in self.block_resolutions:
             in_channels = channels_dict[res // 2] if res > 4 else 0
             block = SynthesisBlock(in_channels, channels_dict[res], w_dim=w_dim, resolution=res, img_channels=img_channels,
-                                   is_last=(res == img_resolution), **block_kwargs)
+                                   is_last=(res == img_resolution), use_fp16=(res >= fp16_resolution), **block_kwargs)
             self.num_ws += block.num_conv
             if res == img_resolution:
                 self.num_ws += block.num_torgb
@@ -312,9 +320,10 @@ class SynthesisNetwork(torch.nn.Module):
             block_ws.append(ws.narrow(1, w_idx, block.num_conv + block.num_torgb))
             w_idx += block.num_conv
         x = img = None
-        # nothing to differentiate (no_grad, or frozen weights and a constant ws): resident bf16-NHWC inference pipeline
+        # resident_bf16 and nothing to differentiate (no_grad, or frozen weights and a constant ws): the bf16-NHWC inference
+        # pipeline.  With resident_bf16 = False the same model gives the same (fp32-storage) numerics with and without grad.
         no_grad = (not torch.is_grad_enabled()) or not (ws.requires_grad or any(p.requires_grad for p in self.parameters()))
-        fast = no_grad and ws.is_cuda and set(block_kwargs) <= {"noise_mode"} \
+        fast = self.resident_bf16 and no_grad and ws.is_cuda and set(block_kwargs) <= {"noise_mode"} \
             and all(getattr(self, f"b{res}").architecture in ("skip", "orig") for res in self.block_resolutions)
         for res, cur_ws in zip(self.block_resolutions, block_ws):
             if fast:  # inference: activations stay resident as bf16 NHWC, no per-layer layout / modulation passes

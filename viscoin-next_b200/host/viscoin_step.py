@@ -94,7 +94,7 @@ class VisCoINTrainer:
          operands with fp32 accumulation)."""
 
     def __init__(self, device, n_classes=200, seed=0, amp=torch.bfloat16, channels_last=True, params=None, models=None,
-                 deterministic=False, fused_adam=None, fold_bn=True):
+                 deterministic=False, fused_adam=None, fold_bn=True, keep_unfolded=False):
         self.device = torch.device(device)
         self.p = params or VisCoINParams()
         self.amp = amp if self.device.type == "cuda" else None
@@ -131,6 +131,8 @@ class VisCoINTrainer:
                 fakes = synthetic_samples(self.generator_gan, 4, self.device, torch.Generator().manual_seed(seed)).float()
             noise = torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(seed + 1)).to(self.device)
             _models.calibrate_batchnorm(self.classifier, torch.cat([noise, fakes]))
+        if keep_unfolded:  # parity tests: the oracle (HF ResNetModel) loads the classifier's state_dict as it was BEFORE the fold
+            self.classifier_unfolded_state = {k: v.detach().cpu().clone() for k, v in self.classifier.state_dict().items()}
         if self.fold_bn:  # f is frozen and in eval mode: conv + BN is one convolution
             _models.fold_batchnorm(self.classifier)
             if self.channels_last:
@@ -158,7 +160,19 @@ class VisCoINTrainer:
         self.optimizer = torch.optim.Adam(main_params, lr=lr, fused=fused, capturable=cap)
         self._graphs = {}
         self.graph_launches = 0  # libvcn kernel launches replayed from graphs so far
-        self._eager_calls = 0
+        self._eager_calls = {}
+
+    def oracle_state(self):
+        """CPU copies of every state_dict the oracle's ``step_losses`` needs (tests / parity tooling; needs keep_unfolded
+        when the BatchNorms were folded)."""
+        cpu = lambda m: {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+        st = {"classifier": getattr(self, "classifier_unfolded_state", None) or cpu(self.classifier),
+              "concept_extractor": cpu(self.concept_extractor), "explainer": cpu(self.explainer),
+              "viscoin_gan": cpu(self.viscoin_gan), "generator_gan": cpu(self.generator_gan)}
+        st["lpips_convs"] = [(l.weight.detach().cpu().clone(), l.bias.detach().cpu().clone()) for s in self.lpips.slices
+                             for l in s if isinstance(l, torch.nn.Conv2d)]
+        st["lpips_lins"] = [p.detach().cpu().clone() for p in self.lpips.lins]
+        return st
 
     def trainable_numel(self):
         return self.buckets.numel()
@@ -210,10 +224,11 @@ class VisCoINTrainer:
         n = len(real_images)
         key = (n, i > self.p.cd_fid_iteration)
         z = torch.randn(n, self.generator_gan.z_dim, generator=z_generator)
-        if self._eager_calls < warm and key not in self._graphs:
-            # eager warm-up on a SIDE stream: autograd binds each parameter's gradient accumulator to the stream it first
-            # runs on, and the legacy default stream cannot take part in a capture
-            self._eager_calls += 1
+        if self._eager_calls.get(key, 0) < warm and key not in self._graphs:
+            # eager warm-up on a SIDE stream (per graph key: every branch a capture will record has run eagerly first):
+            # autograd binds each parameter's gradient accumulator to the stream it first runs on, and the legacy default
+            # stream cannot take part in a capture
+            self._eager_calls[key] = self._eager_calls.get(key, 0) + 1
             if not hasattr(self, "_side"):
                 self._side = torch.cuda.Stream(device=self.device)
             cur = torch.cuda.current_stream(self.device)
