@@ -7,7 +7,8 @@ installer).  Import as ``viscoin_next_b200`` (the hyphenated directory is not an
 """
 
 from . import _lib  # noqa: F401
-from .host import bias_act, conv2d_resample, dp, fma, lpips_tap, modconv, networks, upfirdn2d, viscoin_models, viscoin_step  # noqa: F401
+from .host import bias_act, conv2d_resample, dp, fma, lpips_tap, misc, modconv, networks, persistence, upfirdn2d, viscoin_models, viscoin_step  # noqa: F401
+from .host.persistence import load_generator, load_reference_pickle, load_viscoin_checkpoint  # noqa: F401
 from . import patch  # noqa: F401
 
-__all__ = ["_lib", "bias_act", "conv2d_resample", "dp", "fma", "lpips_tap", "modconv", "networks", "patch", "upfirdn2d", "viscoin_models", "viscoin_step"]
+__all__ = ["_lib", "bias_act", "conv2d_resample", "dp", "fma", "lpips_tap", "modconv", "load_generator", "load_reference_pickle", "load_viscoin_checkpoint", "misc", "networks", "patch", "persistence", "upfirdn2d", "viscoin_models", "viscoin_step"]

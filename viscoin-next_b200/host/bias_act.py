@@ -13,6 +13,7 @@ import math
 import torch
 
 from .. import _lib
+from .misc import profiled_function as _profiled
 
 
 class _Spec(dict):
@@ -62,6 +63,7 @@ def bias_act(x, b=None, dim=1, act="linear", alpha=None, gain=None, clamp=None, 
     return _BiasAct.apply(x, b, dim, spec.cuda_idx, alpha, gain, clamp, spec.ref, spec.has_2nd_grad)
 
 
+@_profiled
 def _bias_act_ref(x, b=None, dim=1, act="linear", alpha=None, gain=None, clamp=None):
     """Plain torch ops, any device (bias_act.py:93-123)."""
     spec, alpha, gain, clamp = _resolve(act, alpha, gain, clamp)

@@ -26,6 +26,7 @@ formulation in plain torch (any device) - the checker, not a fallback."""
 import torch
 
 from .. import _lib
+from .misc import profiled_function as _profiled
 from . import modconv as _modconv
 from . import upfirdn2d as _upfirdn2d
 
@@ -149,6 +150,7 @@ def _unsupported(what):
                         "configuration; there is no library fallback)" % what)
 
 
+@_profiled
 def conv2d_resample(x, w, f=None, up=1, down=1, padding=0, groups=1, flip_weight=True, flip_filter=False, impl="cuda"):
     """conv2d_resample.py:59-154.  x [N,Cin,H,W]; w [Cout,Cin/groups,kh,kw]; f = setup_filter() result or None."""
     assert impl in ["ref", "cuda"]

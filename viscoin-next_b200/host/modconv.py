@@ -21,6 +21,7 @@ import math
 import torch
 
 from .. import _lib
+from .misc import profiled_function as _profiled
 from . import bias_act as _bias_act
 from . import upfirdn2d as _upfirdn2d
 
@@ -406,6 +407,7 @@ def _check_cuda(x, what):
         raise _lib.VcnError("%s(impl='cuda') needs a CUDA tensor; this build has no CPU fallback (use impl='ref')" % what)
 
 
+@_profiled
 def modconv_layer(x, weight, styles, noise=None, bias=None, up=1, padding=None, resample_filter=None, demodulate=True,
                   flip_weight=True, act="lrelu", alpha=None, gain=None, clamp=None):
     """Fused SynthesisLayer / ToRGBLayer body: bias_act(modulated_conv2d(...), bias, act, gain, clamp)
@@ -426,6 +428,7 @@ def modconv_layer(x, weight, styles, noise=None, bias=None, up=1, padding=None, 
     return y
 
 
+@_profiled
 def modulated_conv2d(x, weight, styles, noise=None, up=1, down=1, padding=0, resample_filter=None, demodulate=True,
                      flip_weight=True, fused_modconv=True, impl="cuda"):
     """Signature of training/networks.py:27-40 (+ impl).  x [N,Cin,H,W], weight [Cout,Cin,k,k], styles [N,Cin],

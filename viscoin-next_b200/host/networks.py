@@ -19,10 +19,12 @@ import numpy as np
 import torch
 
 from . import bias_act as _bias_act
+from .misc import profiled_function as _profiled
 from . import modconv as _modconv
 from . import upfirdn2d as _upfirdn2d
 
 
+@_profiled
 def normalize_2nd_moment(x, dim=1, eps=1e-8):
     return x * (x.square().mean(dim=dim, keepdim=True) + eps).rsqrt()
 
@@ -377,8 +379,27 @@ class Generator(torch.nn.Module):
         return self.synthesis(ws, **synthesis_kwargs)
 
 
+class _StackedParams(torch.autograd.Function):
+    """Identity on `stacked` whose gradient is routed, slice by slice, to the parameters that alias its storage."""
+
+    @staticmethod
+    def forward(ctx, stacked, *params):
+        ctx.n = len(params)
+        return stacked.view_as(stacked)
+
+    @staticmethod
+    def backward(ctx, g):
+        return (None,) + tuple(g[i] for i in range(ctx.n))
+
+
 class MappingNetworkAdapted(torch.nn.Module):
-    """viscoin/models/gan.py:147-234: one FC stack per w; stacks coarse..mid read z1, the others z2."""
+    """viscoin/models/gan.py:147-234: one FC stack per w; stacks coarse..mid read z1, the others z2.
+
+    SURVEY 8(f) N1: with one layer per stack (VisCoIN's default) the 14 FCs (2304 -> 512, lrelu) run as TWO batched GEMMs
+    (the z2-fed stacks 0,1,11,12,13 and the z1-fed stacks 2..10) and ONE ``bias_act`` launch over [14*N, 512] instead of
+    14 GEMMs + 14 ``bias_act`` launches - forward, input gradient and weight gradient alike (baddbmm's autograd is two
+    batched GEMMs).  The 14 weight Parameters keep their names (reference ``state_dict``s load unchanged) but alias one
+    stacked [14, 512, 2304] buffer, so no per-step gather copy exists: Adam updates write through to it."""
 
     def __init__(self, z1_dim, z2_dim, w_dim, num_ws, num_layers=1, coarse_layer=2, mid_layer=10, activation="lrelu",
                  lr_multiplier=0.01):
@@ -393,11 +414,53 @@ class MappingNetworkAdapted(torch.nn.Module):
                                                              lr_multiplier=lr_multiplier) for j in range(num_layers)])
             setattr(self, f"s{i}", stack)
 
+    grouped = True  # batched-GEMM path on CUDA tensors (False: the per-stack loop of the reference)
+
+    def _stacked(self):
+        """(W [L,512,K], B [L,512], order): the stacked buffers the layer Parameters alias, z2-fed stacks first.  Re-built
+        (and the Parameters re-pointed) whenever a Parameter's storage moved (``.to()``, a replaced ``.data``)."""
+        order = [i for i in range(self.num_ws) if (i < self.coarse_layer or i > self.mid_layer)]
+        n2 = len(order)
+        order += [i for i in range(self.num_ws) if not (i < self.coarse_layer or i > self.mid_layer)]
+        layers = [getattr(self, f"s{i}")[0] for i in order]
+        hit = getattr(self, "_stack_cache", None)
+        ok = hit is not None and all(l.weight.data_ptr() == hit[0][j].data_ptr() and l.bias.data_ptr() == hit[1][j].data_ptr()
+                                     and l.weight.device == hit[0].device for j, l in enumerate(layers))
+        if not ok:
+            with torch.no_grad():
+                W = torch.stack([l.weight.detach() for l in layers])
+                B = torch.stack([l.bias.detach() for l in layers])
+                for j, l in enumerate(layers):
+                    l.weight.data = W[j]
+                    l.bias.data = B[j]
+            hit = (W, B, order, n2)
+            self._stack_cache = hit
+        return hit + (layers,)
+
+    def _forward_grouped(self, x1, x2):
+        W, B, order, n2, layers = self._stacked()
+        l0 = layers[0]
+        Wg = _StackedParams.apply(W, *[l.weight for l in layers])
+        Bg = _StackedParams.apply(B, *[l.bias for l in layers])
+        n = x1.shape[0]
+        bias = Bg.unsqueeze(1) * l0.bias_gain if l0.bias_gain != 1 else Bg.unsqueeze(1)
+        y2 = torch.baddbmm(bias[:n2], x2.unsqueeze(0).expand(n2, n, x2.shape[1]), Wg[:n2].transpose(1, 2), alpha=l0.weight_gain)
+        y1 = torch.baddbmm(bias[n2:], x1.unsqueeze(0).expand(len(order) - n2, n, x1.shape[1]), Wg[n2:].transpose(1, 2), alpha=l0.weight_gain)
+        y = _bias_act.bias_act(torch.cat([y2, y1]).reshape(len(order) * n, self.w_dim), None, act=l0.activation)
+        key = (tuple(order), y.device)
+        if getattr(self, "_inv_cache", (None,))[0] != key:
+            inv = torch.empty(len(order), dtype=torch.long)
+            inv[torch.tensor(order)] = torch.arange(len(order))  # y row j holds stack order[j]
+            self._inv_cache = (key, inv.to(y.device))
+        return y.reshape(len(order), n, self.w_dim).index_select(0, self._inv_cache[1]).transpose(0, 1) + self.fixed_w_avg
+
     def forward(self, z1, z2):
         if z1.ndim > 3:
             z1 = z1.reshape(-1, self.z1_dim)
         x1 = normalize_2nd_moment(z1.to(torch.float32))
         x2 = normalize_2nd_moment(z2.to(torch.float32))
+        if self.grouped and x1.is_cuda and self.num_layers == 1 and self.z1_dim == self.z2_dim and self.s0[0].bias is not None:
+            return self._forward_grouped(x1, x2)
         outs = []
         for i in range(self.num_ws):
             x = x2 if (i < self.coarse_layer or i > self.mid_layer) else x1

@@ -14,6 +14,7 @@ import numpy as np
 import torch
 
 from .. import _lib
+from .misc import profiled_function as _profiled
 
 
 def _parse_scaling(scaling):
@@ -83,6 +84,7 @@ def upfirdn2d(x, f, up=1, down=1, padding=0, flip_filter=False, gain=1, impl="cu
     return _Upfirdn2d.apply(x, f, upx, upy, downx, downy, px0, px1, py0, py1, bool(flip_filter), float(gain))
 
 
+@_profiled
 def _upfirdn2d_ref(x, f, up=1, down=1, padding=0, flip_filter=False, gain=1):
     """Plain torch ops, any device (upfirdn2d.py:168-208)."""
     assert isinstance(x, torch.Tensor) and x.ndim == 4
