@@ -303,8 +303,9 @@ def test_weight_gradient_vs_oracle(case):
 def test_conv2d_resample_golden(golden):
     """conv2d_resample(impl='cuda') - every branch networks.py uses (plain 3x3 / 1x1, up=2 3x3 = transposed conv + FIR, up=2 1x1,
     down=2 3x3 = FIR + stride-2 conv, down=2 1x1) - against the outputs and gradients recorded from the reference
-    (conv2d_resample.py:59-154, CONV_CASES).  bf16 tensor-core operands: y <= 1e-2, dx / dw <= 2e-2 (rel-L-inf).  Grouped and
-    asymmetric-padding calls are not on the sm_100a path: loud VcnError, no library fallback."""
+    (conv2d_resample.py:59-154, CONV_CASES).  bf16 tensor-core operands: y <= 1e-2, dx / dw <= 2e-2 (rel-L-inf).  The grouped case
+    (groups = N in the fused-modconv pattern) runs on the per-sample-weight GEMM; asymmetric padding is not on the sm_100a
+    path: loud VcnError, no library fallback."""
     import viscoin_next_b200 as V
     from oracle.make_golden import CONV_CASES
     g = golden("conv_modconv")
@@ -313,7 +314,7 @@ def test_conv2d_resample_golden(golden):
     for name, (xs, ws, kw, use_f) in CONV_CASES.items():
         x = g.t(f"conv.{name}.x", device="cuda").requires_grad_(True)
         w = g.t(f"conv.{name}.w", device="cuda").requires_grad_(True)
-        if name in ("grouped_up2", "asym_pad"):
+        if name == "asym_pad":
             with pytest.raises(V._lib.VcnError):
                 V.conv2d_resample.conv2d_resample(x, w, f=(f4 if use_f else None), **kw)
             continue

@@ -276,15 +276,18 @@ def load_reference_pickle(path_or_file, map_location="cpu"):
         obj = RestrictedUnpickler(io.BytesIO(data)).load()
         if isinstance(obj, int):  # torch.save's legacy (pre-zip) stream begins with its magic number
             obj = torch.load(io.BytesIO(data), map_location=map_location, pickle_module=_PickleModule, weights_only=False)
-        elif map_location is not None:
-            obj = _to(obj, map_location)
-    return _convert(obj)
+    obj = _convert(obj)
+    return _to(obj, map_location) if map_location is not None else obj
 
 
 def _to(obj, device):
+    """Rebuilt modules are constructed on the CPU (their recorded tensors may already be on `device`): move everything."""
     if isinstance(obj, torch.nn.Module) or torch.is_tensor(obj):
         return obj.to(device)
-    if isinstance(obj, dict):
+    if isinstance(obj, VisCoINModels):
+        for k, v in list(obj.__dict__.items()):
+            setattr(obj, k, _to(v, device))
+    elif isinstance(obj, dict):
         for k in list(obj.keys()):
             obj[k] = _to(obj[k], device)
     return obj

@@ -94,10 +94,13 @@ class VisCoINTrainer:
          operands with fp32 accumulation)."""
 
     def __init__(self, device, n_classes=200, seed=0, amp=torch.bfloat16, channels_last=True, params=None, models=None,
-                 deterministic=False, fused_adam=None, fold_bn=True, keep_unfolded=False):
+                 deterministic=False, fused_adam=None, fold_bn=True, keep_unfolded=False, amp_psi="same", resident_bf16=None):
         self.device = torch.device(device)
         self.p = params or VisCoINParams()
         self.amp = amp if self.device.type == "cuda" else None
+        # Psi (trainable) may run at a different precision than the frozen f / VGG-16: "same" = follow `amp`
+        self.amp_psi = self.amp if amp_psi == "same" else (amp_psi if self.device.type == "cuda" else None)
+        self._resident_override = resident_bf16
         self.channels_last = channels_last and self.device.type == "cuda"
         torch.manual_seed(seed)
         if models is None:
@@ -143,7 +146,8 @@ class VisCoINTrainer:
                 _models.fuse_conv_bias_relu(self.classifier)
             _models.fuse_conv_bias_relu(self.lpips)
         self.deterministic = deterministic
-        self.viscoin_gan.synthesis.resident_bf16 = self.amp is not None  # bf16 run: activations stay bf16 NHWC
+        # bf16 run: synthesis activations stay bf16 NHWC between layers, forward and backward
+        self.viscoin_gan.synthesis.resident_bf16 = (self.amp is not None) if self._resident_override is None else bool(self._resident_override)
         self.synthesis_kwargs = {}  # e.g. {'noise_mode': 'const'} for parity runs; the reference passes none (:193)
         _dp.broadcast_parameters([self.classifier, self.concept_extractor, self.explainer, self.viscoin_gan,
                                   self.generator_gan, self.lpips])
@@ -196,7 +200,9 @@ class VisCoINTrainer:
             fake_images = synthetic_samples(self.generator_gan, len(real_images), self.device, z_generator)
         all_images = torch.cat([real_images, fake_images.to(real_images.dtype)])
         classes, hidden = self._f(all_images)
-        with self._autocast():
+        with torch.autocast("cuda", dtype=self.amp_psi or torch.bfloat16, enabled=self.amp_psi is not None):
+            if self.amp_psi is None and self.amp is not None:
+                hidden = [h.float() for h in hidden[-3:]]
             encoded_concepts, extra_info = self.concept_extractor(hidden[-3:])
         encoded_concepts, extra_info = encoded_concepts.float(), extra_info.float()
         explainer_classes = self.explainer(encoded_concepts)
