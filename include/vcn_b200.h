@@ -188,6 +188,19 @@ int vcn_lpips_tap_fwd(const void* fa, const void* fb, int dtype, const int64_t a
 int vcn_lpips_tap_bwd(const void* fa, const void* fb, int dtype, const int64_t as[4], const int64_t bs[4],
                       const float* lin, const float* gval, void* da, int n, int c, int h, int w, void* stream);
 
+/* ---- frozen-network passes (LPIPS VGG-16 and the classifier f around the hot path) ------------------------
+ * 16-bit (bf16 / f16) dense channels-last tensors [n,h,w,c], c a multiple of 8, even h and w.  These replace ATen's
+ * max_pool2d / max_pool2d_with_indices_backward / add / threshold_backward passes of
+ * viscoin/training/losses.py:111-123 (lpips VGG-16) and of the ResNet-50 behind viscoin/models/classifiers.py:83-92:
+ *   vcn_maxpool2x2_fwd       y[n,h/2,w/2,c] = max of each 2x2 window (stride 2)
+ *   vcn_relu_mask_bwd        dz = (g + g2) * (y > 0); g2 may be NULL; flat arrays of numel elements
+ *   vcn_maxpool2x2_relu_bwd  dz[n,h,w,c] = (gtap + U(gpool)) * (y > 0), U = max-pool backward (gradient to the first
+ *                            maximum of the window in row-major scan order); gtap may be NULL */
+int vcn_maxpool2x2_fwd(const void* x, void* y, int dtype, int n, int h, int w, int c, void* stream);
+int vcn_relu_mask_bwd(const void* y, const void* g, const void* g2, void* dz, int dtype, int64_t numel, void* stream);
+int vcn_maxpool2x2_relu_bwd(const void* y, const void* gpool, const void* gtap, void* dz, int dtype, int n, int h, int w, int c,
+                            void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,36 +60,38 @@ def test_train_step_matches_oracle_l1_l2_reconstruction():
 
 
 def test_train_step_matches_oracle_all_losses():
-    """All six terms (beta = 3 LPIPS, gamma = 0.1 classifier agreement).  Loss VALUES <= 2e-2.  With random-init VGG /
-    ResNet features the perceptual gradient is ill-conditioned in the rebuilt image (unit-normalisation of near-zero
-    feature vectors): the bf16-operand rounding of the synthesis forward is amplified in d(rec)/d(image), so gradients
-    are gated on direction.  test_all_losses_fp32_reference_modules_conditioning shows what an fp32 GPU run of the
-    reference's own modules reaches on the same harness."""
+    """All six terms (beta = 3 LPIPS, gamma = 0.1 classifier agreement): loss values <= 2e-2 (measured <= 2e-3), every
+    parameter group's gradient rel-L2 <= 3e-2 and cosine >= 0.9995 (measured 1.4e-2 / 0.99991), Adam update cosine >= 0.98.
+    (Round 1 gated this test at cosine 0.8 and blamed the random-init LPIPS: the cause was the random-init ResNet-50 f,
+    which amplifies any rounding ~1.3x per block; with the harness' conditioned initialisation - viscoin_models.
+    condition_random_init - the bf16-operand synthesis path matches the fp32 oracle as closely here as in the L1+L2 test.)"""
     with _tf32_off():
         out = compare(FP32_CONFIG, 3.0, 0.1, n=1, label="fp32lib_all")
     summarize(out)
     assert all(v["rel"] <= 2e-2 for v in out["losses"].values()), out["losses"]
-    bad = {k: v for k, v in out["grads"].items() if v["cos"] < 0.8}
+    bad = {k: v for k, v in _groups(out).items() if v["cos"] < 0.9995 or v["rel_l2"] > 3e-2}
     assert not bad, bad
+    assert all(v["update_cos"] >= 0.98 for v in out["adam"].values()), out["adam"]
 
 
 # ---- the benchmarked configuration ------------------------------------------------------------------------------------
 
 
-# Gates of the benchmarked configuration = the errors measured on a B200 (profiles/parity_r2.json) with a 2x margin on
-# (1 - cosine) and on rel-L2.  They are bf16 numbers at RANDOM INIT, where every gradient is a sum of nearly cancelling
-# terms: the same harness gives cosine 0.99993 / rel-L2 1.2e-2 with fp32 library networks + fp32-storage synthesis
-# (test_train_step_matches_oracle_l1_l2_reconstruction) and 0.9998 for the reference's own modules in fp32 on the GPU;
-# test_bench_config_error_decomposition attributes the rest to its sources (bf16 autocast of f / Psi vs bf16-resident synthesis).
+# Gates of the benchmarked configuration = the errors measured on a B200 (profiles/parity_r2.json) with a ~2x margin on
+# (1 - cosine) and on rel-L2.  Measured: Psi rel-L2 1.35e-1 / cos 0.9908, adapted mapping 3.2e-2 / 0.99955, Theta 7.8e-3;
+# Adam-update cosine 0.893 / 0.979 / 0.996.  test_bench_config_error_decomposition attributes them: the bf16-resident
+# synthesis kernels alone give 1.0e-2 (cos 0.99995) - the rest is bf16 autocast arithmetic in the LIBRARY networks f / Psi
+# (plain torch autocast alone: 1.26e-1 / 3.7e-2).  Yardstick on the same harness: the reference's own modules with torch's
+# default TF32 convolutions against its CPU path: Psi 4.0e-2, mapping 5.9e-3 (tf32_reference_modules_all).
 BENCH_GATES = {  # group -> (min cosine, max rel-L2, min Adam-update cosine)
-    "concept_extractor": (0.82, 0.85, 0.40),
-    "explainer": (0.98, 0.30, 0.95),
-    "viscoin_gan": (0.95, 0.48, 0.68),
+    "concept_extractor": (0.98, 0.27, 0.79),
+    "explainer": (0.999, 0.03, 0.98),
+    "viscoin_gan": (0.999, 0.065, 0.955),
 }
 
 
 def _check_bench(out, all_losses):
-    assert all(v["rel"] <= 3e-2 for v in out["losses"].values()), out["losses"]
+    assert all(v["rel"] <= 1e-2 for v in out["losses"].values()), out["losses"]  # measured <= 1.5e-3
     for name, v in _groups(out).items():
         cos, l2, upd = BENCH_GATES[name.split(" ")[0]]
         assert v["cos"] >= cos and v["rel_l2"] <= l2, (name, v)
@@ -139,41 +141,43 @@ def test_bench_config_error_decomposition():
 def test_step_graphed_equals_eager_step():
     """``step_graphed`` (what bench.py times: the whole iteration replayed from one CUDA graph) against the eager ``step``
     on an identical replica: same z stream, noise_mode='const', dropout off, four iterations (two eager warm-ups, the
-    capture, one replay).  Every kernel of the step is deterministic except atomically accumulated reductions, so the loss
-    trajectories and the final parameters must agree to fp32 reduction-order noise."""
+    capture, one replay).  The yardstick is a SECOND eager replica: a few reductions of the step accumulate with atomics
+    (bias / style gradient sums, cuDNN's split-k weight gradients), so two eager runs already differ in the last bits and
+    Adam's first steps (lr * sign(g) per element) turn that into +-lr flips of near-zero-gradient elements.  The graphed
+    run must sit inside that run-to-run noise (3x margin), i.e. capturing the step does not change what it computes."""
     import viscoin_next_b200 as V
     dev = torch.device("cuda:0")
     trs = []
-    for _ in range(2):
+    for _ in range(3):
         # noise strengths stay at their initial 0: `synthetic_samples` draws its per-layer noise from the device RNG
         # (utils.py:37-38 passes no noise_mode), whose stream a captured graph and an eager run do not share
         tr = V.viscoin_step.VisCoINTrainer(dev, seed=3, deterministic=True)
         tr.synthesis_kwargs = {"noise_mode": "const"}
         trs.append(tr)
-    eager, graphed = trs
+    eager, eager2, graphed = trs
     g = torch.Generator().manual_seed(0)
     real = torch.randn(2, 3, 256, 256, generator=g)
     labels = torch.randint(0, 200, (2,), generator=g)
-    ze, zg = torch.Generator().manual_seed(9), torch.Generator().manual_seed(9)
-    worst, bitwise = 0.0, True
+    gens = [torch.Generator().manual_seed(9) for _ in range(3)]
+    worst = {"graphed": 0.0, "eager2": 0.0}
     for it in range(4):
-        a = eager.step(real.to(dev), labels.to(dev), 1000, z_generator=ze)
-        a = {k: float(v) for k, v in a.items()}
-        b = graphed.step_graphed(real, labels, 1000, z_generator=zg)
-        b = {k: float(v) for k, v in b.items()}
+        a = {k: float(v) for k, v in eager.step(real.to(dev), labels.to(dev), 1000, z_generator=gens[0]).items()}
+        b = {k: float(v) for k, v in eager2.step(real.to(dev), labels.to(dev), 1000, z_generator=gens[1]).items()}
+        c = {k: float(v) for k, v in graphed.step_graphed(real, labels, 1000, z_generator=gens[2]).items()}
         for k in a:
-            worst = max(worst, abs(a[k] - b[k]) / max(abs(a[k]), 1e-6))
-            bitwise = bitwise and a[k] == b[k]
+            worst["eager2"] = max(worst["eager2"], abs(a[k] - b[k]) / max(abs(a[k]), 1e-6))
+            worst["graphed"] = max(worst["graphed"], abs(a[k] - c[k]) / max(abs(a[k]), 1e-6))
+        print("iteration %d: %s" % (it, {k: "%.3e / %.3e" % (abs(a[k] - b[k]), abs(a[k] - c[k])) for k in a}))
     assert (2, True) in graphed._graphs, "the graph was never captured"
-    pe = torch.cat([p.detach().flatten() for p in eager.concept_extractor.parameters()] +
-                   [p.detach().flatten() for p in eager.viscoin_gan.mapping.parameters()])
-    pg = torch.cat([p.detach().flatten() for p in graphed.concept_extractor.parameters()] +
-                   [p.detach().flatten() for p in graphed.viscoin_gan.mapping.parameters()])
-    m = metrics(pg, pe)
-    bitwise = bitwise and bool(torch.equal(pe, pg))
-    print("graphed vs eager: worst loss rel diff %.2e, params rel-L2 %.2e max-abs %.2e, bitwise %s" % (worst, m["rel_l2"], m["max_abs"], bitwise))
-    record("graphed_vs_eager", {"worst_loss_rel": worst, "params": m, "bitwise_equal": bitwise, "iterations": 4})
-    assert worst <= 1e-3 and m["rel_l2"] <= 1e-5
+    flat = lambda tr: torch.cat([p.detach().flatten() for p in tr.concept_extractor.parameters()] +
+                                [p.detach().flatten() for p in tr.viscoin_gan.mapping.parameters()])
+    pe, pe2, pg = flat(eager), flat(eager2), flat(graphed)
+    m2, mg = metrics(pe2, pe), metrics(pg, pe)
+    print("eager2 vs eager : worst loss rel diff %.2e, params rel-L2 %.2e max-abs %.2e" % (worst["eager2"], m2["rel_l2"], m2["max_abs"]))
+    print("graphed vs eager: worst loss rel diff %.2e, params rel-L2 %.2e max-abs %.2e" % (worst["graphed"], mg["rel_l2"], mg["max_abs"]))
+    record("graphed_vs_eager", {"worst_loss_rel": worst["graphed"], "params": mg, "bitwise_equal": bool(torch.equal(pe, pg)), "iterations": 4,
+                                "eager_rerun_worst_loss_rel": worst["eager2"], "eager_rerun_params": m2})
+    assert worst["graphed"] <= max(3 * worst["eager2"], 1e-5) and mg["rel_l2"] <= max(3 * m2["rel_l2"], 1e-7)
 
 
 def test_all_losses_fp32_reference_modules_conditioning():
@@ -206,6 +210,7 @@ def test_all_losses_fp32_reference_modules_conditioning():
     theta.load_state_dict(mine[2].state_dict(), strict=True)
     # BatchNorm statistics of the random-init classifier (what VisCoINTrainer does when it builds the models itself)
     cls = mine[0].cuda()
+    VM.condition_random_init(cls)  # as VisCoINTrainer does for its own random-init harness
     with torch.no_grad():
         fakes = G.cuda()(torch.randn(4, 512, generator=torch.Generator().manual_seed(11)).cuda(), None).float()
     VM.calibrate_batchnorm(cls, torch.cat([torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(12)).cuda(), fakes]))
@@ -215,6 +220,11 @@ def test_all_losses_fp32_reference_modules_conditioning():
     summarize(out)
     assert all(v["rel"] <= 1e-3 for v in out["losses"].values()), out["losses"]
     assert all(v["cos"] >= 0.8 for v in _groups(out).values()), _groups(out)
+    # the yardstick: the reference's DEFAULT GPU arithmetic (torch leaves cudnn.allow_tf32 on; only the GAN trainer turns it
+    # off, training_loop.py:128-129) against its own CPU path on this harness
+    out = compare(FP32_CONFIG, 3.0, 0.1, n=1, label="tf32_reference_modules_all", with_adam=False,
+                  models=(cls, psi, theta, G, GA, lp))
+    summarize(out)
 
 
 def test_train_step_updates_and_is_finite():

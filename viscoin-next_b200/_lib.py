@@ -63,6 +63,9 @@ SIGNATURES = {
     "vcn_lpips_tap_bwd": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     "vcn_conv_wgrad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "vcn_demod_grad": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "vcn_maxpool2x2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vcn_relu_mask_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i64, _vp]),
+    "vcn_maxpool2x2_relu_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
 }
 
 _lock = threading.Lock()

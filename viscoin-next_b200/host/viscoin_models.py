@@ -28,6 +28,25 @@ class Classifier(nn.Module):
         return self.linear(output_state), results["hidden_states"]
 
 
+def condition_random_init(model, residual_gain=0.25):
+    """Random-init harness only.  HF initialises every BatchNorm weight to 1, so each bottleneck adds a unit-variance
+    branch to its shortcut and a random-init ResNet-50 is a chaotic map: measured on a B200, a relative input perturbation
+    grows ~1.3x per bottleneck - 16 blocks turn bf16's 4e-3 rounding into a 50 % error of the last hidden state whatever
+    the implementation (cuDNN under autocast and the fused path alike), which buries the arithmetic a parity test is
+    meant to compare.  Trained networks are not like that; the standard remedy at initialisation ("zero-init residual",
+    Goyal et al. 2017) scales the LAST BatchNorm weight of every residual branch down.  Same FLOPs, same kernels."""
+    n = 0
+    with torch.no_grad():
+        for m in model.modules():
+            layer = getattr(m, "layer", None)
+            if isinstance(layer, nn.Sequential) and hasattr(m, "shortcut") and len(layer) > 0:
+                bn = getattr(layer[-1], "normalization", None)
+                if isinstance(bn, nn.BatchNorm2d):
+                    bn.weight.mul_(residual_gain)
+                    n += 1
+    return n
+
+
 def calibrate_batchnorm(model, images):
     """Random-init harness only (the reference always loads a trained f): one forward in train mode with cumulative
     averaging so that every BatchNorm's running statistics equal the batch statistics of `images`.  Without it a
@@ -167,8 +186,11 @@ class LPIPS(nn.Module):
         self.requires_grad_(False)
         self.eval()
         self.fused = True  # CUDA tensors: fused tap kernels (False = plain torch formulation)
+        self.feature_fn = None  # frozen_nets.FusedVGGFeatures: the bf16 channels_last fast path of the feature stack
 
     def features(self, x):
+        if self.feature_fn is not None and x.is_cuda:
+            return self.feature_fn(x)
         out = []
         x = (x - self.shift) / self.scale
         for s in self.slices:

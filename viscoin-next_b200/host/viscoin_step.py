@@ -94,7 +94,8 @@ class VisCoINTrainer:
          operands with fp32 accumulation)."""
 
     def __init__(self, device, n_classes=200, seed=0, amp=torch.bfloat16, channels_last=True, params=None, models=None,
-                 deterministic=False, fused_adam=None, fold_bn=True, keep_unfolded=False, amp_psi="same", resident_bf16=None):
+                 deterministic=False, fused_adam=None, fold_bn=True, keep_unfolded=False, amp_psi="same", resident_bf16=None,
+                 fused_frozen=True, vgg_impl=None):
         self.device = torch.device(device)
         self.p = params or VisCoINParams()
         self.amp = amp if self.device.type == "cuda" else None
@@ -128,8 +129,10 @@ class VisCoINTrainer:
             for m in (self.classifier, self.lpips):  # frozen nets only: trainable grads are views into flat buckets
                 m.to(memory_format=torch.channels_last)
         if models is None:
-            # random-init harness: give f's BatchNorms the statistics of the images it will see (noise-like "real"
-            # images and smooth generated ones); a trained f ships with its own (see calibrate_batchnorm)
+            # random-init harness: damp f's residual branches (a random-init ResNet-50 amplifies rounding ~1.3x per block,
+            # see condition_random_init) and give its BatchNorms the statistics of the images it will see (noise-like
+            # "real" images and smooth generated ones); a trained f ships with its own weights and statistics
+            _models.condition_random_init(self.classifier)
             with torch.no_grad():
                 fakes = synthetic_samples(self.generator_gan, 4, self.device, torch.Generator().manual_seed(seed)).float()
             noise = torch.randn(4, 3, 256, 256, generator=torch.Generator().manual_seed(seed + 1)).to(self.device)
@@ -145,6 +148,15 @@ class VisCoINTrainer:
             if self.fold_bn:
                 _models.fuse_conv_bias_relu(self.classifier)
             _models.fuse_conv_bias_relu(self.lpips)
+        # frozen f and VGG-16 on the fused bf16 channels_last path (frozen_nets): one launch per conv + bias + ReLU (+ residual),
+        # this package's pool / mask kernels between them, no autocast casts.  Same arithmetic as the autocast path it replaces.
+        self.fused_frozen = bool(fused_frozen) and self.amp == torch.bfloat16 and self.fold_bn and self.device.type == "cuda"
+        self._fused_f = None
+        if self.fused_frozen:
+            from . import frozen_nets as _fz
+            self._fused_f = _fz.FusedResNet(self.classifier)
+            if hasattr(self.lpips, "slices"):
+                self.lpips.feature_fn = _fz.FusedVGGFeatures(self.lpips, impl=vgg_impl or os.environ.get("VCN_VGG_IMPL", "cudnn"))
         self.deterministic = deterministic
         # bf16 run: synthesis activations stay bf16 NHWC between layers, forward and backward
         self.viscoin_gan.synthesis.resident_bf16 = (self.amp is not None) if self._resident_override is None else bool(self._resident_override)
@@ -185,6 +197,8 @@ class VisCoINTrainer:
         return torch.autocast("cuda", dtype=self.amp, enabled=self.amp is not None)
 
     def _f(self, images):
+        if self._fused_f is not None:
+            return self._fused_f(images)
         if self.channels_last:
             images = images.contiguous(memory_format=torch.channels_last)
         with self._autocast():
