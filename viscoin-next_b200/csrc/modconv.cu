@@ -14,6 +14,12 @@
 // A "plan" lists the taps; taps are partitioned into up to 4 accumulator groups (TMEM column ranges): the plain
 // convolution has one group of kh*kw taps, the stride-2 transposed convolution has its 4 output phases as groups
 // (4+2+2+1 taps) so that it costs exactly the reference's FLOPs (2*9*Cin*Cout per INPUT pixel).
+// CTA pairs (`pair`): for wide out-channel tiles the kernel runs as 2-CTA clusters with tcgen05.mma.cta_group::2 - one
+// MMA covers 256 pixels (128 accumulator rows in each CTA's TMEM) x N_TILE channels, each CTA stages its own 128-pixel A
+// tile and HALF of the weight tile, and the tensor cores of both SMs read the two halves from both shared memories: per
+// flop every SM ingests 1/3 less operand bytes through TMA and its shared-memory port.  Both producers complete their TMA
+// bytes on the LEADER's full barrier; the leader's MMA thread releases stages / publishes accumulators to both CTAs with
+// multicast commits; the peer's epilogue warps hand accumulator stages back with remote mbarrier arrives.
 #include <stdlib.h>
 #include <string.h>
 
@@ -31,6 +37,10 @@ constexpr int kMaxPhases = 4;
 constexpr int kEpilogueWarps = 8;  // two warps per TMEM lane quarter, alternating 32-column chunks (the epilogue bounds the small-K tiles)
 constexpr int kThreads = 64 + kEpilogueWarps * 32;
 constexpr uint32_t kABytes = kBlockM * kBlockK * 2;
+#ifndef VCN_CONV_PROF
+#define VCN_CONV_PROF 0  // 1: per-role cycle counters (tools/prof_kernels.py, debug builds only); 0 in the product library
+#endif
+constexpr bool kProf = VCN_CONV_PROF != 0;
 
 struct ConvTap {
   int dy, dx;  // pixel shift of the A tile in the M grid
@@ -49,6 +59,8 @@ struct IgemmArgs {
   int tw, th, tn, tiles_w, tiles_h, tiles_m, tiles_total;
   int n_tile, kblocks_c, stages, tmem_cols;
   int swap;            // 1: operands swapped - UMMA M = 128 out-channels (weights), N = 256 pixels (see header)
+  int pair;            // 1: 2-CTA clusters, cta_group::2 (tw/th/tn describe ONE CTA's 128-pixel half of the pair tile)
+  int pair_dim;        // the pair tile = two half tiles stacked along w (0), h (1) or n (2)
   int log_tw, log_th;  // swap: tile extents are powers of two
   uint32_t pix_bytes, w_bytes;  // bytes of the pixel / weight operand in one pipeline stage
   // staged output (16-bit channels-fastest y): the epilogue writes a 128B-swizzled [pixel][64 ch] tile per 64-channel
@@ -135,7 +147,9 @@ __device__ __forceinline__ void epilogue_dispatch(const IgemmArgs& a, const uint
 // Profiling aid (VCN_CONV_PROFILE=1): cycle counters summed over CTAs, read back with vcn_conv_profile_counters().
 //  [0] epilogue busy  [1] epilogue waiting for an accumulator  [2] MMA warp waiting for a drained accumulator
 //  [3] MMA warp waiting for operands  [4] tiles  [5] TMA producer waiting for a free stage  [6] k-blocks
+#if VCN_CONV_PROF
 __device__ unsigned long long g_conv_prof[8];
+#endif
 
 struct alignas(64) OutMaps {
   CUtensorMap m[kMaxPhases];  // per output phase: the strided view y[n, g_oy::o_mul, g_ox::o_mul, :]
@@ -145,8 +159,10 @@ struct TileCoord {
   int x0, y0, n0, co0, phase;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const IgemmArgs& a, int tile) {
-  // m-tiles fastest: consecutive CTAs share the weight tile (L2 reuse of B), then phases, then out-channel tiles
+template <bool PAIR>
+__device__ __forceinline__ TileCoord decode_tile(const IgemmArgs& a, int tile, int rank) {
+  // m-tiles fastest: consecutive CTAs share the weight tile (L2 reuse of B), then phases, then out-channel tiles.
+  // pair mode: `tile` indexes pair tiles (two half tiles along pair_dim); this CTA owns half `rank`.
   int mt = tile % a.tiles_m;
   int r = tile / a.tiles_m;
   TileCoord t;
@@ -154,7 +170,11 @@ __device__ __forceinline__ TileCoord decode_tile(const IgemmArgs& a, int tile) {
   t.co0 = (r / a.num_phases) * a.n_tile;
   const int wi = mt % a.tiles_w; mt /= a.tiles_w;
   const int hi = mt % a.tiles_h;
-  t.x0 = wi * a.tw; t.y0 = hi * a.th; t.n0 = (mt / a.tiles_h) * a.tn;
+  const int ni = mt / a.tiles_h;
+  const int sw = (PAIR && a.pair_dim == 0) ? 1 : 0, sh = (PAIR && a.pair_dim == 1) ? 1 : 0, sn = (PAIR && a.pair_dim == 2) ? 1 : 0;
+  t.x0 = ((wi << sw) + (sw ? rank : 0)) * a.tw;
+  t.y0 = ((hi << sh) + (sh ? rank : 0)) * a.th;
+  t.n0 = ((ni << sn) + (sn ? rank : 0)) * a.tn;
   return t;
 }
 
@@ -242,6 +262,10 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
+// PAIR = false: one CTA per tile, tcgen05 cta_group::1 only.  PAIR = true: 2-CTA clusters, cta_group::2 only.  Two
+// instantiations because the driver refuses to launch a kernel that contains cta_group::2 instructions without a cluster
+// (cudaErrorInvalidClusterSize), whichever path would run.
+template <bool PAIR>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ OutMaps om, const __grid_constant__ IgemmArgs a) {
@@ -258,23 +282,30 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   float* s_par = reinterpret_cast<float*>(tmem_ptr_smem + 4);  // [2 acc stages][scale n_tile | bias n_tile]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;                  // 0 = leader of the CTA pair (issues the MMAs)
+  const int tile0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;   // persistent walk over (pair) tiles
+  const int tile_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < a.stages; ++s) {
-      mbar_init(full_bar + s, 1);
+      mbar_init(full_bar + s, 1);   // pair mode: only the leader's is used (both producers' TMA bytes land on it)
       mbar_init(empty_bar + s, 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar + s, 1);
-      mbar_init(tmem_empty_bar + s, kEpilogueWarps);
+      mbar_init(tmem_empty_bar + s, PAIR ? 2 * kEpilogueWarps : kEpilogueWarps);  // pair: the peer's warps arrive remotely
     }
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc(tmem_ptr_smem, (uint32_t)a.tmem_cols);
+  if (warp == 2) {
+    if constexpr (PAIR) tmem_alloc_2cta(tmem_ptr_smem, (uint32_t)a.tmem_cols);
+    else tmem_alloc(tmem_ptr_smem, (uint32_t)a.tmem_cols);
+  }
   tcgen05_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();  // barrier inits + the pair's TMEM allocation visible to both CTAs
+  else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
@@ -284,49 +315,61 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int s = 0;
       uint32_t ph = 0;
       long long prof_wait = 0;
-      for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x) {
-        const TileCoord tc = decode_tile(a, tile);
+      const int co_half = PAIR ? rank * (a.n_tile >> 1) : 0;  // pair: this CTA stages its half of the weight tile
+      for (int tile = tile0; tile < a.tiles_total; tile += tile_step) {
+        const TileCoord tc = decode_tile<PAIR>(a, tile, rank);
         const int nw = a.w_per_sample ? tc.n0 : 0;
         for (int t = a.phase_first[tc.phase]; t < a.phase_first[tc.phase + 1]; ++t) {
           const ConvTap tap = a.taps[t];
           const int ax = tc.x0 * a.a_mul + tap.dx, ay = tc.y0 * a.a_mul + tap.dy;
           for (int cb = 0; cb < a.kblocks_c; ++cb) {
-            const long long t0 = a.prof ? clock64() : 0;
+            const long long t0 = (kProf && a.prof) ? clock64() : 0;
             mbar_wait(empty_bar + s, ph ^ 1u);
-            if (a.prof) prof_wait += clock64() - t0;
+            if (kProf && a.prof) prof_wait += clock64() - t0;
             unsigned char* sa = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(full_bar + s, stage_bytes);
-            tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, ax, ay, tc.n0);
-            tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * kBlockK, tc.co0, tap.wtap, nw);
+            if constexpr (!PAIR) {
+              mbar_expect_tx(full_bar + s, stage_bytes);
+              tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, ax, ay, tc.n0);
+              tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * kBlockK, tc.co0, tap.wtap, nw);
+            } else {
+              // both CTAs load into their OWN shared memory and complete the bytes on the LEADER's barrier, which the
+              // leader arms for the whole pair (a complete_tx that overtakes the expect_tx only drives the count negative)
+              if (rank == 0) mbar_expect_tx(full_bar + s, 2u * stage_bytes);
+              const uint32_t lead_bar = mapa_u32(full_bar + s, 0);
+              tma_load_4d_2cta(sa, &tmap_a, lead_bar, cb * kBlockK, ax, ay, tc.n0);
+              tma_load_4d_2cta(sa + a.pix_bytes, &tmap_b, lead_bar, cb * kBlockK, tc.co0 + co_half, tap.wtap, nw);
+            }
             if (++s == a.stages) { s = 0; ph ^= 1u; }
           }
         }
       }
+#if VCN_CONV_PROF
       if (a.prof) atomicAdd(&g_conv_prof[5], (unsigned long long)prof_wait);
+#endif
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {  // pair mode: the leader issues for both CTAs
       const int acc_cols = a.swap ? 256 : a.n_tile;
-      const uint32_t idesc = umma_idesc_bf16_f32(kBlockM, acc_cols);
+      const uint32_t idesc = umma_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, acc_cols);
       int s = 0;
       uint32_t ph = 0;
       int tile_iter = 0;
       long long prof_acc = 0, prof_ops = 0, prof_kb = 0;
-      for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
-        const TileCoord tc = decode_tile(a, tile);
+      for (int tile = tile0; tile < a.tiles_total; tile += tile_step, ++tile_iter) {
+        const TileCoord tc = decode_tile<PAIR>(a, tile, rank);
         const int num_kb = (a.phase_first[tc.phase + 1] - a.phase_first[tc.phase]) * a.kblocks_c;
         const int as = tile_iter & 1;
         const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
-        long long t0 = a.prof ? clock64() : 0;
-        mbar_wait(tmem_empty_bar + as, aph ^ 1u);  // epilogue has drained this accumulator stage
-        if (a.prof) prof_acc += clock64() - t0;
+        long long t0 = (kProf && a.prof) ? clock64() : 0;
+        mbar_wait(tmem_empty_bar + as, aph ^ 1u);  // epilogue (of both CTAs in pair mode) has drained this accumulator stage
+        if (kProf && a.prof) prof_acc += clock64() - t0;
         tcgen05_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(as * acc_cols);
         for (int kb = 0; kb < num_kb; ++kb) {
-          if (a.prof) t0 = clock64();
+          if (kProf && a.prof) t0 = clock64();
           mbar_wait(full_bar + s, ph);
-          if (a.prof) { prof_ops += clock64() - t0; ++prof_kb; }
+          if (kProf && a.prof) { prof_ops += clock64() - t0; ++prof_kb; }
           tcgen05_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
           const uint64_t dpix = umma_desc_k_sw128(sa), dwt = umma_desc_k_sw128(sa + a.pix_bytes);
@@ -334,18 +377,23 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
-            umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            if constexpr (PAIR) umma_bf16_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            else umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(empty_bar + s);
+          if constexpr (PAIR) umma_commit_2cta(empty_bar + s, 3);  // frees stage s in BOTH CTAs
+          else umma_commit(empty_bar + s);
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
-        umma_commit(tmem_full_bar + as);
+        if constexpr (PAIR) umma_commit_2cta(tmem_full_bar + as, 3);  // accumulator ready: both CTAs' epilogues
+        else umma_commit(tmem_full_bar + as);
       }
+#if VCN_CONV_PROF
       if (a.prof) {
         atomicAdd(&g_conv_prof[2], (unsigned long long)prof_acc);
         atomicAdd(&g_conv_prof[3], (unsigned long long)prof_ops);
         atomicAdd(&g_conv_prof[6], (unsigned long long)prof_kb);
       }
+#endif
     }
   } else {
     // ===== epilogue: warps 2..9, two per TMEM lane quarter (warp % 4), alternating 32-column chunks =====
@@ -361,8 +409,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     long long prof_busy = 0, prof_wait = 0;
     if (a.swap) {
       // lane = out channel, columns = the 256 pixels of the tile (one sample per tile: tn == 1)
-      for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
-        const TileCoord tc = decode_tile(a, tile);
+      for (int tile = tile0; tile < a.tiles_total; tile += tile_step, ++tile_iter) {
+        const TileCoord tc = decode_tile<PAIR>(a, tile, rank);
         const int as = tile_iter & 1;
         const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
         const int co = tc.co0 + m;
@@ -376,9 +424,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (et == 0) tma_store_wait_read();
           named_bar_sync(1, kEpilogueWarps * 32);
         }
-        long long t0 = a.prof ? clock64() : 0;
+        long long t0 = (kProf && a.prof) ? clock64() : 0;
         mbar_wait(tmem_full_bar + as, aph);
-        if (a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
+        if (kProf && a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
         tcgen05_fence_after();
         for (int c = cg0; c < 256; c += cg_step) {
           uint32_t acc[32];
@@ -422,7 +470,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         tcgen05_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tmem_empty_bar + as);
-        if (a.prof) prof_busy += clock64() - t0;
+        if (kProf && a.prof) prof_busy += clock64() - t0;
         if (a.stage_out) {
           fence_proxy_async();  // generic-proxy writes of the staging tile -> visible to TMA
           named_bar_sync(2, kEpilogueWarps * 32);
@@ -434,8 +482,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
       }
     } else
-    for (int tile = blockIdx.x; tile < a.tiles_total; tile += gridDim.x, ++tile_iter) {
-      const TileCoord tc = decode_tile(a, tile);
+    for (int tile = tile0; tile < a.tiles_total; tile += tile_step, ++tile_iter) {
+      const TileCoord tc = decode_tile<PAIR>(a, tile, rank);
       const int as = tile_iter & 1;
       const uint32_t aph = (uint32_t)(tile_iter >> 1) & 1u;
       float* sp = s_par + as * 2 * a.n_tile;
@@ -460,9 +508,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int co_end = min(a.cout, tc.co0 + a.n_tile);  // channels past the tile belong to another CTA
       if (a.stage_out && et == 0) tma_store_wait_read();  // previous tile's TMA stores have read the staging tile
       named_bar_sync(1, kEpilogueWarps * 32);
-      long long t0 = a.prof ? clock64() : 0;
+      long long t0 = (kProf && a.prof) ? clock64() : 0;
       mbar_wait(tmem_full_bar + as, aph);
-      if (a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
+      if (kProf && a.prof) { const long long t1 = clock64(); prof_wait += t1 - t0; t0 = t1; }
       tcgen05_fence_after();
       for (int c = cg0; c < a.n_tile; c += cg_step) {
         if (tc.co0 + c >= a.cout) break;  // warp-uniform
@@ -494,11 +542,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           else if (a.y_dtype == VCN_F16) epilogue_dispatch<__half>(a, acc, static_cast<__half*>(a.y) + yoff, tc.co0 + c, co_end, noise, scp, bip, has_scale, stg_row, m & 7, c);
         }
       }
-      // hand the accumulator stage back to the MMA warp
+      // hand the accumulator stage back to the MMA warp (pair mode: the leader's barrier, remotely from the peer CTA)
       tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tmem_empty_bar + as);
-      if (a.prof) prof_busy += clock64() - t0;
+      if (lane == 0) {
+        if constexpr (PAIR) {
+          if (rank != 0) mbar_arrive_cluster(mapa_u32(tmem_empty_bar + as, 0));
+          else mbar_arrive(tmem_empty_bar + as);
+        } else {
+          mbar_arrive(tmem_empty_bar + as);
+        }
+      }
+      if (kProf && a.prof) prof_busy += clock64() - t0;
       if (a.stage_out) {
         fence_proxy_async();
         named_bar_sync(2, kEpilogueWarps * 32);
@@ -510,17 +565,21 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
     if (a.stage_out && et == 0) tma_store_wait_all();
+#if VCN_CONV_PROF
     if (a.prof && et == 0) {
       atomicAdd(&g_conv_prof[0], (unsigned long long)prof_busy);
       atomicAdd(&g_conv_prof[1], (unsigned long long)prof_wait);
       atomicAdd(&g_conv_prof[4], (unsigned long long)tile_iter);
     }
+#endif
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();  // the peer may still be arriving on this CTA's barriers / the leader's MMAs read the peer's smem
+  else __syncthreads();
   if (warp == 2) {
     tcgen05_fence_after();
-    tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+    if constexpr (PAIR) tmem_dealloc_2cta(tmem_base, (uint32_t)a.tmem_cols);
+    else tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
   }
 }
 
@@ -541,6 +600,46 @@ void choose_tile(int gw, int gh, int n, int one_sample, int pixels, int max_w, i
       if (best < 0 || tiles < best) { best = tiles; *tw = w; *th = h; *tn = nn; }
     }
   }
+}
+
+// CTA pairs: (tw, th, tn) = ONE CTA's 128-pixel half tile and the dimension along which the two halves sit side by side,
+// minimising the number of pair tiles (ties -> wider rows, then stacking along h).  Returns the pair-tile count.
+int64_t choose_pair_tile(int gw, int gh, int n, int one_sample, int max_w, int* tw, int* th, int* tn, int* pair_dim) {
+  int64_t best = -1;
+  for (int w = 128 < max_w ? 128 : max_w; w >= 1; w >>= 1) {
+    for (int h = 1; w * h <= 128; h <<= 1) {
+      const int nn = 128 / (w * h);
+      if (one_sample && nn != 1) continue;
+      static const int kOrder[3] = {1, 0, 2};  // prefer stacking along h, then w, then n
+      for (int oi = 0; oi < 3; ++oi) {
+        const int pd = kOrder[oi];
+        if (pd == 2 && one_sample) continue;
+        if (pd == 0 && 2 * w > max_w) continue;
+        const int pw = pd == 0 ? 2 * w : w, phh = pd == 1 ? 2 * h : h, pn = pd == 2 ? 2 * nn : nn;
+        const int64_t tiles = (int64_t)((gw + pw - 1) / pw) * ((gh + phh - 1) / phh) * ((n + pn - 1) / pn);
+        if (best < 0 || tiles < best) { best = tiles; *tw = w; *th = h; *tn = nn; *pair_dim = pd; }
+      }
+    }
+  }
+  return best;
+}
+
+// environment switches (experiments), read ONCE per process - never on the launch path
+struct ConvEnv {
+  int swap = -1;   // VCN_CONV_SWAP: 0 never, 2 also for the transposed conv, unset = policy
+  int stage = -1;  // VCN_CONV_STAGE: 0 = no TMA-store epilogue
+  int pair = -1;   // VCN_CONV_PAIR: 0 never, 2 = every tile of >= 64 out channels, unset = policy (n_tile == 256)
+  int prof = 0;    // VCN_CONV_PROFILE (only meaningful in -DVCN_CONV_PROF=1 builds)
+  ConvEnv() {
+    if (const char* e = getenv("VCN_CONV_SWAP")) swap = atoi(e);
+    if (const char* e = getenv("VCN_CONV_STAGE")) stage = atoi(e);
+    if (const char* e = getenv("VCN_CONV_PAIR")) pair = atoi(e);
+    if (const char* e = getenv("VCN_CONV_PROFILE")) prof = atoi(e);
+  }
+};
+const ConvEnv& conv_env() {
+  static const ConvEnv env;
+  return env;
 }
 
 }  // namespace
@@ -613,26 +712,45 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   // of this kernel is the ~50 B/clk an SM ingests from L2, not the tensor pipe.
   // Not for the transposed conv: its phase tiles carry 1..4 taps only (9 k-blocks per tile on average at 256 channels), the
   // tile is epilogue-bound either way and the swapped epilogue costs 1.7x per pixel (measured: 0.168 ms vs 0.131 ms).
+  const ConvEnv& env = conv_env();
   a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256 && d->kind != VCN_CONV_TCONV2;
-  if (const char* e = getenv("VCN_CONV_SWAP")) {  // 0: never, 2: also for the transposed conv (experiments)
+  if (env.swap >= 0) {  // 0: never, 2: also for the transposed conv (experiments)
     const bool base = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256;
-    a.swap = atoi(e) == 2 ? base : (a.swap && atoi(e) != 0);
+    a.swap = env.swap == 2 ? base : (a.swap && env.swap != 0);
   }
-  choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample || a.swap, a.swap ? 256 : 128, 256 / a.a_mul,
-              (a.swap && a.grid_w > 16) ? 32 : 1 /* swapped epilogue: 32 consecutive x per TMEM chunk */, &a.tw, &a.th, &a.tn);
-  for (a.log_tw = 0; (1 << a.log_tw) < a.tw; ++a.log_tw) {}
-  for (a.log_th = 0; (1 << a.log_th) < a.th; ++a.log_th) {}
-  a.tiles_w = (a.grid_w + a.tw - 1) / a.tw;
-  a.tiles_h = (a.grid_h + a.th - 1) / a.th;
-  const int tiles_n = (d->n + a.tn - 1) / a.tn;
-  a.tiles_m = a.tiles_w * a.tiles_h * tiles_n;
   // two accumulator stages of n_tile fp32 columns each must fit the 512 TMEM columns
   a.n_tile = (d->cout + 15) / 16 * 16;
   if (a.n_tile > 256) a.n_tile = 256;
   if (a.swap) a.n_tile = 128;  // out channels per tile = the 128 UMMA rows (TMA zero-fills rows past cout)
+  // CTA pairs (cta_group::2): worth it when the weight tile is wide - with N = 256 each SM stages 16 + 16 KB per k-block
+  // instead of 16 + 32 - and when there are enough pair tiles to fill the machine
+  {
+    int ptw = 0, pth = 0, ptn = 0, pd = 0;
+    const int64_t ptiles = choose_pair_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample, 256 / a.a_mul, &ptw, &pth, &ptn, &pd) *
+                           a.num_phases * ((d->cout + a.n_tile - 1) / a.n_tile);
+    // measured (B200, L2 flushed; profiles/README.md): FPROP / DGRAD 256->256 and 512->512 gain 5-8 % as pairs; the transposed
+    // conv's short-K phase tiles are epilogue-bound and lose (512->256: 0.52 vs 0.56 of peak), so it stays on single CTAs
+    bool want = !a.swap && a.n_tile == 256 && d->kind != VCN_CONV_TCONV2;
+    if (env.pair == 0) want = false;
+    if (env.pair == 2) want = !a.swap && a.n_tile >= 64;
+    if (want && a.n_tile % 32 == 0 && ptiles >= sm_count() / 2) {
+      a.pair = 1; a.pair_dim = pd; a.tw = ptw; a.th = pth; a.tn = ptn;
+    }
+  }
+  if (!a.pair)
+    choose_tile(a.grid_w, a.grid_h, d->n, a.w_per_sample || a.swap, a.swap ? 256 : 128, 256 / a.a_mul,
+                (a.swap && a.grid_w > 16) ? 32 : 1 /* swapped epilogue: 32 consecutive x per TMEM chunk */, &a.tw, &a.th, &a.tn);
+  for (a.log_tw = 0; (1 << a.log_tw) < a.tw; ++a.log_tw) {}
+  for (a.log_th = 0; (1 << a.log_th) < a.th; ++a.log_th) {}
+  {
+    const int pw = a.tw << (a.pair && a.pair_dim == 0), phh = a.th << (a.pair && a.pair_dim == 1), pn = a.tn << (a.pair && a.pair_dim == 2);
+    a.tiles_w = (a.grid_w + pw - 1) / pw;
+    a.tiles_h = (a.grid_h + phh - 1) / phh;
+    a.tiles_m = a.tiles_w * a.tiles_h * ((d->n + pn - 1) / pn);
+  }
   // few M tiles (tiny resolutions): narrower out-channel tiles spread the weight stream over more SMs - one CTA
   // ingests only ~75 GB/s through TMA, so a 4.7 MB weight tensor on 2 CTAs is latency/bandwidth bound
-  while (!a.swap && a.n_tile > 32 && a.n_tile % 32 == 0 &&
+  while (!a.swap && !a.pair && a.n_tile > 32 && a.n_tile % 32 == 0 &&
          (int64_t)a.tiles_m * a.num_phases * ((d->cout + a.n_tile - 1) / a.n_tile) < sm_count() / 2)
     a.n_tile /= 2;
   const int tiles_co = (d->cout + a.n_tile - 1) / a.n_tile;
@@ -643,7 +761,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   a.tmem_cols = a.swap ? 512 : pow2_ceil(2 * a.n_tile);
   if (a.tmem_cols < 32) a.tmem_cols = 32;
   a.pix_bytes = (a.swap ? 2u : 1u) * kABytes;
-  a.w_bytes = (uint32_t)a.n_tile * kBlockK * 2;
+  a.w_bytes = (uint32_t)(a.pair ? a.n_tile / 2 : a.n_tile) * kBlockK * 2;  // pair: each CTA stages half of the weight tile
   const size_t stage_bytes = (size_t)a.pix_bytes + a.w_bytes;
   const size_t tail_bytes = (2 * (size_t)8 + 4) * 8 + 16 + 4 * (size_t)a.n_tile * sizeof(float) + 64;
 
@@ -654,7 +772,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   a.vec_store = d->ys[1] == 1 && aligned16(y) && d->ys[0] % vq == 0 && d->ys[2] % vq == 0 && d->ys[3] % vq == 0;
   // staged TMA-store epilogue: 16-bit channels-fastest output whose 64-channel blocks fill whole staging rows
   a.stage_out = a.vec_store && oe == 2 && (a.swap || a.n_tile % 64 == 0);
-  if (const char* e = getenv("VCN_CONV_STAGE")) a.stage_out = a.stage_out && atoi(e) != 0;
+  if (env.stage >= 0) a.stage_out = a.stage_out && env.stage != 0;
   if (a.stage_out) {
     a.out_blocks = a.n_tile / 64;
     a.stage_blk_bytes = (a.swap ? 256u : 128u) * 128u;
@@ -672,10 +790,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
     VCN_REQUIRE(a.act == 0 || (a.act >= VCN_ACT_LINEAR && a.act <= VCN_ACT_SWISH), "conv_igemm: bad epilogue act %d", a.act);
   }
 
-  if (const char* e = getenv("VCN_CONV_PROFILE")) a.prof = atoi(e) != 0;
-  if (const char* e = getenv("VCN_CONV_DEBUG_NOSTORE")) {  // profiling aid: the epilogue drains TMEM but stores nothing
-    if (atoi(e) != 0) a.y_dtype = -1;
-  }
+  a.prof = kProf && env.prof != 0;
   CUtensorMap tmap_a, tmap_b;
   {
     const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
@@ -693,7 +808,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
     const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->cout, taps, (uint64_t)(a.w_per_sample ? d->n : 1)};
     const uint64_t strides[3] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->cout * d->cin_pad * 2,
                                  taps * d->cout * d->cin_pad * 2};
-    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)a.n_tile, 1u, 1u};
+    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)(a.pair ? a.n_tile / 2 : a.n_tile), 1u, 1u};
     const int rc = make_tensor_map(&tmap_b, VCN_BF16, 4, wt, dims, strides, box, nullptr, 1);
     if (rc) return rc;
   }
@@ -711,10 +826,27 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
       if (rc) return rc;
     }
   }
-  VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int grid = sm_count();
-  if (grid > a.tiles_total) grid = a.tiles_total;
-  conv_igemm_kernel<<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, om, a);
+  if (a.pair) VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  else VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (!a.pair) {
+    int grid = sm_count();
+    if (grid > a.tiles_total) grid = a.tiles_total;
+    conv_igemm_kernel<false><<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, om, a);
+  } else {
+    int pairs = sm_count() / 2;
+    if (pairs > a.tiles_total) pairs = a.tiles_total;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(2 * pairs), 1, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    VCN_CUDA(cudaLaunchKernelEx(&cfg, conv_igemm_kernel<true>, tmap_a, tmap_b, om, a));
+  }
   VCN_LAUNCH_CHECK("conv_igemm_kernel");
   return VCN_OK;
 }
@@ -722,6 +854,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
 extern "C" int vcn_conv_profile_counters(uint64_t out[8], int reset) {
   using namespace vcn;
   VCN_REQUIRE(out != nullptr, "conv_profile_counters: out must not be NULL");
+#if VCN_CONV_PROF
   unsigned long long h[8];
   VCN_CUDA(cudaMemcpyFromSymbol(h, g_conv_prof, sizeof(h)));
   for (int i = 0; i < 8; ++i) out[i] = h[i];
@@ -730,4 +863,10 @@ extern "C" int vcn_conv_profile_counters(uint64_t out[8], int reset) {
     VCN_CUDA(cudaMemcpyToSymbol(g_conv_prof, h, sizeof(h)));
   }
   return VCN_OK;
+#else
+  (void)reset;
+  for (int i = 0; i < 8; ++i) out[i] = 0;
+  set_error("conv_profile_counters: this build has no profiling counters (compile csrc/modconv.cu with -DVCN_CONV_PROF=1)");
+  return VCN_ERR_UNSUPPORTED;
+#endif
 }
