@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define VCN_ABI_VERSION 1
+#define VCN_ABI_VERSION 2
 
 typedef enum {
   VCN_OK = 0,
@@ -131,12 +131,21 @@ typedef struct {
   int y_dtype;              /* VCN_F32 / VCN_BF16 / VCN_F16 */
   int64_t ys[4];            /* element strides of y for (n, c, h, w): NCHW, channels_last or padded pitch */
   int w_per_sample;         /* wt has a leading sample dimension [n][tap][cout][cin_pad] (per-sample modulated weights) */
+  int tf32;                 /* 0: xhat / wt are bf16 (tcgen05 kind::f16); 1: both are fp32 and the GEMM runs kind::tf32 - the
+                               fp32-fidelity mode: 10-bit-mantissa operands like the reference's cuDNN TF32 convolutions
+                               (torch default), fp32 accumulation, half the bf16 tensor rate */
 } vcn_conv_desc;
 
 int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat,
                       int n, int cin, int cin_pad, int h, int w, void* stream);
 int vcn_pack_weights(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io,
                      void* wt, int cols_pad, float* wsq, void* stream);
+/* _ex variants: the GEMM operand dtype is explicit - VCN_BF16 (what the plain entry points produce) or VCN_F32 (operands
+ * of the kind::tf32 GEMM, desc.tf32 = 1). */
+int vcn_modulate_pack_ex(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat, int xhat_dtype,
+                         int n, int cin, int cin_pad, int h, int w, void* stream);
+int vcn_pack_weights_ex(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io, void* wt, int wt_dtype,
+                        int cols_pad, float* wsq, void* stream);
 int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int cin, int cout, void* stream);
 /* Per-sample modulated (and, with dcoef, demodulated) weights of the reference's fused branch (networks.py:54-60):
  * wn bf16 [n][kh*kw][cout][cin_pad] = W[co,ci,tap] * styles[n,ci] * dcoef[n,co]; consumed with desc.w_per_sample = 1. */
@@ -158,6 +167,9 @@ int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_des
 int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
                          const vcn_upfirdn2d_epilogue* epi, void* dy0, float* gsum, float* db,
                          int n, int c, int c_pad, int h, int w, void* stream);
+int vcn_modconv_bwd_pack_ex(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
+                            const vcn_upfirdn2d_epilogue* epi, void* dy0, int dy0_dtype, float* gsum, float* db,
+                            int n, int c, int c_pad, int h, int w, void* stream);
 int vcn_modconv_bwd_finish(float* dxhat, const int64_t ds[4], const void* x, int x_dtype, const int64_t xs[4],
                            const float* styles, float* dsum, int n, int c, int h, int w, void* stream);
 /* Resident 16-bit channels-last pipeline: dxhat is a dense bf16 [n,h,w,c_pad] buffer (the DGRAD / SCONV2 GEMM output),

@@ -35,9 +35,25 @@ def _keys(g):
     return sorted({k.rsplit(".", 1)[0] for k in g.keys if k.startswith("mod.")})
 
 
-def test_golden_modconv(golden):
-    """The 36 reference-recorded cases (up 1/2, k 3/1, demod on/off, noise none/const/random, fused flag both)."""
+TOL_TF32_FWD, TOL_TF32_GRAD = 3e-3, 5e-3  # fp32 I/O on TF32 tensor cores
+
+
+@pytest.fixture(params=["tf32", "bf16"])
+def operand_mode(request):
+    """fp32 activations through the API: 'tf32' = fp32 operands on tcgen05 kind::tf32 (the default, the reference's own GPU
+    arithmetic), 'bf16' = operands rounded to bf16 (round 1's only mode).  Yields (mode, forward gate, gradient gate)."""
     M = _M()
+    old = M.fp32_operands
+    M.fp32_operands = request.param
+    yield (request.param,) + ((TOL_TF32_FWD, TOL_TF32_GRAD) if request.param == "tf32" else (TOL_FWD, TOL_GRAD))
+    M.fp32_operands = old
+
+
+def test_golden_modconv(golden, operand_mode):
+    """The 36 reference-recorded cases (up 1/2, k 3/1, demod on/off, noise none/const/random, fused flag both), in both
+    operand precisions: TF32 operands fwd <= 3e-3 / grads <= 5e-3, bf16 operands 1e-2 / 2e-2."""
+    M = _M()
+    mode, TOL_FWD, TOL_GRAD = operand_mode
     g = golden("conv_modconv")
     f4 = g.t("f4", device="cuda")
     worst = {}
@@ -52,7 +68,7 @@ def test_golden_modconv(golden):
         e = (_rel(y, g.t(key + ".y")), _rel(dx, g.t(key + ".dx")), _rel(ds, g.t(key + ".ds")))
         worst[key] = e
         assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, (key, e)
-    print("worst fwd/dx/ds:", [max(v[i] for v in worst.values()) for i in range(3)])
+    print("[%s operands] worst fwd/dx/ds:" % mode, [max(v[i] for v in worst.values()) for i in range(3)])
 
 
 CASES = [

@@ -206,3 +206,50 @@ def test_channels_last_fused_epilogue(dtype, act, alpha, gain, clamp, sep):
     y = U.launch(xc, f.cuda(), 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi)
     assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
     assert _rel(y, y_ref) <= 2 * torch.finfo(dtype).eps
+
+
+SYM6 = [0.015404109327027373, 0.0034907120842174702, -0.11799011114819057, -0.048311742585633, 0.4910559419267466,
+        0.787641141030194, 0.3379294217276218, -0.07263752278646252, -0.021060292512300564, 0.04472490177066578,
+        0.0017677118642428036, -0.007800708325034148]  # the 12-tap wavelet AugmentPipe resamples with (augment.py:27)
+
+
+@pytest.mark.parametrize("taps", [5, 8, 12, 13, 24, 31])
+@pytest.mark.parametrize("up,down", [(1, 1), (2, 1), (1, 2)])
+@pytest.mark.parametrize("flip", [False, True])
+def test_separable_long_filter_1d_kernels(taps, up, down, flip):
+    """1-D filters of 5..32 taps (the reference's separable specialisations, upfirdn2d.cu:219-246,264-338)
+    run two `upfirdn1d` passes (x then y).  Exact-FMA fp32 kernels: rel-Linf <= 1e-5 vs the oracle; odd sizes, asymmetric
+    and negative padding, both factor directions, forward and the swapped-factor backward."""
+    U = _ops()
+    g = torch.Generator().manual_seed(taps * 7 + up * 3 + down)
+    f = torch.tensor(SYM6) if taps == 12 else torch.randn(taps, generator=g)
+    x = torch.randn(2, 3, 37, 141, generator=g, requires_grad=True)
+    pad = [taps // 2 + 1, taps // 2 - 2, taps // 2 - 1, taps // 2] if taps != 13 else [-1, 9, 7, -2]
+    y_ref = R.upfirdn2d(x, f, up=up, down=down, padding=pad, flip_filter=flip, gain=float(up * up))
+    dy = torch.randn(y_ref.shape, generator=g)
+    (dx_ref,) = torch.autograd.grad(y_ref, [x], dy)
+    xc = x.detach().cuda().requires_grad_(True)
+    import viscoin_next_b200 as V
+    before = V._lib.load().vcn_launch_count()
+    y = U.upfirdn2d(xc, f.cuda(), up=up, down=down, padding=pad, flip_filter=flip, gain=float(up * up), impl="cuda")
+    assert V._lib.load().vcn_launch_count() - before == 2  # one launch per 1-D pass
+    (dx,) = torch.autograd.grad(y, [xc], dy.cuda())
+    assert _rel(y, y_ref) <= 1e-5 and _rel(dx, dx_ref) <= 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_separable_long_filter_16bit_and_full_size(dtype):
+    """AugmentPipe-sized call (images at twice the 256^2 resolution, 12-tap sym6, up then down by 2): the 16-bit kernels
+    against the fp32 oracle at the storage tolerance, and the up-then-down round trip at full size against the same
+    composition through the generic gather kernel's arithmetic (linearity: f(2x) = 2 f(x), a size-independent property)."""
+    U = _ops()
+    g = torch.Generator().manual_seed(3)
+    f = torch.tensor(SYM6)
+    x = torch.randn(2, 3, 64, 80, generator=g)
+    y_ref = R.upfirdn2d(x, f, up=2, padding=[6, 5, 6, 5], gain=4)
+    y = U.upfirdn2d(x.cuda().to(dtype), f.cuda(), up=2, padding=[6, 5, 6, 5], gain=4, impl="cuda")
+    assert y.dtype == dtype and _rel(y.float(), y_ref) <= 2e-2
+    big = torch.randn(8, 3, 512, 512, device="cuda", generator=torch.Generator(device="cuda").manual_seed(4))
+    a = U.upfirdn2d(U.upfirdn2d(big, f.cuda(), up=2, padding=[6, 5, 6, 5], gain=4), f.cuda(), down=2, padding=[5, 5, 5, 5])
+    b = U.upfirdn2d(U.upfirdn2d(2 * big, f.cuda(), up=2, padding=[6, 5, 6, 5], gain=4), f.cuda(), down=2, padding=[5, 5, 5, 5])
+    assert a.shape == big.shape and torch.allclose(2 * a, b, rtol=1e-5, atol=1e-6)

@@ -82,7 +82,17 @@ def collect(device, peaks, time_fn, iters=10, include_cudnn=True, n=8):
     hbm("upfirdn2d_cl_sep_kernel<bf16> pattern A [%d,128,257,257] bf16 NHWC" % n,
         lambda: V.upfirdn2d.upfirdn2d(xcl, f4, padding=[1, 1, 1, 1], gain=4), (xcl.numel() + n * 128 * 256 * 256) * 2,
         key="upfirdn2d_cl_sep_kernel")
-    del xa, xb, xcl, x
+    # separable long filter (AugmentPipe's 12-tap sym6 at twice the image resolution): one 1-D pass each
+    sym6 = torch.tensor([0.0154, 0.0035, -0.118, -0.0483, 0.4911, 0.7876, 0.3379, -0.0726, -0.0211, 0.0447, 0.0018, -0.0078], device=device)
+    xs_ = rn(n, 3, 1024, 1024)
+    hbm("upfirdn1d_x_kernel<float,12 taps> [%d,3,1024,1024] fp32 NCHW (one separable pass along x)" % n,
+        lambda: V.upfirdn2d.launch(xs_, sym6.unsqueeze(0), 1, 1, 1, 1, 6, 5, 0, 0, False, 1.0), 2 * xs_.numel() * 4)
+    hbm("upfirdn1d_y_kernel<float,12 taps> [%d,3,1024,1024] fp32 NCHW (one separable pass along y)" % n,
+        lambda: V.upfirdn2d.launch(xs_, sym6.unsqueeze(1), 1, 1, 1, 1, 0, 0, 6, 5, False, 1.0), 2 * xs_.numel() * 4)
+    xh_ = xs_[:, :, :, :512].contiguous()
+    hbm("upfirdn1d_x_kernel<float,12 taps, up 2> [%d,3,1024,512]->[.,.,1024,1024] fp32 NCHW" % n,
+        lambda: V.upfirdn2d.launch(xh_, sym6.unsqueeze(0), 2, 1, 1, 1, 6, 5, 0, 0, False, 2.0), (xh_.numel() + xs_.numel()) * 4)
+    del xa, xb, xcl, x, xs_, xh_
 
     # ---- channels-last passes around the GEMMs (bf16, the train step's N = 2*batch) ----------------------------------
     n2 = 2 * n

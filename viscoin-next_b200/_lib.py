@@ -33,7 +33,7 @@ class ConvDesc(_c.Structure):
 
     _fields_ = [
         ("kind", _i), ("n", _i), ("h", _i), ("w", _i), ("cin_pad", _i), ("cout", _i), ("kh", _i), ("kw", _i),
-        ("out_h", _i), ("out_w", _i), ("y_dtype", _i), ("ys", _i64 * 4), ("w_per_sample", _i),
+        ("out_h", _i), ("out_w", _i), ("y_dtype", _i), ("ys", _i64 * 4), ("w_per_sample", _i), ("tf32", _i),
     ]
 
 
@@ -52,6 +52,10 @@ SIGNATURES = {
                            _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _c.POINTER(UpfirdnEpilogue), _vp]),
     "vcn_modulate_pack": (_i, [_vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_pack_weights": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
+    "vcn_modulate_pack_ex": (_i, [_vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "vcn_pack_weights_ex": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _i, _i, _vp, _vp]),
+    "vcn_modconv_bwd_pack_ex": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _c.POINTER(UpfirdnEpilogue),
+                                     _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_demod_coefs": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "vcn_pack_weights_mod": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "vcn_conv_igemm": (_i, [_vp, _vp, _vp, _c.POINTER(ConvDesc), _c.POINTER(UpfirdnEpilogue), _vp]),

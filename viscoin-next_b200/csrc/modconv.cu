@@ -59,6 +59,8 @@ struct IgemmArgs {
   int tw, th, tn, tiles_w, tiles_h, tiles_m, tiles_total;
   int n_tile, kblocks_c, stages, tmem_cols;
   int swap;            // 1: operands swapped - UMMA M = 128 out-channels (weights), N = 256 pixels (see header)
+  int tf32;            // 1: fp32 operands, tcgen05 kind::tf32 (a k-block = 32 channels = one 128-byte swizzle span)
+  int kbk;             // channels per k-block: 64 (bf16) or 32 (tf32)
   int pair;            // 1: 2-CTA clusters, cta_group::2 (tw/th/tn describe ONE CTA's 128-pixel half of the pair tile)
   int pair_dim;        // the pair tile = two half tiles stacked along w (0), h (1) or n (2)
   int log_tw, log_th;  // swap: tile extents are powers of two
@@ -329,15 +331,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             unsigned char* sa = smem + (size_t)s * stage_bytes;
             if constexpr (!PAIR) {
               mbar_expect_tx(full_bar + s, stage_bytes);
-              tma_load_4d(sa, &tmap_a, full_bar + s, cb * kBlockK, ax, ay, tc.n0);
-              tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * kBlockK, tc.co0, tap.wtap, nw);
+              tma_load_4d(sa, &tmap_a, full_bar + s, cb * a.kbk, ax, ay, tc.n0);
+              tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * a.kbk, tc.co0, tap.wtap, nw);
             } else {
               // both CTAs load into their OWN shared memory and complete the bytes on the LEADER's barrier, which the
               // leader arms for the whole pair (a complete_tx that overtakes the expect_tx only drives the count negative)
               if (rank == 0) mbar_expect_tx(full_bar + s, 2u * stage_bytes);
               const uint32_t lead_bar = mapa_u32(full_bar + s, 0);
-              tma_load_4d_2cta(sa, &tmap_a, lead_bar, cb * kBlockK, ax, ay, tc.n0);
-              tma_load_4d_2cta(sa + a.pix_bytes, &tmap_b, lead_bar, cb * kBlockK, tc.co0 + co_half, tap.wtap, nw);
+              tma_load_4d_2cta(sa, &tmap_a, lead_bar, cb * a.kbk, ax, ay, tc.n0);
+              tma_load_4d_2cta(sa + a.pix_bytes, &tmap_b, lead_bar, cb * a.kbk, tc.co0 + co_half, tap.wtap, nw);
             }
             if (++s == a.stages) { s = 0; ph ^= 1u; }
           }
@@ -351,7 +353,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // ===== MMA issuer =====
     if (lane == 0 && rank == 0) {  // pair mode: the leader issues for both CTAs
       const int acc_cols = a.swap ? 256 : a.n_tile;
-      const uint32_t idesc = umma_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, acc_cols);
+      const uint32_t idesc = a.tf32 ? umma_idesc_tf32_f32(PAIR ? 2 * kBlockM : kBlockM, acc_cols)
+                                    : umma_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, acc_cols);
       int s = 0;
       uint32_t ph = 0;
       int tile_iter = 0;
@@ -377,8 +380,15 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int k = 0; k < kBlockK / kUmmaK; ++k) {
             // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
-            if constexpr (PAIR) umma_bf16_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
-            else umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            // one MMA = 32 bytes of K per row: 16 bf16 or 8 tf32 channels
+            const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
+            if constexpr (PAIR) {
+              if (a.tf32) umma_tf32_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+              else umma_bf16_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+            } else {
+              if (a.tf32) umma_tf32_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+              else umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+            }
           }
           if constexpr (PAIR) umma_commit_2cta(empty_bar + s, 3);  // frees stage s in BOTH CTAs
           else umma_commit(empty_bar + s);
@@ -705,6 +715,10 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   VCN_REQUIRE(aligned16(xhat) && aligned16(wt), "conv_igemm: xhat and wt must be 16-byte aligned");
 
   a.a_mul = d->kind == VCN_CONV_SCONV2 ? 2 : 1;
+  a.tf32 = d->tf32 ? 1 : 0;
+  a.kbk = a.tf32 ? 32 : kBlockK;  // either way a k-block is one 128-byte swizzle span per row
+  const int op_dtype = a.tf32 ? VCN_F32 : VCN_BF16;
+  const uint64_t op_size = a.tf32 ? 4 : 2;
   a.w_per_sample = d->w_per_sample ? 1 : 0;
   a.n = d->n; a.cout = d->cout; a.out_h = d->out_h; a.out_w = d->out_w;
   // Operand swap (UMMA M = out channels, N = 256 pixels) for 65..128 out channels and a channels-fastest output: a
@@ -757,7 +771,7 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   const int64_t total = (int64_t)a.tiles_m * a.num_phases * tiles_co;
   VCN_REQUIRE(total <= 0x7fffffffLL, "conv_igemm: too many tiles");
   a.tiles_total = (int)total;
-  a.kblocks_c = (d->cin_pad + kBlockK - 1) / kBlockK;
+  a.kblocks_c = (d->cin_pad + a.kbk - 1) / a.kbk;
   a.tmem_cols = a.swap ? 512 : pow2_ceil(2 * a.n_tile);
   if (a.tmem_cols < 32) a.tmem_cols = 32;
   a.pix_bytes = (a.swap ? 2u : 1u) * kABytes;
@@ -794,22 +808,22 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   CUtensorMap tmap_a, tmap_b;
   {
     const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->w, (uint64_t)d->h, (uint64_t)d->n};
-    const uint64_t strides[3] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->w * d->cin_pad * 2,
-                                 (uint64_t)d->h * d->w * d->cin_pad * 2};
+    const uint64_t strides[3] = {(uint64_t)d->cin_pad * op_size, (uint64_t)d->w * d->cin_pad * op_size,
+                                 (uint64_t)d->h * d->w * d->cin_pad * op_size};
     // stride-2 gather: traversal strides (1,2,2,1); the box spans 2*TW x 2*TH input pixels and delivers TW x TH
     const uint32_t m = (uint32_t)a.a_mul;
-    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)a.tw * m, (uint32_t)a.th * m, (uint32_t)a.tn};
+    const uint32_t box[4] = {(uint32_t)a.kbk, (uint32_t)a.tw * m, (uint32_t)a.th * m, (uint32_t)a.tn};
     const uint32_t estr[4] = {1u, m, m, 1u};
-    const int rc = make_tensor_map(&tmap_a, VCN_BF16, 4, xhat, dims, strides, box, estr, 1);
+    const int rc = make_tensor_map(&tmap_a, op_dtype, 4, xhat, dims, strides, box, estr, 1);
     if (rc) return rc;
   }
   {
     const uint64_t taps = (uint64_t)(kh * kw);
     const uint64_t dims[4] = {(uint64_t)d->cin_pad, (uint64_t)d->cout, taps, (uint64_t)(a.w_per_sample ? d->n : 1)};
-    const uint64_t strides[3] = {(uint64_t)d->cin_pad * 2, (uint64_t)d->cout * d->cin_pad * 2,
-                                 taps * d->cout * d->cin_pad * 2};
-    const uint32_t box[4] = {(uint32_t)kBlockK, (uint32_t)(a.pair ? a.n_tile / 2 : a.n_tile), 1u, 1u};
-    const int rc = make_tensor_map(&tmap_b, VCN_BF16, 4, wt, dims, strides, box, nullptr, 1);
+    const uint64_t strides[3] = {(uint64_t)d->cin_pad * op_size, (uint64_t)d->cout * d->cin_pad * op_size,
+                                 taps * d->cout * d->cin_pad * op_size};
+    const uint32_t box[4] = {(uint32_t)a.kbk, (uint32_t)(a.pair ? a.n_tile / 2 : a.n_tile), 1u, 1u};
+    const int rc = make_tensor_map(&tmap_b, op_dtype, 4, wt, dims, strides, box, nullptr, 1);
     if (rc) return rc;
   }
   OutMaps om;

@@ -12,10 +12,35 @@
 namespace vcn {
 namespace {
 
-template <typename T>
+// GEMM operand element: bf16 (tcgen05 kind::f16) or fp32 (kind::tf32: the tensor core reads the upper 19 bits)
+template <typename TO> __device__ __forceinline__ TO to_op(float v);
+template <> __device__ __forceinline__ __nv_bfloat16 to_op<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ float to_op<float>(float v) { return v; }
+
+template <typename TO> __device__ __forceinline__ void store_pair(TO* p, float a, float b);
+template <> __device__ __forceinline__ void store_pair<__nv_bfloat16>(__nv_bfloat16* p, float a, float b) {
+  *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b);
+}
+template <> __device__ __forceinline__ void store_pair<float>(float* p, float a, float b) {
+  *reinterpret_cast<float2*>(p) = make_float2(a, b);
+}
+
+template <typename TO> __device__ __forceinline__ void store8(TO* p, const float (&v)[8]);
+template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  Vec16<__nv_bfloat16> o;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) o.v[k] = __float2bfloat16_rn(v[k]);
+  *reinterpret_cast<Vec16<__nv_bfloat16>*>(p) = o;
+}
+template <> __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+template <typename T, typename TO>
 __global__ void __launch_bounds__(256) modulate_pack_kernel(const T* __restrict__ x, int64_t xs_n, int64_t xs_c,
                                                             int64_t xs_h, int64_t xs_w, const float* __restrict__ styles,
-                                                            __nv_bfloat16* __restrict__ xhat, int cin, int cin_pad, int h,
+                                                            TO* __restrict__ xhat, int cin, int cin_pad, int h,
                                                             int w) {
   // grid: (ceil(h*w/32), ceil(cin_pad/64), n); tile = 64 channels x 32 pixels
   __shared__ float tile[64][33];
@@ -42,18 +67,15 @@ __global__ void __launch_bounds__(256) modulate_pack_kernel(const T* __restrict_
     const int pp = warp * 4 + i;
     const int gp = p0 + pp;
     const int c = c0 + 2 * lane;
-    if (gp < hw && c < cin_pad) {
-      const __nv_bfloat162 v = __floats2bfloat162_rn(tile[2 * lane][pp], tile[2 * lane + 1][pp]);
-      *reinterpret_cast<__nv_bfloat162*>(xhat + ((int64_t)n * hw + gp) * cin_pad + c) = v;
-    }
+    if (gp < hw && c < cin_pad) store_pair<TO>(xhat + ((int64_t)n * hw + gp) * cin_pad + c, tile[2 * lane][pp], tile[2 * lane + 1][pp]);
   }
 }
 
 // channels-fastest input (xs_c == 1): elementwise pass, 8 channels (16 bytes of bf16 output) per thread
-template <typename T>
+template <typename T, typename TO>
 __global__ void __launch_bounds__(256) modulate_pack_cl_kernel(const T* __restrict__ x, int64_t xs_n, int64_t xs_h,
                                                                int64_t xs_w, const float* __restrict__ styles,
-                                                               __nv_bfloat16* __restrict__ xhat, int n_img, int cin,
+                                                               TO* __restrict__ xhat, int n_img, int cin,
                                                                int cin_pad, int h, int w, int vec_in) {
   const int groups = cin_pad / 8;
   const int64_t total = (int64_t)n_img * h * w * groups;
@@ -87,10 +109,7 @@ __global__ void __launch_bounds__(256) modulate_pack_cl_kernel(const T* __restri
 #pragma unroll
       for (int k = 0; k < 8; ++k) v[k] *= (c + k < cin) ? sp[k] : 0.f;
     }
-    Vec16<__nv_bfloat16> o;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) o.v[k] = __float2bfloat16_rn(v[k]);
-    *reinterpret_cast<Vec16<__nv_bfloat16>*>(xhat + (((int64_t)n * h + py) * w + px) * cin_pad + c) = o;
+    store8<TO>(xhat + (((int64_t)n * h + py) * w + px) * cin_pad + c, v);
   }
 }
 
@@ -129,9 +148,9 @@ __global__ void __launch_bounds__(256) modulate_pack_cl_rows_kernel(const T* __r
   }
 }
 
-template <typename T>
+template <typename T, typename TO>
 __global__ void __launch_bounds__(256) pack_weights_kernel(const T* __restrict__ w, int cout, int cin, int taps,
-                                                           int transpose_io, __nv_bfloat16* __restrict__ wt, int rows,
+                                                           int transpose_io, TO* __restrict__ wt, int rows,
                                                            int cols, int cols_pad) {
   // one thread per (tap, row, col_pad) element of wt
   const int64_t total = (int64_t)taps * rows * cols_pad;
@@ -145,7 +164,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const T* __restrict__
       const int co = transpose_io ? col : row, ci = transpose_io ? row : col;
       v = to_acc<T>(w[((int64_t)co * cin + ci) * taps + tap]);
     }
-    wt[i] = __float2bfloat16_rn(v);
+    wt[i] = to_op<TO>(v);
   }
 }
 
@@ -185,7 +204,7 @@ struct BwdPackArgs {
   int64_t dys[4], ys[4];
   const float* noise; int64_t noise_stride_n;
   const float* bias; const float* dcoef;
-  __nv_bfloat16* dy0; float* gsum; float* db;
+  void* dy0; float* gsum; float* db;
   int n, c, c_pad, h, w;
   int act; float alpha, gain, clamp;
   int subs;  // 32-pixel sub-tiles per CTA
@@ -194,7 +213,7 @@ struct BwdPackArgs {
 // dz = bias_act'(dy; y), r = act^-1(y) - bias - noise (= y0 * d), gsum[n,c] += sum_p dz*r, db[c] += sum_p dz,
 // dy0 = dz * d[n,c] -> bf16 NHWC.  Tile = 64 channels x 128 pixels; lanes run along pixels for the NCHW reads and
 // along channels for the NHWC writes (transposed through shared memory).
-template <typename T>
+template <typename T, typename TO>
 __global__ void __launch_bounds__(256) modconv_bwd_pack_kernel(const BwdPackArgs a) {
   __shared__ float tile[64][33];
   const int n = blockIdx.z, c0 = blockIdx.y * 64;
@@ -243,8 +262,7 @@ __global__ void __launch_bounds__(256) modconv_bwd_pack_kernel(const BwdPackArgs
       const int gp = p0 + pp;
       const int c = c0 + 2 * lane;
       if (gp < hw && c < a.c_pad)
-        *reinterpret_cast<__nv_bfloat162*>(a.dy0 + ((int64_t)n * hw + gp) * a.c_pad + c) =
-            __floats2bfloat162_rn(tile[2 * lane][pp], tile[2 * lane + 1][pp]);
+        store_pair<TO>(static_cast<TO*>(a.dy0) + ((int64_t)n * hw + gp) * a.c_pad + c, tile[2 * lane][pp], tile[2 * lane + 1][pp]);
     }
     __syncthreads();
   }
@@ -360,11 +378,11 @@ __global__ void __launch_bounds__(128) pack_weights_mod_kernel(const T* __restri
   }
 }
 
-template <typename T>
+template <typename T, typename TO>
 int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* xhat, int n, int cin, int cin_pad, int h,
                  int w, cudaStream_t st) {
   const T* px = static_cast<const T*>(x);
-  __nv_bfloat16* po = static_cast<__nv_bfloat16*>(xhat);
+  TO* po = static_cast<TO*>(xhat);
   if (xs[1] == 1 && cin > 1) {
     const int64_t total = (int64_t)n * h * w * (cin_pad / 8);
     int64_t grid = (total + 255) / 256;
@@ -372,7 +390,7 @@ int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* 
     if (grid > cap) grid = cap;
     const int64_t vq = 16 / (int64_t)sizeof(T);
     const int vec_in = aligned16(x) && xs[0] % vq == 0 && xs[2] % vq == 0 && xs[3] % vq == 0;
-    if constexpr (sizeof(T) == 2) {
+    if constexpr (sizeof(T) == 2 && sizeof(TO) == 2) {
       const int groups = cin_pad / 8;
       const bool pow2 = (groups & (groups - 1)) == 0 && groups <= 256;
       if (vec_in && cin == cin_pad && pow2 && xs[2] == (int64_t)w * xs[3] && (int64_t)h * w <= 0x7fffffff) {
@@ -385,17 +403,17 @@ int run_modulate(const void* x, const int64_t xs[4], const float* styles, void* 
         return VCN_OK;
       }
     }
-    modulate_pack_cl_kernel<T><<<(unsigned)grid, 256, 0, st>>>(px, xs[0], xs[2], xs[3], styles, po, n, cin, cin_pad, h, w, vec_in);
+    modulate_pack_cl_kernel<T, TO><<<(unsigned)grid, 256, 0, st>>>(px, xs[0], xs[2], xs[3], styles, po, n, cin, cin_pad, h, w, vec_in);
     VCN_LAUNCH_CHECK("modulate_pack_cl_kernel");
     return VCN_OK;
   }
   dim3 grid((unsigned)((h * w + 31) / 32), (unsigned)((cin_pad + 63) / 64), (unsigned)n);
-  modulate_pack_kernel<T><<<grid, 256, 0, st>>>(px, xs[0], xs[1], xs[2], xs[3], styles, po, cin, cin_pad, h, w);
+  modulate_pack_kernel<T, TO><<<grid, 256, 0, st>>>(px, xs[0], xs[1], xs[2], xs[3], styles, po, cin, cin_pad, h, w);
   VCN_LAUNCH_CHECK("modulate_pack_kernel");
   return VCN_OK;
 }
 
-template <typename T>
+template <typename T, typename TO>
 int run_pack(const void* w, int cout, int cin, int taps, int transpose_io, void* wt, int cols_pad, float* wsq,
              cudaStream_t st) {
   const int rows = transpose_io ? cin : cout, cols = transpose_io ? cout : cin;
@@ -404,8 +422,8 @@ int run_pack(const void* w, int cout, int cin, int taps, int transpose_io, void*
     int64_t grid = (total + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
     if (grid > cap) grid = cap;
-    pack_weights_kernel<T><<<(unsigned)grid, 256, 0, st>>>(static_cast<const T*>(w), cout, cin, taps, transpose_io,
-                                                          static_cast<__nv_bfloat16*>(wt), rows, cols, cols_pad);
+    pack_weights_kernel<T, TO><<<(unsigned)grid, 256, 0, st>>>(static_cast<const T*>(w), cout, cin, taps, transpose_io,
+                                                              static_cast<TO*>(wt), rows, cols, cols_pad);
     VCN_LAUNCH_CHECK("pack_weights_kernel");
   }
   if (wsq) {
@@ -429,7 +447,13 @@ extern "C" {
 
 int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat, int n, int cin,
                       int cin_pad, int h, int w, void* stream) {
+  return vcn_modulate_pack_ex(x, x_dtype, xs, styles, xhat, VCN_BF16, n, cin, cin_pad, h, w, stream);
+}
+
+int vcn_modulate_pack_ex(const void* x, int x_dtype, const int64_t xs[4], const float* styles, void* xhat, int xhat_dtype,
+                         int n, int cin, int cin_pad, int h, int w, void* stream) {
   using namespace vcn;
+  VCN_REQUIRE(xhat_dtype == VCN_BF16 || xhat_dtype == VCN_F32, "modulate_pack: operand dtype must be bf16 or f32 (tf32), got %d", xhat_dtype);
   VCN_REQUIRE(n >= 0 && cin >= 1 && h >= 1 && w >= 1, "modulate_pack: bad shape [%d,%d,%d,%d]", n, cin, h, w);
   VCN_REQUIRE(cin_pad >= cin && cin_pad % 8 == 0, "modulate_pack: cin_pad (%d) must be a multiple of 8 and >= cin (%d)",
               cin_pad, cin);
@@ -437,10 +461,18 @@ int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const flo
   VCN_REQUIRE(x && xhat && xs, "modulate_pack: x, xs and xhat must not be NULL");
   VCN_REQUIRE((int64_t)n * h * w * cin_pad <= 0x7fffffffLL * 4, "modulate_pack: tensor too large");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  switch (x_dtype) {
-    case VCN_F32: return run_modulate<float>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
-    case VCN_F16: return run_modulate<__half>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
-    case VCN_BF16: return run_modulate<__nv_bfloat16>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+  if (xhat_dtype == VCN_F32) {
+    switch (x_dtype) {
+      case VCN_F32: return run_modulate<float, float>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+      case VCN_F16: return run_modulate<__half, float>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+      case VCN_BF16: return run_modulate<__nv_bfloat16, float>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+    }
+  } else {
+    switch (x_dtype) {
+      case VCN_F32: return run_modulate<float, __nv_bfloat16>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+      case VCN_F16: return run_modulate<__half, __nv_bfloat16>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+      case VCN_BF16: return run_modulate<__nv_bfloat16, __nv_bfloat16>(x, xs, styles, xhat, n, cin, cin_pad, h, w, st);
+    }
   }
   set_error("modulate_pack: unsupported dtype %d", x_dtype);
   return VCN_ERR_INVALID;
@@ -448,16 +480,30 @@ int vcn_modulate_pack(const void* x, int x_dtype, const int64_t xs[4], const flo
 
 int vcn_pack_weights(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io, void* wt,
                      int cols_pad, float* wsq, void* stream) {
+  return vcn_pack_weights_ex(w, w_dtype, cout, cin, kh, kw, transpose_io, wt, VCN_BF16, cols_pad, wsq, stream);
+}
+
+int vcn_pack_weights_ex(const void* w, int w_dtype, int cout, int cin, int kh, int kw, int transpose_io, void* wt, int wt_dtype,
+                        int cols_pad, float* wsq, void* stream) {
   using namespace vcn;
+  VCN_REQUIRE(wt_dtype == VCN_BF16 || wt_dtype == VCN_F32, "pack_weights: operand dtype must be bf16 or f32 (tf32), got %d", wt_dtype);
   VCN_REQUIRE(w != nullptr, "pack_weights: w must not be NULL");
   VCN_REQUIRE(cout >= 1 && cin >= 1 && kh >= 1 && kw >= 1, "pack_weights: bad shape [%d,%d,%d,%d]", cout, cin, kh, kw);
   const int cols = transpose_io ? cout : cin;
   if (wt) VCN_REQUIRE(cols_pad >= cols && cols_pad % 8 == 0, "pack_weights: cols_pad (%d) must be a multiple of 8 >= %d", cols_pad, cols);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  switch (w_dtype) {
-    case VCN_F32: return run_pack<float>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
-    case VCN_F16: return run_pack<__half>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
-    case VCN_BF16: return run_pack<__nv_bfloat16>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+  if (wt_dtype == VCN_F32) {
+    switch (w_dtype) {
+      case VCN_F32: return run_pack<float, float>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+      case VCN_F16: return run_pack<__half, float>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+      case VCN_BF16: return run_pack<__nv_bfloat16, float>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+    }
+  } else {
+    switch (w_dtype) {
+      case VCN_F32: return run_pack<float, __nv_bfloat16>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+      case VCN_F16: return run_pack<__half, __nv_bfloat16>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+      case VCN_BF16: return run_pack<__nv_bfloat16, __nv_bfloat16>(w, cout, cin, kh * kw, transpose_io, wt, cols_pad, wsq, st);
+    }
   }
   set_error("pack_weights: unsupported dtype %d", w_dtype);
   return VCN_ERR_INVALID;
@@ -478,14 +524,21 @@ int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int 
 int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
                          const vcn_upfirdn2d_epilogue* epi, void* dy0, float* gsum, float* db, int n, int c, int c_pad,
                          int h, int w, void* stream) {
+  return vcn_modconv_bwd_pack_ex(dy, y, dtype, dys, ys, epi, dy0, VCN_BF16, gsum, db, n, c, c_pad, h, w, stream);
+}
+
+int vcn_modconv_bwd_pack_ex(const void* dy, const void* y, int dtype, const int64_t dys[4], const int64_t ys[4],
+                            const vcn_upfirdn2d_epilogue* epi, void* dy0, int dy0_dtype, float* gsum, float* db, int n, int c,
+                            int c_pad, int h, int w, void* stream) {
   using namespace vcn;
+  VCN_REQUIRE(dy0_dtype == VCN_BF16 || dy0_dtype == VCN_F32, "modconv_bwd_pack: operand dtype must be bf16 or f32 (tf32), got %d", dy0_dtype);
   VCN_REQUIRE(n >= 0 && c >= 1 && h >= 1 && w >= 1, "modconv_bwd_pack: bad shape");
   VCN_REQUIRE(c_pad >= c && c_pad % 8 == 0, "modconv_bwd_pack: c_pad must be a multiple of 8 >= c");
   if (n == 0) return VCN_OK;
   VCN_REQUIRE(dy && dy0 && dys, "modconv_bwd_pack: dy, dys, dy0 must not be NULL");
   BwdPackArgs a;
   memset(&a, 0, sizeof(a));
-  a.dy = dy; a.y = y; a.dy0 = static_cast<__nv_bfloat16*>(dy0); a.gsum = gsum; a.db = db;
+  a.dy = dy; a.y = y; a.dy0 = dy0; a.gsum = gsum; a.db = db;
   for (int i = 0; i < 4; ++i) { a.dys[i] = dys[i]; a.ys[i] = ys ? ys[i] : dys[i]; }
   a.n = n; a.c = c; a.c_pad = c_pad; a.h = h; a.w = w;
   a.gain = 1.f; a.clamp = -1.f;
@@ -503,16 +556,25 @@ int vcn_modconv_bwd_pack(const void* dy, const void* y, int dtype, const int64_t
   while (a.subs < 64 && c <= 16 && (int64_t)n * ((h * w + 32 * a.subs - 1) / (32 * a.subs)) > (int64_t)sm_count() * 4) a.subs *= 2;
   dim3 grid((unsigned)((h * w + 32 * a.subs - 1) / (32 * a.subs)), (unsigned)((c_pad + 63) / 64), (unsigned)n);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  {  // 16-bit channels-last operands: streaming kernel of modconv_bwd_cl.cu
+  if (dy0_dtype == VCN_BF16) {  // 16-bit channels-last operands: streaming kernel of modconv_bwd_cl.cu
     const int rc = bwd_pack_cl_try(dy, y, dtype, a.dys, a.ys, epi, dy0, gsum, db, n, c, c_pad, h, w, a.act, a.alpha, a.gain,
                                    a.clamp, st);
     if (rc >= 0) return rc;
   }
-  switch (dtype) {
-    case VCN_F32: modconv_bwd_pack_kernel<float><<<grid, 256, 0, st>>>(a); break;
-    case VCN_F16: modconv_bwd_pack_kernel<__half><<<grid, 256, 0, st>>>(a); break;
-    case VCN_BF16: modconv_bwd_pack_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(a); break;
-    default: set_error("modconv_bwd_pack: unsupported dtype %d", dtype); return VCN_ERR_INVALID;
+  if (dy0_dtype == VCN_F32) {
+    switch (dtype) {
+      case VCN_F32: modconv_bwd_pack_kernel<float, float><<<grid, 256, 0, st>>>(a); break;
+      case VCN_F16: modconv_bwd_pack_kernel<__half, float><<<grid, 256, 0, st>>>(a); break;
+      case VCN_BF16: modconv_bwd_pack_kernel<__nv_bfloat16, float><<<grid, 256, 0, st>>>(a); break;
+      default: set_error("modconv_bwd_pack: unsupported dtype %d", dtype); return VCN_ERR_INVALID;
+    }
+  } else {
+    switch (dtype) {
+      case VCN_F32: modconv_bwd_pack_kernel<float, __nv_bfloat16><<<grid, 256, 0, st>>>(a); break;
+      case VCN_F16: modconv_bwd_pack_kernel<__half, __nv_bfloat16><<<grid, 256, 0, st>>>(a); break;
+      case VCN_BF16: modconv_bwd_pack_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, st>>>(a); break;
+      default: set_error("modconv_bwd_pack: unsupported dtype %d", dtype); return VCN_ERR_INVALID;
+    }
   }
   VCN_LAUNCH_CHECK("modconv_bwd_pack_kernel");
   return VCN_OK;

@@ -844,6 +844,178 @@ int try_launch_cl(const UpfirdnArgs& a, int dtype, int y_dtype, cudaStream_t st)
   return VCN_OK;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// separable long filters: one 1-D pass along x (fh == 1) or along y (fw == 1), 5..32 taps, up / down in {1, 2} along the
+// axis (the reference's 1-D specialisations upfirdn2d.cu:219-246,264-338 - AugmentPipe's 12-tap sym6 resampling,
+// augment.py:167,290,301 - and the two passes of every `separable` setup_filter, upfirdn2d.py:239-240).  Dense NCHW,
+// fp32 / fp16 / bf16.  The CTA stages the input segment of its output tile in shared memory (zero outside the image = the
+// op's padding), every thread keeps the taps ITS output phase uses in registers (gain folded in, zero-extended to the
+// template size) and reads consecutive shared-memory words: K = FWMAX / UP shared loads + FMAs per output, one coalesced
+// global read and write per element.
+// ---------------------------------------------------------------------------------------------
+constexpr int k1dTW = 128, k1dTL = 16;   // x pass: 128 outputs x 16 lines per CTA
+constexpr int k1dTX = 64, k1dTH = 64;    // y pass: 64 columns x 64 outputs per CTA
+
+template <int FWMAX, int UP>
+__device__ __forceinline__ void load_taps_1d(const UpfirdnArgs& a, int ntaps, int fx0, float (&w)[(FWMAX + UP - 1) / UP]) {
+  // tap fx of the pass: the filter as given when `flip`, reversed otherwise (upfirdn2d.cu:125-127); gain folded in
+#pragma unroll
+  for (int k = 0; k < (FWMAX + UP - 1) / UP; ++k) {
+    const int fx = fx0 + UP * k;
+    w[k] = fx < ntaps ? __ldg(a.f + (a.flip ? fx : ntaps - 1 - fx)) * a.gain : 0.f;
+  }
+}
+
+template <typename T, int FWMAX, int UP>
+__global__ void __launch_bounds__(256) upfirdn1d_x_kernel(const UpfirdnArgs a, int down, int lines, int tiles_x) {
+  constexpr int K = (FWMAX + UP - 1) / UP;
+  constexpr int SEG = (k1dTW - 1) * 2 / UP + K + 4;
+  constexpr int PITCH = SEG + 1;
+  __shared__ float s[k1dTL * PITCH];
+  __shared__ int64_t s_in[k1dTL], s_out[k1dTL];  // element offsets of the CTA's lines (-1: past the end)
+  const int bx = blockIdx.x % tiles_x, bl = blockIdx.x / tiles_x;
+  const int ox0 = bx * k1dTW, line0 = bl * k1dTL;
+  const int seg_lo = floor_div(ox0 * down - a.padx0, UP);
+  const T* __restrict__ px = static_cast<const T*>(a.x);
+  T* __restrict__ py = static_cast<T*>(a.y);
+  if (threadIdx.x < k1dTL) {
+    const int line = line0 + threadIdx.x;
+    int64_t oi = -1, oo = -1;
+    if (line < lines) {
+      const int y = line % a.in_h, pc = line / a.in_h;
+      oi = (int64_t)(pc / a.c) * a.xs[0] + (int64_t)(pc % a.c) * a.xs[1] + (int64_t)y * a.xs[2];
+      oo = (int64_t)(pc / a.c) * a.ys[0] + (int64_t)(pc % a.c) * a.ys[1] + (int64_t)y * a.ys[2];
+    }
+    s_in[threadIdx.x] = oi; s_out[threadIdx.x] = oo;
+  }
+  __syncthreads();
+  // stage the input segments: one flat index space so that every thread has ~17 independent loads in flight
+  constexpr int NLD = (k1dTL * SEG + 255) / 256;
+  T v[NLD];
+#pragma unroll
+  for (int i = 0; i < NLD; ++i) {  // all loads first (independent), then the shared-memory writes
+    const int e = threadIdx.x + i * 256;
+    const int l = e / SEG, j = e - l * SEG;
+    const int ix = seg_lo + j;
+    const int64_t off = e < k1dTL * SEG ? s_in[l] : -1;
+    v[i] = (off >= 0 && ix >= 0 && ix < a.in_w) ? px[off + ix] : T(0);
+  }
+#pragma unroll
+  for (int i = 0; i < NLD; ++i) {
+    const int e = threadIdx.x + i * 256;
+    const int l = e / SEG, j = e - l * SEG;
+    if (e < k1dTL * SEG) s[l * PITCH + j] = to_acc<T>(v[i]);
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & (k1dTW - 1), lg = threadIdx.x >> 7;
+  const int ox = ox0 + tx;
+  if (ox >= a.out_w) return;
+  const int mx = ox * down - a.padx0;
+  const int fx0 = ((-mx) % UP + UP) % UP;
+  float w[K];
+  load_taps_1d<FWMAX, UP>(a, a.fw, fx0, w);
+  const int base = (mx + fx0) / UP - seg_lo;  // exact division: mx + fx0 is a multiple of UP
+#pragma unroll 2
+  for (int q = 0; q < k1dTL / 2; ++q) {
+    const int l = lg * (k1dTL / 2) + q;
+    const int64_t oo = s_out[l];
+    if (oo < 0) break;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc = fmaf(w[k], s[l * PITCH + base + k], acc);
+    py[oo + ox] = from_acc<T>(acc);
+  }
+}
+
+template <typename T, int FWMAX, int UP>
+__global__ void __launch_bounds__(256) upfirdn1d_y_kernel(const UpfirdnArgs a, int down, int tiles_x, int tiles_y) {
+  constexpr int K = (FWMAX + UP - 1) / UP;
+  constexpr int SEG = (k1dTH - 1) * 2 / UP + K + 4;
+  __shared__ float s[SEG][k1dTX + 1];
+  int b = blockIdx.x;
+  const int bx = b % tiles_x; b /= tiles_x;
+  const int by = b % tiles_y;
+  const int pc = b / tiles_y;
+  const int x0 = bx * k1dTX, oy0 = by * k1dTH;
+  const int seg_lo = floor_div(oy0 * down - a.pady0, UP);
+  // rows this tile reads, zero-extended taps included (they multiply by 0 but must not meet uninitialised NaN bit patterns)
+  const int seg_n = min(SEG, ((min(k1dTH, a.out_h - oy0) - 1) * down) / UP + K + 2);
+  const T* __restrict__ src = static_cast<const T*>(a.x) + (int64_t)(pc / a.c) * a.xs[0] + (int64_t)(pc % a.c) * a.xs[1];
+  T* __restrict__ dst = static_cast<T*>(a.y) + (int64_t)(pc / a.c) * a.ys[0] + (int64_t)(pc % a.c) * a.ys[1];
+  const int tx = threadIdx.x & (k1dTX - 1), tg = threadIdx.x >> 6;  // 4 row groups
+  const int x = x0 + tx;
+#pragma unroll 1
+  for (int j0 = tg; j0 < seg_n; j0 += 32) {  // 8 independent loads per thread per round
+    T v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int j = j0 + 4 * i, iy = seg_lo + j;
+      v[i] = (j < seg_n && x < a.in_w && iy >= 0 && iy < a.in_h) ? src[(int64_t)iy * a.xs[2] + x] : T(0);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int j = j0 + 4 * i;
+      if (j < seg_n) s[j][tx] = to_acc<T>(v[i]);
+    }
+  }
+  __syncthreads();
+  if (x >= a.out_w) return;
+  float w[2][K];  // the two output phases of an up = 2 pass use different taps (UP = 1: both rows are the same)
+  load_taps_1d<FWMAX, UP>(a, a.fh, 0, w[0]);
+  load_taps_1d<FWMAX, UP>(a, a.fh, UP - 1, w[1]);
+#pragma unroll 2
+  for (int q = 0; q < k1dTH / 4; ++q) {
+    const int oy = oy0 + tg + 4 * q;
+    if (oy >= a.out_h) break;
+    const int my = oy * down - a.pady0;
+    const int fy0 = ((-my) % UP + UP) % UP;
+    const int base = (my + fy0) / UP - seg_lo;
+    float acc = 0.f;
+    if (UP == 1 || fy0 == 0) {
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc = fmaf(w[0][k], s[base + k][tx], acc);
+    } else {
+#pragma unroll
+      for (int k = 0; k < K; ++k) acc = fmaf(w[1][k], s[base + k][tx], acc);
+    }
+    dst[(int64_t)oy * a.ys[2] + x] = from_acc<T>(acc);
+  }
+}
+
+// Eligibility + launch of the 1-D kernels.  Returns -1 when the configuration is not covered.
+template <typename T>
+int try_launch_1d(const UpfirdnArgs& a, cudaStream_t st) {
+  if (a.scale || a.noise || a.act) return -1;
+  if (!(a.xs[3] == 1 && a.ys[3] == 1)) return -1;
+  const bool xpass = a.fh == 1 && a.fw > kF && a.upy == 1 && a.downy == 1 && a.pady0 == 0 && a.out_h == a.in_h;
+  const bool ypass = a.fw == 1 && a.fh > kF && a.upx == 1 && a.downx == 1 && a.padx0 == 0 && a.out_w == a.in_w;
+  if (!xpass && !ypass) return -1;
+  const int taps = xpass ? a.fw : a.fh, up = xpass ? a.upx : a.upy, down = xpass ? a.downx : a.downy;
+  if (taps > 32 || up > 2 || down > 2) return -1;
+  const int64_t planes = (int64_t)a.n * a.c;
+#define VCN_1D(FW, UPV)                                                                                              \
+  do {                                                                                                               \
+    if (xpass) {                                                                                                     \
+      const int64_t lines = planes * a.in_h;                                                                         \
+      const int tiles_x = (a.out_w + k1dTW - 1) / k1dTW;                                                             \
+      const int64_t blocks = (int64_t)tiles_x * ((lines + k1dTL - 1) / k1dTL);                                       \
+      if (blocks > 0x7fffffffLL) return -1;                                                                          \
+      upfirdn1d_x_kernel<T, FW, UPV><<<(unsigned)blocks, 256, 0, st>>>(a, down, (int)lines, tiles_x);               \
+    } else {                                                                                                         \
+      const int tiles_x = (a.out_w + k1dTX - 1) / k1dTX, tiles_y = (a.out_h + k1dTH - 1) / k1dTH;                    \
+      const int64_t blocks = (int64_t)tiles_x * tiles_y * planes;                                                    \
+      if (blocks > 0x7fffffffLL) return -1;                                                                          \
+      upfirdn1d_y_kernel<T, FW, UPV><<<(unsigned)blocks, 256, 0, st>>>(a, down, tiles_x, tiles_y);                  \
+    }                                                                                                                \
+  } while (0)
+  if (up == 1) { if (taps <= 12) VCN_1D(12, 1); else if (taps <= 24) VCN_1D(24, 1); else VCN_1D(32, 1); }
+  else { if (taps <= 12) VCN_1D(12, 2); else if (taps <= 24) VCN_1D(24, 2); else VCN_1D(32, 2); }
+#undef VCN_1D
+  VCN_LAUNCH_CHECK("upfirdn1d_kernel");
+  return VCN_OK;
+}
+
 inline int pow2_ceil(int v) {
   int p = 1;
   while (p < v) p <<= 1;
@@ -973,6 +1145,10 @@ int run(const UpfirdnArgs& a, int dtype, cudaStream_t st) {
     if (phx == 1 && phy == 0) return launch_tile<T, 2, 1, 1, 0>(a, g, dtype, st);
     if (phx == 0 && phy == 1) return launch_tile<T, 2, 1, 0, 1>(a, g, dtype, st);
     return launch_tile<T, 2, 1, 1, 1>(a, g, dtype, st);
+  }
+  if constexpr (sizeof(T) != 8) {  // separable long filters (one 1-D pass per call)
+    const int rc = try_launch_1d<T>(a, st);
+    if (rc >= 0) return rc;
   }
   const int64_t total = (int64_t)a.n * a.c * a.out_h * a.out_w;
   int64_t grid = (total + 255) / 256;

@@ -17,6 +17,7 @@ the fused SynthesisLayer body (networks.py:286-305): the bias + activation + gai
 
 import ctypes
 import math
+import os
 
 import torch
 
@@ -24,6 +25,18 @@ from .. import _lib
 from .misc import profiled_function as _profiled
 from . import bias_act as _bias_act
 from . import upfirdn2d as _upfirdn2d
+
+
+# Operand precision of the implicit GEMM for fp32 activations (the reference's layout / dtype):
+#   'tf32' (default)  fp32 operands on tcgen05 kind::tf32 - 10-bit mantissa, what the reference's own GPU path computes
+#                     (cuDNN TF32 convolutions, torch default; SURVEY 8(c) gate: fwd <= 3e-3), half the bf16 tensor rate;
+#   'bf16'            operands rounded to bf16 (8-bit mantissa; gate 1e-2 / 2e-2) at the full rate.
+# 16-bit activations (the bf16-resident pipeline the train step and the inference fast path run) always use bf16 operands.
+fp32_operands = os.environ.get("VCN_FP32_OPERANDS", "tf32")
+
+
+def _operand_dtype(x):
+    return torch.float32 if (x.dtype == torch.float32 and fp32_operands == "tf32") else torch.bfloat16
 
 
 def _strides4(t):
@@ -37,36 +50,37 @@ def _round_up(v, m):
 # ---- thin launch helpers (one C-ABI call each) ---------------------------------------------------------------
 
 
-def modulate_pack(x, styles):
-    """x [N,C,H,W] (any dense-ish strides) * styles [N,C] (fp32 or None) -> bf16 NHWC [N,H,W,C_pad]."""
+def modulate_pack(x, styles, out_dtype=torch.bfloat16):
+    """x [N,C,H,W] (any dense-ish strides) * styles [N,C] (fp32 or None) -> NHWC [N,H,W,C_pad] GEMM operand (bf16, or fp32
+    for the kind::tf32 GEMM)."""
     lib = _lib.load()
     n, c, h, w = x.shape
     c_pad = _round_up(c, 8)
-    out = torch.empty([n, h, w, c_pad], dtype=torch.bfloat16, device=x.device)
+    out = torch.empty([n, h, w, c_pad], dtype=out_dtype, device=x.device)
     if styles is not None:
         styles = styles.to(torch.float32).contiguous()
         assert styles.shape == (n, c)
     if n == 0:
         return out
     with torch.cuda.device(x.device):
-        st = lib.vcn_modulate_pack(_lib.ptr(x), _lib.dtype_code(x.dtype), ctypes.byref(_strides4(x)), _lib.ptr(styles),
-                                   _lib.ptr(out), n, c, c_pad, h, w, _lib.current_stream(x.device))
+        st = lib.vcn_modulate_pack_ex(_lib.ptr(x), _lib.dtype_code(x.dtype), ctypes.byref(_strides4(x)), _lib.ptr(styles),
+                                      _lib.ptr(out), _lib.dtype_code(out_dtype), n, c, c_pad, h, w, _lib.current_stream(x.device))
     _lib.check(st, "vcn_modulate_pack")
     return out
 
 
-def pack_weights(weight, transpose_io=False, want_wsq=False):
-    """W [Cout,Cin,kh,kw] -> (wt bf16 [kh*kw, rows, cols_pad], wsq fp32 [Cout,Cin] or None)."""
+def pack_weights(weight, transpose_io=False, want_wsq=False, out_dtype=torch.bfloat16):
+    """W [Cout,Cin,kh,kw] -> (wt [kh*kw, rows, cols_pad] in the GEMM operand dtype, wsq fp32 [Cout,Cin] or None)."""
     lib = _lib.load()
     weight = weight.detach().contiguous()
     cout, cin, kh, kw = weight.shape
     rows, cols = (cin, cout) if transpose_io else (cout, cin)
     cols_pad = _round_up(cols, 8)
-    wt = torch.empty([kh * kw, rows, cols_pad], dtype=torch.bfloat16, device=weight.device)
+    wt = torch.empty([kh * kw, rows, cols_pad], dtype=out_dtype, device=weight.device)
     wsq = torch.empty([cout, cin], dtype=torch.float32, device=weight.device) if want_wsq else None
     with torch.cuda.device(weight.device):
-        st = lib.vcn_pack_weights(_lib.ptr(weight), _lib.dtype_code(weight.dtype), cout, cin, kh, kw, int(transpose_io),
-                                  _lib.ptr(wt), cols_pad, _lib.ptr(wsq), _lib.current_stream(weight.device))
+        st = lib.vcn_pack_weights_ex(_lib.ptr(weight), _lib.dtype_code(weight.dtype), cout, cin, kh, kw, int(transpose_io),
+                                     _lib.ptr(wt), _lib.dtype_code(out_dtype), cols_pad, _lib.ptr(wsq), _lib.current_stream(weight.device))
     _lib.check(st, "vcn_pack_weights")
     return wt, wsq
 
@@ -123,12 +137,12 @@ def make_epilogue(scale=None, noise=None, bias=None, act=None, alpha=None, gain=
 
 def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_last=False, epilogue=None, out=None,
                w_per_sample=False):
-    """One vcn_conv_igemm launch.  xhat bf16 [N,H,W,Cin_pad]; wt bf16 [kh*kw, cout, Cin_pad].  Returns y as a
-    logical [N,cout,OH,OW] tensor (NCHW memory, or channels_last memory when requested)."""
+    """One vcn_conv_igemm launch.  xhat [N,H,W,Cin_pad] and wt [kh*kw, cout, Cin_pad] both bf16 (kind::f16 GEMM) or both
+    fp32 (kind::tf32 GEMM).  Returns y as a logical [N,cout,OH,OW] tensor (NCHW memory, or channels_last when requested)."""
     lib = _lib.load()
     _lib.require_device(xhat.device.index)
     n, h, w, cin_pad = xhat.shape
-    assert xhat.dtype == torch.bfloat16 and wt.dtype == torch.bfloat16 and xhat.is_contiguous() and wt.is_contiguous()
+    assert xhat.dtype in (torch.bfloat16, torch.float32) and wt.dtype == xhat.dtype and xhat.is_contiguous() and wt.is_contiguous()
     want = (n, kh * kw, cout, cin_pad) if w_per_sample else (kh * kw, cout, cin_pad)
     assert tuple(wt.shape) == want, (tuple(wt.shape), want)
     oh, ow = (2 * h + 1, 2 * w + 1) if kind == _lib.CONV_TCONV2 else ((h - 1) // 2, (w - 1) // 2) if kind == _lib.CONV_SCONV2 else (h, w)
@@ -139,7 +153,8 @@ def conv_igemm(xhat, wt, kind, cout, kh, kw, out_dtype=torch.float32, channels_l
     if n == 0:
         return out
     d = _lib.ConvDesc(kind=kind, n=n, h=h, w=w, cin_pad=cin_pad, cout=cout, kh=kh, kw=kw, out_h=oh, out_w=ow,
-                      y_dtype=_lib.dtype_code(out.dtype), ys=_strides4(out), w_per_sample=int(w_per_sample))
+                      y_dtype=_lib.dtype_code(out.dtype), ys=_strides4(out), w_per_sample=int(w_per_sample),
+                      tf32=int(xhat.dtype == torch.float32))
     epi = ctypes.byref(epilogue) if epilogue is not None else None
     with torch.cuda.device(xhat.device):
         st = lib.vcn_conv_igemm(_lib.ptr(xhat), _lib.ptr(wt), _lib.ptr(out), ctypes.byref(d), epi,
@@ -166,12 +181,12 @@ def pack_weights_mod(weight, styles, dcoef=None):
     return wn
 
 
-def bwd_pack(dy, y, epilogue, want_gsum, want_db):
-    """vcn_modconv_bwd_pack: (dy0 bf16 NHWC [N,H,W,C_pad], gsum [N,C] or None, db [C] or None)."""
+def bwd_pack(dy, y, epilogue, want_gsum, want_db, out_dtype=torch.bfloat16):
+    """vcn_modconv_bwd_pack: (dy0 NHWC [N,H,W,C_pad] in the GEMM operand dtype, gsum [N,C] or None, db [C] or None)."""
     lib = _lib.load()
     n, c, h, w = dy.shape
     c_pad = _round_up(c, 8)
-    dy0 = torch.empty([n, h, w, c_pad], dtype=torch.bfloat16, device=dy.device)
+    dy0 = torch.empty([n, h, w, c_pad], dtype=out_dtype, device=dy.device)
     gsum = torch.zeros([n, c], dtype=torch.float32, device=dy.device) if want_gsum else None
     db = torch.zeros([c], dtype=torch.float32, device=dy.device) if want_db else None
     if n == 0:
@@ -179,10 +194,10 @@ def bwd_pack(dy, y, epilogue, want_gsum, want_db):
     if y is not None:
         assert y.shape == dy.shape and y.dtype == dy.dtype
     with torch.cuda.device(dy.device):
-        st = lib.vcn_modconv_bwd_pack(_lib.ptr(dy), _lib.ptr(y), _lib.dtype_code(dy.dtype), ctypes.byref(_strides4(dy)),
-                                      ctypes.byref(_strides4(y)) if y is not None else None, ctypes.byref(epilogue),
-                                      _lib.ptr(dy0), _lib.ptr(gsum), _lib.ptr(db), n, c, c_pad, h, w,
-                                      _lib.current_stream(dy.device))
+        st = lib.vcn_modconv_bwd_pack_ex(_lib.ptr(dy), _lib.ptr(y), _lib.dtype_code(dy.dtype), ctypes.byref(_strides4(dy)),
+                                         ctypes.byref(_strides4(y)) if y is not None else None, ctypes.byref(epilogue),
+                                         _lib.ptr(dy0), _lib.dtype_code(out_dtype), _lib.ptr(gsum), _lib.ptr(db), n, c, c_pad, h, w,
+                                         _lib.current_stream(dy.device))
     _lib.check(st, "vcn_modconv_bwd_pack")
     return dy0, gsum, db
 
@@ -256,11 +271,11 @@ def demod_grad(ds, styles, gsum, dcoef, wsq):
 _wcache = {}
 
 
-def _packed(weight, transpose_io, flip, want_wsq):
-    """Packed bf16 taps (+ wsq) of `weight`, cached per tensor object and version.  The entry holds a weak reference to
-    the tensor so that a recycled address or id can never alias a dead tensor's entry."""
+def _packed(weight, transpose_io, flip, want_wsq, dtype=torch.bfloat16):
+    """Packed taps (+ wsq) of `weight` in the GEMM operand dtype, cached per tensor object and version.  The entry holds a
+    weak reference to the tensor so that a recycled address or id can never alias a dead tensor's entry."""
     import weakref
-    key = (id(weight), transpose_io, flip)
+    key = (id(weight), transpose_io, flip, dtype)
     hit = _wcache.get(key)
     if hit is not None:
         ref, version, ptr, wt, wsq = hit
@@ -269,7 +284,7 @@ def _packed(weight, transpose_io, flip, want_wsq):
     src = weight.detach()
     if flip:
         src = src.flip([2, 3])
-    wt, wsq = pack_weights(src, transpose_io=transpose_io, want_wsq=True)
+    wt, wsq = pack_weights(src, transpose_io=transpose_io, want_wsq=True, out_dtype=dtype)
     if len(_wcache) > 512:
         for k in [k for k, v in _wcache.items() if v[0]() is None]:
             del _wcache[k]
@@ -293,15 +308,16 @@ class _ModConvLayer(torch.autograd.Function):
         assert styles is None or tuple(styles.shape) == (n, cin)
         styles32 = styles.to(torch.float32).contiguous() if styles is not None else None
         hold = []
+        op = _operand_dtype(x)  # fp32 activations: tf32 operands unless modconv.fp32_operands == 'bf16'
         if up == 1:
-            wt, wsq = _packed(weight, False, False, demodulate)
+            wt, wsq = _packed(weight, False, False, demodulate, op)
         else:
             assert up == 2 and kh == 3, "modulated_conv2d(impl='cuda'): up=2 needs a 3x3 kernel"
             assert resample_filter is not None and tuple(resample_filter.shape) == (4, 4), "up=2 needs a 4x4 resample filter"
             # reference: flip_weight=False -> conv_transpose2d with the weight as is (conv2d_resample.py:127-138)
-            wt, wsq = _packed(weight, False, bool(flip_weight), demodulate)
+            wt, wsq = _packed(weight, False, bool(flip_weight), demodulate, op)
         d = demod_coefs(styles32, wsq) if demodulate else None
-        xhat = modulate_pack(x, styles32)
+        xhat = modulate_pack(x, styles32, op)
         epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp,
                                   out_shape=(n, h * up, w * up))
         # resident pipeline: 16-bit channels-last activations stay 16-bit channels-last (forward and backward); a ToRGB
@@ -320,6 +336,7 @@ class _ModConvLayer(torch.autograd.Function):
             y = _upfirdn2d.launch(z, f, 1, 1, 1, 1, 1, 1, 1, 1, False, 4.0, epilogue=epi,
                                   out=torch.empty([n, cout, 2 * h, 2 * w], dtype=out_dtype, device=x.device, memory_format=fmt))
         ctx.resident = resident
+        ctx.op = op
         ctx.cfg = cfg
         ctx.has = (styles is not None, noise is not None, bias is not None)
         ctx.save_for_backward(x, weight, styles32, noise, bias, resample_filter, d, wsq, y)
@@ -343,7 +360,8 @@ class _ModConvLayer(torch.autograd.Function):
         epi, hold = make_epilogue(scale=d, noise=noise, bias=bias, act=act, alpha=alpha, gain=gain, clamp=clamp,
                                   out_shape=(n, h * up, w * up))
         want_g = demodulate and (need_s or need_w)
-        dy0, gsum, db = bwd_pack(dy, y if (act is not None or want_g) else None, epi, want_g, need_b and bias is not None)
+        op = ctx.op
+        dy0, gsum, db = bwd_pack(dy, y if (act is not None or want_g) else None, epi, want_g, need_b and bias is not None, op)
         dx = ds = dnoise = dw = None
         dz = None
         if up == 2 and (need_x or need_s or need_w):
@@ -354,12 +372,12 @@ class _ModConvLayer(torch.autograd.Function):
             assert dz.is_contiguous()
         if need_x or need_s:
             if up == 1:
-                wt_t, _ = _packed(weight, True, False, False)
+                wt_t, _ = _packed(weight, True, False, False, op)
                 kind = _lib.CONV_DGRAD if flip_weight else _lib.CONV_FPROP
                 dxhat = conv_igemm(dy0, wt_t, kind, cin, kh, kw, out_dtype=torch.bfloat16 if resident else torch.float32,
                                    channels_last=resident)
             else:
-                wt_t, _ = _packed(weight, True, bool(flip_weight), False)
+                wt_t, _ = _packed(weight, True, bool(flip_weight), False, op)
                 dxhat = conv_igemm(dz, wt_t, _lib.CONV_SCONV2, cin, 3, 3, out_dtype=torch.bfloat16 if resident else torch.float32,
                                    channels_last=resident)
             if resident:
@@ -375,7 +393,11 @@ class _ModConvLayer(torch.autograd.Function):
         if need_w:
             # dW = sum_n,p dy0 (x) xhat on the tensor cores (both operands as the other GEMMs use them), plus the path
             # through the demodulation coefficients: d = rsqrt(sum (s W)^2) gives  -W * sum_n gsum d^2 s^2
+            # the weight-gradient GEMM (MN-major operands) runs bf16 operands in either mode
             xhat = modulate_pack(x, styles32)
+            if op != torch.bfloat16:
+                dy0 = dy0.to(torch.bfloat16)
+                dz = dz.to(torch.bfloat16) if dz is not None else None
             if up == 1:
                 dw = conv_wgrad(dy0, xhat, cout, cin, kh, kw)
                 if not flip_weight:
