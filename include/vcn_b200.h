@@ -70,6 +70,24 @@ int vcn_bias_act(const void* x, const void* b, const void* xref, const void* yre
                  int dtype, int grad, int act, float alpha, float gain, float clamp,
                  int64_t size_x, int64_t size_b, int64_t step_b, void* stream);
 
+/* Allocation-free variant of vcn_bias_act.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments and results as vcn_bias_act without the workspace pair: the partial sums of the fused `db`
+ * reduction go to a file-scope `static __device__` array inside the library (VCN_BIAS_ACT_STATIC_SCRATCH_BYTES = 1 MiB,
+ * held by every GPU that loads the library until the process exits; its device address is resolved once per device with
+ * cudaGetSymbolAddress).  The call itself performs no cudaMalloc/cudaFree and calls no allocating routine.
+ * A shape whose vcn_bias_act_workspace() exceeds the array returns VCN_ERR_INVALID with a message (1 MiB = 262144 fp32
+ * partial sums, one per (sample, channel, row chunk); the largest hot-path call, [16,128,256,256], needs 128 KiB).
+ * All calls on a device share the array and it keeps the last call's contents; nothing in it has to start at zero
+ * (every slot read is written earlier in the same call).  Two calls whose kernels overlap on the GPU (different
+ * streams, no ordering between them) RACE on it: order them, or use vcn_bias_act with separate workspaces. */
+#define VCN_BIAS_ACT_STATIC_SCRATCH_BYTES (1u << 20)
+size_t vcn_bias_act_static_scratch_bytes(void);
+int vcn_bias_act_static(const void* x, const void* b, const void* xref, const void* yref, const void* dy,
+                        void* y, void* db,
+                        int dtype, int grad, int act, float alpha, float gain, float clamp,
+                        int64_t size_x, int64_t size_b, int64_t step_b, void* stream);
+
 /* ---- upfirdn2d ---------------------------------------------------------------------------
  * Replaces `upfirdn2d(x, f, upx, upy, downx, downy, padx0, padx1, pady0, pady1, flip, gain)`
  * (upfirdn2d.cpp:16-94, kernels upfirdn2d.cu:29-200).  x is [n, c, in_h, in_w] with element

@@ -48,6 +48,8 @@ SIGNATURES = {
     "vcn_device_info": (_i, [_i, _c.POINTER(_i), _c.POINTER(_i64), _c.POINTER(_i), _c.POINTER(_i)]),
     "vcn_bias_act_workspace": (_sz, [_i, _i64, _i64, _i64]),
     "vcn_bias_act": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _i, _i, _i, _f, _f, _f, _i64, _i64, _i64, _vp]),
+    "vcn_bias_act_static_scratch_bytes": (_sz, []),
+    "vcn_bias_act_static": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _f, _i64, _i64, _i64, _vp]),
     "vcn_upfirdn2d": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _c.POINTER(_i64 * 4), _i, _i, _c.POINTER(_i64 * 4),
                            _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _f, _c.POINTER(UpfirdnEpilogue), _vp]),
     "vcn_modulate_pack": (_i, [_vp, _i, _c.POINTER(_i64 * 4), _vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -15,6 +15,8 @@
 // Algorithmic bytes: forward 2*S*e; grad 1 and 2: 3*S*e (+S*e when both xref and yref are read).
 #include "act_math.cuh"
 
+#include <mutex>
+
 namespace vcn {
 namespace {
 
@@ -396,6 +398,71 @@ int vcn_bias_act(const void* x, const void* b, const void* xref, const void* yre
     case VCN_F64: return run<double>(a, db, workspace, workspace_bytes, st);
   }
   return VCN_ERR_INVALID;
+}
+
+}  // extern "C"
+
+// ---- allocation-free variant -----------------------------------------------------------------------------------
+// The partial-sum scratch of the fused db reduction lives in a file-scope device array instead of a caller-provided
+// workspace.  Every device that loads the library holds VCN_BIAS_ACT_STATIC_SCRATCH_BYTES of it until the process exits.
+// In host code `g_bias_act_static_scratch` is only a stand-in for the symbol: its device address is looked up once per
+// device with cudaGetSymbolAddress (with that device current) and that pointer is what the kernels receive.
+namespace vcn {
+namespace {
+constexpr size_t kStaticScratchBytes = 1u << 20;  // 1 MiB == VCN_BIAS_ACT_STATIC_SCRATCH_BYTES in include/vcn_b200.h
+constexpr int kMaxDevices = 64;
+}  // namespace
+}  // namespace vcn
+
+static __device__ __align__(256) unsigned char g_bias_act_static_scratch[vcn::kStaticScratchBytes];
+
+namespace vcn {
+namespace {
+std::mutex g_static_scratch_mu;
+void* g_static_scratch_ptr[kMaxDevices] = {};
+
+// Device address of the scratch array on the CURRENT device (0 + error text on failure).
+int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_error("bias_act_static: cudaGetDevice: %s", cudaGetErrorString(e)); return VCN_ERR_CUDA; }
+  VCN_REQUIRE(dev >= 0 && dev < kMaxDevices, "bias_act_static: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_scratch_mu);
+  if (!g_static_scratch_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_bias_act_static_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("bias_act_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return VCN_ERR_CUDA;
+    }
+    g_static_scratch_ptr[dev] = p;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return VCN_OK;
+}
+}  // namespace
+}  // namespace vcn
+
+extern "C" {
+
+size_t vcn_bias_act_static_scratch_bytes(void) { return vcn::kStaticScratchBytes; }
+
+int vcn_bias_act_static(const void* x, const void* b, const void* xref, const void* yref, const void* dy, void* y,
+                        void* db, int dtype, int grad, int act, float alpha, float gain, float clamp, int64_t size_x,
+                        int64_t size_b, int64_t step_b, void* stream) {
+  using namespace vcn;
+  size_t need = 0;
+  void* scratch = nullptr;
+  if (db) {
+    need = vcn_bias_act_workspace(dtype, size_x, size_b, step_b);
+    VCN_REQUIRE(need <= kStaticScratchBytes,
+                "bias_act_static: this shape needs %zu bytes of reduction scratch, the built-in array holds %zu "
+                "(use vcn_bias_act with a caller workspace)", need, (size_t)kStaticScratchBytes);
+    // every slot the finalize pass reads is written by the rows kernel of the same call: nothing has to start at zero
+    if (int rc = static_scratch_for_current_device(&scratch)) return rc;
+  }
+  return vcn_bias_act(x, b, xref, yref, dy, y, db, scratch, db ? kStaticScratchBytes : 0, dtype, grad, act, alpha,
+                      gain, clamp, size_x, size_b, step_b, stream);
 }
 
 }  // extern "C"
