@@ -753,13 +753,26 @@ def main():
                 pass
         print(json.dumps(line), flush=True)
     if world > 1:
-        # CUDA graphs that captured NCCL collectives keep the communicator busy: tearing the process group down under them
-        # can hang.  Everything is printed and synchronised: leave without the teardown.
+        # Orderly teardown: the CUDA graphs that captured NCCL collectives go first (they pin the communicator's streams), then
+        # the process group.  A daemon watchdog leaves the process if the communicator still refuses to come down - the line
+        # is printed and every rank is synchronised by then, so a stuck teardown must not cost the run.
         sys.stdout.flush()
         sys.stderr.flush()
         torch.cuda.synchronize()
         barrier(world)
-        os._exit(0)
+        import gc
+        import threading
+        dog = threading.Timer(20.0, lambda: os._exit(0))
+        dog.daemon = True
+        dog.start()
+        tr = getattr(wl, "tr", None)
+        if tr is not None:
+            tr._graphs.clear()
+        del wl, tr
+        gc.collect()
+        torch.cuda.synchronize()
+        torch.distributed.destroy_process_group()
+        dog.cancel()
 
 
 if __name__ == "__main__":

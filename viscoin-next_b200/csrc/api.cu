@@ -1,5 +1,6 @@
 // api.cu - library-level entry points: status/error text, device probe, TMA descriptor factory.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -83,6 +84,28 @@ int make_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, con
     es[i] = elem_strides ? elem_strides[i] : 1u;
   }
   for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
+  // Immutable descriptor cache (per thread, direct-mapped): an encoded map is a pure function of the arguments below, and a
+  // training loop presents the same (pointer, shape, box) tuples every iteration (caching allocator), so the steady state
+  // of the eager path does no driver call here.  The full key is compared, a hash collision only costs a re-encode.
+  struct Key {
+    const void* base; uint64_t d[5], s[4]; uint32_t b[5], e[5]; int dtype, rank, swz;
+  };
+  struct Slot { Key k; CUtensorMap m; bool used; };
+  constexpr int kSlots = 256;
+  static thread_local Slot* cache = nullptr;
+  if (!cache) cache = static_cast<Slot*>(calloc(kSlots, sizeof(Slot)));
+  Key key;
+  memset(&key, 0, sizeof(key));
+  key.base = base; key.dtype = dtype; key.rank = rank; key.swz = swizzle_128b;
+  for (int i = 0; i < rank; ++i) { key.d[i] = gd[i]; key.b[i] = bx[i]; key.e[i] = es[i]; }
+  for (int i = 0; i + 1 < rank; ++i) key.s[i] = gs[i];
+  uint64_t h = 1469598103934665603ull;
+  for (size_t i = 0; i < sizeof(Key) / 8; ++i) { h ^= reinterpret_cast<const uint64_t*>(&key)[i]; h *= 1099511628211ull; }
+  Slot* slot = cache ? cache + (h >> 20) % kSlots : nullptr;
+  if (slot && slot->used && memcmp(&slot->k, &key, sizeof(Key)) == 0) {
+    memcpy(out, &slot->m, sizeof(CUtensorMap));
+    return VCN_OK;
+  }
   CUresult r = fn(out, dt, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   swizzle_128b ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -92,6 +115,11 @@ int make_tensor_map(CUtensorMap* out, int dtype, int rank, const void* base, con
               (unsigned long long)(rank > 2 ? gd[2] : 0), (unsigned long long)(rank > 3 ? gd[3] : 0), bx[0],
               rank > 1 ? bx[1] : 0, rank > 2 ? bx[2] : 0, rank > 3 ? bx[3] : 0);
     return VCN_ERR_CUDA;
+  }
+  if (slot) {
+    slot->k = key;
+    memcpy(&slot->m, out, sizeof(CUtensorMap));
+    slot->used = true;
   }
   return VCN_OK;
 }

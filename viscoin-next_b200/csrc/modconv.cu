@@ -283,8 +283,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
   float* s_par = reinterpret_cast<float*>(tmem_ptr_smem + 4);  // [2 acc stages][scale n_tile | bias n_tile]
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int rank = PAIR ? (int)cluster_ctarank() : 0;                  // 0 = leader of the CTA pair (issues the MMAs)
+  // the warp index goes through a shuffle so that the compiler KNOWS it is warp-uniform: the role branches below are then
+  // uniform control flow, the TMA / MMA operands (descriptors, barrier addresses, coordinates) live in uniform registers and
+  // the one-lane issue is an `elect.sync` predicate - with a divergent `lane == 0` branch every UTMALDG / UTCHMMA sat in
+  // its own ELECT / R2UR waterfall loop (~20-40 issue slots per MMA on the single issuing thread)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int rank = PAIR ? __shfl_sync(0xffffffffu, (int)cluster_ctarank(), 0) : 0;  // 0 = leader of the CTA pair (issues the MMAs)
   const int tile0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;   // persistent walk over (pair) tiles
   const int tile_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
@@ -312,8 +316,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer (whole warp walks the loop, one elected lane issues) =====
+    {
       int s = 0;
       uint32_t ph = 0;
       long long prof_wait = 0;
@@ -329,29 +333,32 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             mbar_wait(empty_bar + s, ph ^ 1u);
             if (kProf && a.prof) prof_wait += clock64() - t0;
             unsigned char* sa = smem + (size_t)s * stage_bytes;
-            if constexpr (!PAIR) {
-              mbar_expect_tx(full_bar + s, stage_bytes);
-              tma_load_4d(sa, &tmap_a, full_bar + s, cb * a.kbk, ax, ay, tc.n0);
-              tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * a.kbk, tc.co0, tap.wtap, nw);
-            } else {
-              // both CTAs load into their OWN shared memory and complete the bytes on the LEADER's barrier, which the
-              // leader arms for the whole pair (a complete_tx that overtakes the expect_tx only drives the count negative)
-              if (rank == 0) mbar_expect_tx(full_bar + s, 2u * stage_bytes);
-              const uint32_t lead_bar = mapa_u32(full_bar + s, 0);
-              tma_load_4d_2cta(sa, &tmap_a, lead_bar, cb * a.kbk, ax, ay, tc.n0);
-              tma_load_4d_2cta(sa + a.pix_bytes, &tmap_b, lead_bar, cb * a.kbk, tc.co0 + co_half, tap.wtap, nw);
+            if (elect_one()) {
+              if constexpr (!PAIR) {
+                mbar_expect_tx(full_bar + s, stage_bytes);
+                tma_load_4d(sa, &tmap_a, full_bar + s, cb * a.kbk, ax, ay, tc.n0);
+                tma_load_4d(sa + a.pix_bytes, &tmap_b, full_bar + s, cb * a.kbk, tc.co0, tap.wtap, nw);
+              } else {
+                // both CTAs load into their OWN shared memory and complete the bytes on the LEADER's barrier, which the
+                // leader arms for the whole pair (a complete_tx that overtakes the expect_tx only drives the count negative)
+                if (rank == 0) mbar_expect_tx(full_bar + s, 2u * stage_bytes);
+                const uint32_t lead_bar = mapa_u32(full_bar + s, 0);
+                tma_load_4d_2cta(sa, &tmap_a, lead_bar, cb * a.kbk, ax, ay, tc.n0);
+                tma_load_4d_2cta(sa + a.pix_bytes, &tmap_b, lead_bar, cb * a.kbk, tc.co0 + co_half, tap.wtap, nw);
+              }
             }
+            __syncwarp();
             if (++s == a.stages) { s = 0; ph ^= 1u; }
           }
         }
       }
 #if VCN_CONV_PROF
-      if (a.prof) atomicAdd(&g_conv_prof[5], (unsigned long long)prof_wait);
+      if (a.prof && lane == 0) atomicAdd(&g_conv_prof[5], (unsigned long long)prof_wait);
 #endif
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0 && rank == 0) {  // pair mode: the leader issues for both CTAs
+    if (rank == 0) {  // pair mode: the leader issues for both CTAs; the whole warp walks the loop, one elected lane issues
       const int acc_cols = a.swap ? 256 : a.n_tile;
       const uint32_t idesc = a.tf32 ? umma_idesc_tf32_f32(PAIR ? 2 * kBlockM : kBlockM, acc_cols)
                                     : umma_idesc_bf16_f32(PAIR ? 2 * kBlockM : kBlockM, acc_cols);
@@ -377,28 +384,37 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
           const uint64_t dpix = umma_desc_k_sw128(sa), dwt = umma_desc_k_sw128(sa + a.pix_bytes);
           const uint64_t da = a.swap ? dwt : dpix, db = a.swap ? dpix : dwt;
-#pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          if (elect_one()) {
             // advancing K inside the swizzle span = +32 bytes on the start address (>>4 encoded)
             // one MMA = 32 bytes of K per row: 16 bf16 or 8 tf32 channels
-            const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
-            if constexpr (PAIR) {
-              if (a.tf32) umma_tf32_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
-              else umma_bf16_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+            if (a.tf32) {
+#pragma unroll
+              for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
+                if constexpr (PAIR) umma_tf32_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+                else umma_tf32_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+              }
             } else {
-              if (a.tf32) umma_tf32_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
-              else umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+#pragma unroll
+              for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                const uint32_t acc = (kb > 0 || k > 0) ? 1u : 0u;
+                if constexpr (PAIR) umma_bf16_ss_2cta(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+                else umma_bf16_ss(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, acc);
+              }
+            }
+            if constexpr (PAIR) umma_commit_2cta(empty_bar + s, 3);  // frees stage s in BOTH CTAs
+            else umma_commit(empty_bar + s);
+            if (kb == num_kb - 1) {  // accumulator ready (pair: both CTAs' epilogues)
+              if constexpr (PAIR) umma_commit_2cta(tmem_full_bar + as, 3);
+              else umma_commit(tmem_full_bar + as);
             }
           }
-          if constexpr (PAIR) umma_commit_2cta(empty_bar + s, 3);  // frees stage s in BOTH CTAs
-          else umma_commit(empty_bar + s);
+          __syncwarp();
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
-        if constexpr (PAIR) umma_commit_2cta(tmem_full_bar + as, 3);  // accumulator ready: both CTAs' epilogues
-        else umma_commit(tmem_full_bar + as);
       }
 #if VCN_CONV_PROF
-      if (a.prof) {
+      if (a.prof && lane == 0) {
         atomicAdd(&g_conv_prof[2], (unsigned long long)prof_acc);
         atomicAdd(&g_conv_prof[3], (unsigned long long)prof_ops);
         atomicAdd(&g_conv_prof[6], (unsigned long long)prof_kb);
@@ -840,8 +856,18 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
       if (rc) return rc;
     }
   }
-  if (a.pair) VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  else VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  {
+    // opt in to the full dynamic shared-memory carve-out ONCE per device and kernel instead of on every launch
+    static bool smem_set[2][64] = {};
+    int dev = 0;
+    VCN_CUDA(cudaGetDevice(&dev));
+    const int p = a.pair ? 1 : 0;
+    if (dev < 0 || dev >= 64 || !smem_set[p][dev]) {
+      if (a.pair) VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+      else VCN_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+      if (dev >= 0 && dev < 64) smem_set[p][dev] = true;
+    }
+  }
   if (!a.pair) {
     int grid = sm_count();
     if (grid > a.tiles_total) grid = a.tiles_total;

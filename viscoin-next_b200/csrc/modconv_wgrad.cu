@@ -76,7 +76,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   uint64_t* tmem_full_bar = empty_bar + a.stages;  // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;    // [2]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // shuffled so that the compiler knows the role branches are warp-uniform (see conv_igemm_kernel): TMA / MMA operands stay
+  // in uniform registers and the one-lane issue is an elect.sync predicate instead of per-instruction waterfall loops
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
   const int units = a.taps * a.tiles_co * a.tiles_ci * a.splits;
   const int tiles_x = (a.pix_w + a.tw - 1) / a.tw, tiles_y = (a.pix_h + a.th - 1) / a.th;
 
@@ -94,8 +96,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer (whole warp walks the loop, one elected lane issues) =====
+    {
       int s = 0;
       uint32_t ph = 0;
       for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -109,18 +111,21 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           else { ax = 2 * x0 + kx; ay = 2 * y0 + ky; bx = x0; by = y0; }
           mbar_wait(empty_bar + s, ph ^ 1u);
           unsigned char* sa = smem + (size_t)s * stage_bytes;
-          mbar_expect_tx(full_bar + s, stage_bytes);
-          tma_load_4d(sa, &tmap_a, full_bar + s, w.co0, ax, ay, n);
-          tma_load_4d(sa + kBoxBytes, &tmap_a, full_bar + s, w.co0 + 64, ax, ay, n);
-          for (int j = 0; j < a.n_tile / 64; ++j)
-            tma_load_4d(sa + a_bytes + j * kBoxBytes, &tmap_b, full_bar + s, w.ci0 + 64 * j, bx, by, n);
+          if (elect_one()) {
+            mbar_expect_tx(full_bar + s, stage_bytes);
+            tma_load_4d(sa, &tmap_a, full_bar + s, w.co0, ax, ay, n);
+            tma_load_4d(sa + kBoxBytes, &tmap_a, full_bar + s, w.co0 + 64, ax, ay, n);
+            for (int j = 0; j < a.n_tile / 64; ++j)
+              tma_load_4d(sa + a_bytes + j * kBoxBytes, &tmap_b, full_bar + s, w.ci0 + 64 * j, bx, by, n);
+          }
+          __syncwarp();
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer (whole warp walks the loop, one elected lane issues) =====
+    {
       const uint32_t idesc = umma_idesc_bf16_f32(128, a.n_tile) | (1u << 15) | (1u << 16);  // A and B MN-major
       int s = 0, it = 0;
       uint32_t ph = 0;
@@ -134,17 +139,21 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(full_bar + s, ph);
           tcgen05_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kKPix / 16; ++k) {
-            // 16 pixels further along K = 16 rows of 128 bytes
-            const uint64_t da = umma_desc_mn_sw128(sa + k * 2048u, kBoxBytes);
-            const uint64_t db = umma_desc_mn_sw128(sa + a_bytes + k * 2048u, kBoxBytes);
-            umma_bf16_ss(d_tmem, da, db, idesc, (kb > w.kb0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < kKPix / 16; ++k) {
+              // 16 pixels further along K = 16 rows of 128 bytes
+              const uint64_t da = umma_desc_mn_sw128(sa + k * 2048u, kBoxBytes);
+              const uint64_t db = umma_desc_mn_sw128(sa + a_bytes + k * 2048u, kBoxBytes);
+              umma_bf16_ss(d_tmem, da, db, idesc, (kb > w.kb0 || k > 0) ? 1u : 0u);
+            }
+            umma_commit(empty_bar + s);
           }
-          umma_commit(empty_bar + s);
+          __syncwarp();
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
-        umma_commit(tmem_full_bar + as);
+        if (elect_one()) umma_commit(tmem_full_bar + as);
+        __syncwarp();
       }
     }
   } else {

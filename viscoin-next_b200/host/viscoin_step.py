@@ -167,7 +167,7 @@ class VisCoINTrainer:
         gan_params = list(self.viscoin_gan.mapping.parameters())
         main_params = list(itertools.chain(self.concept_extractor.parameters(), self.explainer.parameters()))
         # backward reaches the mapping network before Psi: register in forward order, buckets fill in reverse
-        self.buckets = _dp.GradBuckets(main_params + gan_params)
+        self.buckets = _dp.GradBuckets(main_params + gan_params, bucket_bytes=int(os.environ.get("VCN_DP_BUCKET_MB", "32")) << 20)
         fused = (self.device.type == "cuda") if fused_adam is None else fused_adam
         # capturable: step counters and lr live on the device, so the update can sit inside a CUDA graph (step_graphed)
         cap = fused and self.device.type == "cuda"
@@ -175,6 +175,8 @@ class VisCoINTrainer:
         self.gan_optimizer = torch.optim.Adam(gan_params, lr=lr, fused=fused, capturable=cap)
         self.optimizer = torch.optim.Adam(main_params, lr=lr, fused=fused, capturable=cap)
         self._graphs = {}
+        self._z_ahead = {}  # per graph key: the z already drawn for the next iteration (step_graphed's generator pipelining)
+        self.prefetch_fake = os.environ.get("VCN_PREFETCH_FAKE", "1") == "1"
         self.graph_launches = 0  # libvcn kernel launches replayed from graphs so far
         self._eager_calls = {}
 
@@ -240,10 +242,19 @@ class VisCoINTrainer:
         synthesis kernels with their tensor maps as kernel parameters, both Adam updates, the bucket memsets and - under
         torch.distributed - the NCCL all-reduces) are captured once per (batch size, i > cd_fid_iteration) and then cost
         one host call.  The first `warm` calls run eagerly (they fill the weight-pack caches and the allocator); z is
-        drawn on the host every call like utils.py:37 and copied into the graph's static input."""
+        drawn on the host every call like utils.py:37 and copied into the graph's static input.
+
+        Software pipelining of the frozen generator (``self.prefetch_fake``): `synthetic_samples` depends on nothing the
+        step updates (generator_gan is frozen, viscoin.py:116,163-166), so the graph generates the fake images of the NEXT
+        iteration right after backward - under the tail of the gradient all-reduce, whose last buckets (Psi's convolutions)
+        only become final with the last backward kernels - and this iteration consumes the batch the previous replay left
+        in a static buffer.  The z stream is unchanged: iteration k still sees the k-th draw of `z_generator`; the draw for
+        iteration k+1 just happens one call earlier."""
         n = len(real_images)
         key = (n, i > self.p.cd_fid_iteration)
-        z = torch.randn(n, self.generator_gan.z_dim, generator=z_generator)
+        z = self._z_ahead.pop(key, None)
+        if z is None:
+            z = torch.randn(n, self.generator_gan.z_dim, generator=z_generator)
         if self._eager_calls.get(key, 0) < warm and key not in self._graphs:
             # eager warm-up on a SIDE stream (per graph key: every branch a capture will record has run eagerly first):
             # autograd binds each parameter's gradient accumulator to the stream it first runs on, and the legacy default
@@ -265,29 +276,50 @@ class VisCoINTrainer:
                   "labels": torch.empty(labels.shape, dtype=labels.dtype, device=self.device),
                   "z": torch.empty(n, self.generator_gan.z_dim, device=self.device)}
             st["real"].copy_(real_images); st["labels"].copy_(labels); st["z"].copy_(z)
+            st["prefetch"] = bool(self.prefetch_fake)
+            if st["prefetch"]:  # this iteration's batch, generated eagerly once; every replay leaves the next one here
+                with torch.no_grad():
+                    st["fake"] = self.generator_gan(st["z"], None).clone()
             torch.cuda.synchronize(self.device)
             count0 = _lib.load().vcn_launch_count()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                with torch.no_grad():
-                    fake = self.generator_gan(st["z"], None)
-                st["out"] = self.step(st["real"], st["labels"], i, fake_images=fake)
+                if st["prefetch"]:
+                    def next_fakes():
+                        with torch.no_grad():
+                            st["fake"].copy_(self.generator_gan(st["z"], None))
+                    st["out"] = self.step(st["real"], st["labels"], i, fake_images=st["fake"], _after_backward=next_fakes)
+                else:
+                    with torch.no_grad():
+                        fake = self.generator_gan(st["z"], None)
+                    st["out"] = self.step(st["real"], st["labels"], i, fake_images=fake)
             st["graph"] = graph
             st["launches"] = int(_lib.load().vcn_launch_count() - count0)  # libvcn kernels per replay
             self._graphs[key] = st
+            if st["prefetch"]:
+                # the capture does not execute: st["fake"] still holds G(z) of THIS iteration; fall through to the replay,
+                # which consumes it and generates the next one from the z drawn below
+                pass
         st = self._graphs[key]
         st["real"].copy_(real_images, non_blocking=True)
         st["labels"].copy_(labels, non_blocking=True)
+        if st["prefetch"]:
+            z = torch.randn(n, self.generator_gan.z_dim, generator=z_generator)  # iteration k+1's draw
+            self._z_ahead[key] = z
         st["z"].copy_(z, non_blocking=True)
         st["graph"].replay()
         self.graph_launches += st["launches"]
         return st["out"]
 
-    def step(self, real_images, labels, i=1000, fake_images=None, z_generator=None):
-        """One iteration (gradient_accumulation = 1).  Returns the dict of detached loss terms + 'total'."""
+    def step(self, real_images, labels, i=1000, fake_images=None, z_generator=None, _after_backward=None):
+        """One iteration (gradient_accumulation = 1).  Returns the dict of detached loss terms + 'total'.
+        `_after_backward` (step_graphed): work that is independent of this step's update, issued between the last
+        backward kernel and the wait on the gradient exchange so that it runs under the all-reduce tail."""
         losses = self.forward_losses(real_images, labels, i, fake_images, z_generator)
         total = sum(losses.values())
         total.backward()
+        if _after_backward is not None:
+            _after_backward()
         self.buckets.finish()
         self.optimizer.step()
         self.gan_optimizer.step()
