@@ -178,6 +178,15 @@ __device__ __forceinline__ void tma_load_4d_2cta(void* dst, const CUtensorMap* m
       : "memory");
 }
 
+// 1-D bulk copy global -> shared through the TMA engine (no tensor map): 16-byte aligned addresses, size a multiple of 16;
+// completes `bytes` on the mbarrier.
+__device__ __forceinline__ void bulk_load_1d(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }

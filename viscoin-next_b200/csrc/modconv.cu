@@ -652,7 +652,7 @@ int64_t choose_pair_tile(int gw, int gh, int n, int one_sample, int max_w, int* 
 
 // environment switches (experiments), read ONCE per process - never on the launch path
 struct ConvEnv {
-  int swap = -1;   // VCN_CONV_SWAP: 0 never, 2 also for the transposed conv, unset = policy
+  int swap = -1;   // VCN_CONV_SWAP: 0 never, 1 not for the transposed conv, unset = policy
   int stage = -1;  // VCN_CONV_STAGE: 0 = no TMA-store epilogue
   int pair = -1;   // VCN_CONV_PAIR: 0 never, 2 = every tile of >= 64 out channels, unset = policy (n_tile == 256)
   int prof = 0;    // VCN_CONV_PROFILE (only meaningful in -DVCN_CONV_PROF=1 builds)
@@ -740,13 +740,12 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
   // Operand swap (UMMA M = out channels, N = 256 pixels) for 65..128 out channels and a channels-fastest output: a
   // 128 x 128 tile pulls 1/64 byte of operands per flop through TMA, a 128 x 256 tile 1/85 - and the measured ceiling
   // of this kernel is the ~50 B/clk an SM ingests from L2, not the tensor pipe.
-  // Not for the transposed conv: its phase tiles carry 1..4 taps only (9 k-blocks per tile on average at 256 channels), the
-  // tile is epilogue-bound either way and the swapped epilogue costs 1.7x per pixel (measured: 0.168 ms vs 0.131 ms).
+  // Also for the transposed conv (256 -> 128 at 128^2: 0.104 ms swapped vs 0.110 ms; profiles/r2i_rooflines_conv_policy.txt) -
+  // with the waterfall issue loops of round 1 the swapped form lost there (0.168 vs 0.131 ms).
   const ConvEnv& env = conv_env();
-  a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256 && d->kind != VCN_CONV_TCONV2;
-  if (env.swap >= 0) {  // 0: never, 2: also for the transposed conv (experiments)
-    const bool base = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256;
-    a.swap = env.swap == 2 ? base : (a.swap && env.swap != 0);
+  a.swap = d->cout > 64 && d->cout <= 128 && d->ys[1] == 1 && (int64_t)a.grid_w * a.grid_h >= 256;
+  if (env.swap >= 0) {  // 0: never, 1: not for the transposed conv (experiments)
+    a.swap = a.swap && env.swap != 0 && !(env.swap == 1 && d->kind == VCN_CONV_TCONV2);
   }
   // two accumulator stages of n_tile fp32 columns each must fit the 512 TMEM columns
   a.n_tile = (d->cout + 15) / 16 * 16;

@@ -189,9 +189,153 @@ __global__ void __launch_bounds__(256, FINISH ? 4 : (FAST ? 3 : 2)) modconv_bwd_
   if (!FINISH && a.sum_c) group_reduce_add(red, acc1, tid, groups, rows, a.sum_c, a.c);
 }
 
+// ---- bulk-copy staged variant (dense NHWC, full channel groups, homogeneous activation) ----------------------------------
+// The register-staged kernel above keeps 3 CTAs x 256 threads x 2 x 2 16-byte loads = 49 KB in flight per SM - about what HBM3e
+// needs at its loaded latency, hence 0.55 (pack) / 0.73 (finish) of the copy peak.  Here the TMA engine streams both input
+// tensors into a shared-memory ring (cp.async.bulk, 16 KB per stage, kStagesBulk stages per CTA, 3 CTAs per SM = 192 KB in
+// flight per SM, no registers spent on it); the threads read their 16-byte vectors from the ring, do the same arithmetic and
+// write the result straight to global memory.  A stage = 2 * rows consecutive pixels of one sample (contiguous in NHWC).
+constexpr int kStagesBulk = 4;
+constexpr uint32_t kStageTensorBytes = 8192;  // per tensor and stage: 2 pixels per thread x 256 threads x 16 bytes
+
+template <typename T, bool FINISH>
+__global__ void __launch_bounds__(256, 3) modconv_bwd_cl_bulk_kernel(const BwdClArgs a) {
+  extern __shared__ __align__(128) unsigned char ring[];  // [kStagesBulk][2][kStageTensorBytes]
+  __shared__ float red[256][8];
+  __shared__ __align__(8) uint64_t full_bar[kStagesBulk];
+  const int tid = threadIdx.x, n = blockIdx.y;
+  const int groups = a.c_pad >> 3;  // power of two <= 256 (host-checked)
+  const int rows = 256 / groups;
+  const int g = tid % groups, row = tid / groups;
+  const int c = g * 8;
+  const int hw = a.h * a.w;
+  const int p0 = blockIdx.x * a.chunk, p_end = min(hw, p0 + a.chunk);
+  const int sp = 2 * rows;  // pixels per stage
+  const int nit = (p_end - p0 + sp - 1) / sp;
+  const uint32_t row_bytes = (uint32_t)a.c_pad * 2u;
+  const bool two = a.y != nullptr;
+  const unsigned char* ga = static_cast<const unsigned char*>(a.dy) + ((int64_t)n * hw + p0) * row_bytes;
+  const unsigned char* gb = two ? static_cast<const unsigned char*>(a.y) + ((int64_t)n * hw + p0) * row_bytes : nullptr;
+
+  auto fill = [&](int it) {  // one elected thread: arm the barrier, start the copies of stage `it`
+    const int s = it % kStagesBulk;
+    const int px = min(sp, p_end - p0 - it * sp);
+    const uint32_t bytes = (uint32_t)px * row_bytes;
+    unsigned char* dst = ring + (size_t)s * 2 * kStageTensorBytes;
+    mbar_expect_tx(full_bar + s, two ? 2u * bytes : bytes);
+    bulk_load_1d(dst, ga + (int64_t)it * sp * row_bytes, bytes, full_bar + s);
+    if (two) bulk_load_1d(dst + kStageTensorBytes, gb + (int64_t)it * sp * row_bytes, bytes, full_bar + s);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kStagesBulk; ++s) mbar_init(full_bar + s, 1);
+    fence_mbar_init();
+    for (int it = 0; it < min(nit, kStagesBulk); ++it) fill(it);
+  }
+  float sc[8], bi[8], acc0[8], acc1[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sc[k] = a.scale ? a.scale[(int64_t)n * a.c + c + k] : 1.f;
+    bi[k] = (!FINISH && a.bias && a.act) ? a.bias[c + k] : 0.f;
+    acc0[k] = acc1[k] = 0.f;
+  }
+  const float* noise_n = (!FINISH && a.noise) ? a.noise + (int64_t)n * a.noise_stride_n : nullptr;
+  const bool has_clamp = !FINISH && a.clamp >= 0.f;
+  __syncthreads();  // barrier inits visible
+  for (int it = 0; it < nit; ++it) {
+    const int s = it % kStagesBulk;
+    mbar_wait(full_bar + s, (uint32_t)(it / kStagesBulk) & 1u);
+    const unsigned char* sa = ring + (size_t)s * 2 * kStageTensorBytes;
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int pl = row + b * rows;         // pixel inside the stage
+      const int p = p0 + it * sp + pl;       // pixel inside the sample
+      if (p < p_end) {
+        const Vec16<T> ru = *reinterpret_cast<const Vec16<T>*>(sa + (size_t)pl * row_bytes + g * 16);
+        Vec16<T> rv;
+        if (two) rv = *reinterpret_cast<const Vec16<T>*>(sa + kStageTensorBytes + (size_t)pl * row_bytes + g * 16);
+        Vec16<__nv_bfloat16> o;
+        if (FINISH) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float u = to_acc<T>(ru.v[k]);
+            if (two) acc0[k] = fmaf(u, to_acc<T>(rv.v[k]), acc0[k]);
+            o.v[k] = __float2bfloat16_rn(u * sc[k]);
+          }
+          // in place: this pixel of dxhat has already been copied into the ring
+          *reinterpret_cast<Vec16<__nv_bfloat16>*>(const_cast<unsigned char*>(ga) + ((int64_t)it * sp + pl) * row_bytes + g * 16) = o;
+        } else {
+          const float nz = noise_n ? __ldg(noise_n + p) : 0.f;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const float u = to_acc<T>(ru.v[k]), v = two ? to_acc<T>(rv.v[k]) : 0.f;
+            const bool pos = v > 0.f;
+            float dz = u * (pos ? a.g : a.ag);
+            if (has_clamp) dz = fabsf(v) < a.clamp ? dz : 0.f;
+            const float r = fmaf(v, pos ? a.cr_pos : a.cr_neg, -(bi[k] + nz));
+            acc0[k] = fmaf(dz, r, acc0[k]);
+            acc1[k] += dz;
+            o.v[k] = __float2bfloat16_rn(dz * sc[k]);
+          }
+          st_stream<__nv_bfloat16>(a.out + ((int64_t)n * hw + p) * a.c_pad + c, o);
+        }
+      }
+    }
+    __syncthreads();  // every thread has read stage s
+    if (tid == 0 && it + kStagesBulk < nit) {
+      fence_proxy_async();  // the generic-proxy reads above are ordered before the async-proxy refill
+      fill(it + kStagesBulk);
+    }
+  }
+  if (a.sum_nc) group_reduce_add(red, acc0, tid, groups, rows, a.sum_nc + (int64_t)n * a.c, a.c);
+  if (!FINISH && a.sum_c) group_reduce_add(red, acc1, tid, groups, rows, a.sum_c, a.c);
+}
+
+// dense [n,h,w,c_pad] 16-bit tensor with c == c_pad, 16-byte aligned
+inline bool dense_nhwc(const void* p, const int64_t s[4], int c, int c_pad, int h, int w) {
+  return c == c_pad && s[1] == 1 && s[3] == c_pad && s[2] == (int64_t)w * c_pad && s[0] == (int64_t)h * w * c_pad &&
+         (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
+
+template <bool FINISH>
+int launch_bulk(BwdClArgs& a, int dtype, cudaStream_t st, const char* name) {
+  const int hw = a.h * a.w;
+  const int rows = 256 / (a.c_pad >> 3);
+  const int sp = 2 * rows;
+  // one wave of 3 CTAs per SM, every CTA a whole number of stages
+  int per_sample = (sm_count() * 3) / a.n;
+  if (per_sample < 1) per_sample = 1;
+  int chunk = (hw + per_sample - 1) / per_sample;
+  chunk = (chunk + sp - 1) / sp * sp;
+  if (chunk < 4 * sp) chunk = 4 * sp;
+  a.chunk = chunk;
+  dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)a.n);
+  const size_t smem = (size_t)kStagesBulk * 2 * kStageTensorBytes;
+  static bool attr_set[2][2][64] = {};
+  int dev = 0;
+  VCN_CUDA(cudaGetDevice(&dev));
+  const int ti = dtype == VCN_BF16 ? 0 : 1;
+  auto kern = dtype == VCN_BF16 ? modconv_bwd_cl_bulk_kernel<__nv_bfloat16, FINISH> : modconv_bwd_cl_bulk_kernel<__half, FINISH>;
+  if (dev < 0 || dev >= 64 || !attr_set[FINISH ? 1 : 0][ti][dev]) {
+    VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 64) attr_set[FINISH ? 1 : 0][ti][dev] = true;
+  }
+  kern<<<grid, 256, smem, st>>>(a);
+  VCN_LAUNCH_CHECK(name);
+  return VCN_OK;
+}
+
 template <bool FINISH>
 int launch(BwdClArgs& a, int dtype, cudaStream_t st, const char* name) {
   const int hw = a.h * a.w;
+  {
+    // bulk-copy staged kernel: dense tensors, power-of-two channel count, the homogeneous activation form, enough pixels
+    static const bool allow = [] { const char* e = getenv("VCN_BWD_CL_BULK"); return !e || atoi(e) != 0; }();
+    const int groups = a.c_pad >> 3;
+    const bool pow2 = groups >= 1 && groups <= 256 && (groups & (groups - 1)) == 0;
+    if (allow && pow2 && (FINISH || a.fast_act) && dense_nhwc(a.dy, a.as, a.c, a.c_pad, a.h, a.w) &&
+        (!a.y || dense_nhwc(a.y, a.bs, a.c, a.c_pad, a.h, a.w)) && (int64_t)a.n * hw * a.c_pad >= (1 << 21))
+      return launch_bulk<FINISH>(a, dtype, st, name);
+  }
   const int rows = 256 / (a.c_pad >> 3);
   // about 16 CTAs per SM in total, at least 32 pixel iterations each
   int chunk = hw;

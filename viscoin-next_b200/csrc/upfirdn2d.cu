@@ -307,6 +307,9 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
   const int tile_ox = cur.bx * g.tw, tile_oy = cur.by * g.th;
   const int plane0 = cur.bp * g.tp;
   cur = nxt;
+  // register-staged tiles may use fewer than blockDim.x compute threads (balanced tiles of a 2^k+1 output): the rest only
+  // help with the staging
+  if (tid < g.tx * g.ty * g.tp) {
   const T* wbase = tile + ((size_t)t_p * g.ih + (ry * DOWN) / UP) * g.iwp + (rx * DOWN) / UP;
 
   S acc[kMR][MC];
@@ -392,6 +395,7 @@ upfirdn2d_tile_kernel(const UpfirdnArgs a, const TileGeom g, const __grid_consta
     }
   }
   }
+  }
   __syncthreads();  // buffer b is free for the tile after next
   if constexpr (STG != 0) {
     if (has_next) stash();
@@ -413,7 +417,8 @@ constexpr int kClTx = 32, kClTy = 16, kClCb = 64;
 
 template <typename T, typename TO>
 __global__ void __launch_bounds__(256, 2)
-upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y) {
+upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y,
+                    const int ncb) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int HX = kClTx + kF - 1, HY = kClTy + kF - 1;
   T* tile = reinterpret_cast<T*>(smem_raw);                                   // [HY][HX][64]
@@ -421,11 +426,14 @@ upfirdn2d_cl_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tma
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_par + 2 * kClCb + kF * kF);
 
   const int tid = threadIdx.x;
+  // channel block fastest: the CTAs that read the two 128-byte halves of the same 256-byte L2 line (TMA promotes every
+  // request to 256 bytes) run at the same time - with the channel block as the SLOWEST index the promoted half was fetched
+  // from DRAM a second time one whole tensor pass later (ncu: 1.49x read amplification on [8,128,257,257])
   int bid = blockIdx.x;
+  const int c0 = (bid % ncb) * kClCb; bid /= ncb;
   const int bx = bid % tiles_x; bid /= tiles_x;
   const int by = bid % tiles_y;
   const int n = bid / tiles_y;
-  const int c0 = blockIdx.y * kClCb;
   const int ox0 = bx * kClTx, oy0 = by * kClTy;
 
   if (tid == 0) {
@@ -639,7 +647,8 @@ __device__ __forceinline__ void cl_emit_packed(const UpfirdnArgs& a, const uint6
 
 template <typename T, typename TO, int EPI>
 __global__ void __launch_bounds__(256, 2)
-upfirdn2d_cl_sep_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y) {
+upfirdn2d_cl_sep_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap tmap, const int tiles_x, const int tiles_y,
+                        const int ncb) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int HX = kClTx + kF - 1, HY = kClTy + kF - 1;
   constexpr int RT = kClTy / 2;  // output rows per thread
@@ -648,11 +657,14 @@ upfirdn2d_cl_sep_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_par + 2 * kClCb + kF * kF);
 
   const int tid = threadIdx.x;
+  // channel block fastest: the CTAs that read the two 128-byte halves of the same 256-byte L2 line (TMA promotes every
+  // request to 256 bytes) run at the same time - with the channel block as the SLOWEST index the promoted half was fetched
+  // from DRAM a second time one whole tensor pass later (ncu: 1.49x read amplification on [8,128,257,257])
   int bid = blockIdx.x;
+  const int c0 = (bid % ncb) * kClCb; bid /= ncb;
   const int bx = bid % tiles_x; bid /= tiles_x;
   const int by = bid % tiles_y;
   const int n = bid / tiles_y;
-  const int c0 = blockIdx.y * kClCb;
   const int ox0 = bx * kClTx, oy0 = by * kClTy;
 
   const float epi_g = (EPI == 1 && a.act) ? a.act_gain : 1.f;  // EPI 1 folds the activation gain into scale / bias / noise
@@ -795,10 +807,11 @@ upfirdn2d_cl_sep_kernel(const UpfirdnArgs a, const __grid_constant__ CUtensorMap
 }
 
 template <typename T, typename TO, int EPI>
-int launch_cl_sep(const UpfirdnArgs& a, const CUtensorMap& tmap, dim3 grid, size_t smem, int tiles_x, int tiles_y, cudaStream_t st) {
+int launch_cl_sep(const UpfirdnArgs& a, const CUtensorMap& tmap, dim3 grid, size_t smem, int tiles_x, int tiles_y, int ncb,
+                  cudaStream_t st) {
   auto kern = upfirdn2d_cl_sep_kernel<T, TO, EPI>;
   VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
+  kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y, ncb);
   VCN_LAUNCH_CHECK("upfirdn2d_cl_sep_kernel");
   return VCN_OK;
 }
@@ -821,24 +834,26 @@ int try_launch_cl(const UpfirdnArgs& a, int dtype, int y_dtype, cudaStream_t st)
   if (rc) return rc;
   const int tiles_x = (a.out_w + kClTx - 1) / kClTx, tiles_y = (a.out_h + kClTy - 1) / kClTy;
   const size_t smem = (size_t)(kClTy + kF - 1) * (kClTx + kF - 1) * kClCb * 2 + (2 * kClCb + kF * kF) * sizeof(float) + 16;
-  dim3 grid((unsigned)((int64_t)tiles_x * tiles_y * a.n), (unsigned)((a.c + kClCb - 1) / kClCb));
+  const int ncb = (a.c + kClCb - 1) / kClCb;
+  if ((int64_t)tiles_x * tiles_y * a.n * ncb > 0x7fffffffLL) return -1;
+  dim3 grid((unsigned)((int64_t)tiles_x * tiles_y * a.n * ncb), 1u);
   static const bool use_sep = [] { const char* e = getenv("VCN_FIR_CL_SEP"); return !e || atoi(e) != 0; }();
   if constexpr (sizeof(T) == 2) {
     if (use_sep && y_dtype != VCN_F32) {
-      if (!a.scale && !a.noise && !a.act) return launch_cl_sep<T, T, 0>(a, tmap, grid, smem, tiles_x, tiles_y, st);
+      if (!a.scale && !a.noise && !a.act) return launch_cl_sep<T, T, 0>(a, tmap, grid, smem, tiles_x, tiles_y, ncb, st);
       const bool homog = a.act == 0 || (a.act_gain > 0.f && (a.act == VCN_ACT_LINEAR || (a.act == VCN_ACT_LRELU && a.alpha >= 0.f && a.alpha <= 1.f)));
-      if (homog) return launch_cl_sep<T, T, 1>(a, tmap, grid, smem, tiles_x, tiles_y, st);
-      return launch_cl_sep<T, T, 2>(a, tmap, grid, smem, tiles_x, tiles_y, st);
+      if (homog) return launch_cl_sep<T, T, 1>(a, tmap, grid, smem, tiles_x, tiles_y, ncb, st);
+      return launch_cl_sep<T, T, 2>(a, tmap, grid, smem, tiles_x, tiles_y, ncb, st);
     }
   }
   if (y_dtype == VCN_F32) {
     auto kern = upfirdn2d_cl_kernel<T, float>;
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
+    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y, ncb);
   } else {
     auto kern = upfirdn2d_cl_kernel<T, T>;
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y);
+    kern<<<grid, 256, smem, st>>>(a, tmap, tiles_x, tiles_y, ncb);
   }
   VCN_LAUNCH_CHECK("upfirdn2d_cl_kernel");
   return VCN_OK;
@@ -1035,6 +1050,22 @@ TileGeom make_geom(const UpfirdnArgs& a, int up, int down) {
   g.th = pow2_ceil(a.out_h); if (g.th < kMR) g.th = kMR;
   if (g.th > kMR * ty_cap) g.th = kMR * ty_cap;
   g.ty = g.th / kMR;
+  // Balanced tiles for fp32 outputs just above a multiple of the power-of-two tile (the 2^k+1 transposed-conv intermediate
+  // as an OUTPUT: pattern A', the backward of the FIR after the up-sampling convolution): 257 = 3 x 88 columns and 6 x 44
+  // rows = 18 nearly full tiles per plane instead of 3 x 9 = 27 tiles of 128 x 32 of which 11 carry one row or column.
+  // Sized for the register-staged path STG 2 (<= 72 staged rows x 96 columns).
+  if (sizeof(T) == 4 && up == 1 && down == 1 && a.out_w > tw_cap && a.out_h > 64) {
+    const int cur_tiles = ((a.out_w + g.tw - 1) / g.tw) * ((a.out_h + g.th - 1) / g.th);
+    const int nx = (a.out_w + 87) / 88;
+    const int bw = ((a.out_w + nx - 1) / nx + MC - 1) / MC * MC;        // <= 88
+    const int btx = bw / MC;
+    int bty = max_threads / btx; if (bty > 17) bty = 17;                 // 17 * 4 + 3 = 71 staged rows
+    const int ny = (a.out_h + kMR * bty - 1) / (kMR * bty);
+    const int bh = ((a.out_h + ny - 1) / ny + kMR - 1) / kMR * kMR;
+    if (nx * ny * 5 <= cur_tiles * 4 && btx * (bh / kMR) >= 192) {  // at least 20 % fewer tiles, most threads computing
+      g.tw = bw; g.tx = btx; g.th = bh; g.ty = bh / kMR;
+    }
+  }
   g.tp = max_threads / (g.tx * g.ty);
   const int planes = a.n * a.c;
   while (g.tp > 1 && g.tp / 2 >= planes && g.tx * g.ty * (g.tp / 2) >= 32) g.tp /= 2;
@@ -1081,7 +1112,7 @@ int launch_tile_epi(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st
   if (!g.use_tma && e == 4 && g.iwp > 160) { set_error("upfirdn2d: staged pitch %d exceeds the cp.async path", g.iwp); return VCN_ERR_UNSUPPORTED; }
   const size_t buf_bytes = ((size_t)g.tp * g.ih * g.iwp * e + 127) & ~(size_t)127;
   const size_t smem = 2 * buf_bytes + kF * kF * sizeof(float) + 16;
-  const bool reg_ok = kCanReg && !g.use_tma && g.tp == 1 && g.tx * g.ty == 256;
+  const bool reg_ok = kCanReg && !g.use_tma && g.tp == 1 && g.tx * g.ty <= 256 && g.tx * g.ty >= 192;
   const int reg_path = !reg_ok ? 0 : (g.ih <= 40 && g.iwp <= 160) ? 1 : (g.ih <= 72 && g.iwp <= 96) ? 2 : 0;
   const int64_t tiles = (int64_t)g.tiles_x * g.tiles_y * g.tiles_p;
   if (tiles > 0x7fffffffLL) { set_error("upfirdn2d: too many tiles"); return VCN_ERR_INVALID; }
