@@ -227,6 +227,12 @@ int vcn_lpips_tap_bwd(const void* fa, const void* fb, int dtype, const int64_t a
  *   vcn_maxpool2x2_relu_bwd  dz[n,h,w,c] = (gtap + U(gpool)) * (y > 0), U = max-pool backward (gradient to the first
  *                            maximum of the window in row-major scan order); gtap may be NULL */
 int vcn_maxpool2x2_fwd(const void* x, void* y, int dtype, int n, int h, int w, int c, void* stream);
+/* 3x3 / stride 2 / padding 1 max-pool of the ResNet stem (HF ResNetEmbeddings.pooler = torch.nn.MaxPool2d(3, 2, 1); the
+ * reference reaches it through transformers' ResNetModel, viscoin/models/classifiers.py:83-92): x [n,h,w,c] -> y [n,oh,ow,c],
+ * oh = (h-1)/2+1.  idx (may be NULL when no backward follows) = one byte per output element: the winning window position
+ * dy*3+dx, first maximum in scan order (ATen's max_pool2d_with_indices).  _bwd: gx [n,h,w,c] from gy [n,oh,ow,c] and idx. */
+int vcn_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int dtype, int n, int h, int w, int c, void* stream);
+int vcn_maxpool3x3s2_bwd(const void* gy, const void* idx, void* gx, int dtype, int n, int h, int w, int c, void* stream);
 int vcn_relu_mask_bwd(const void* y, const void* g, const void* g2, void* dz, int dtype, int64_t numel, void* stream);
 int vcn_maxpool2x2_relu_bwd(const void* y, const void* gpool, const void* gtap, void* dz, int dtype, int n, int h, int w, int c,
                             void* stream);

@@ -61,6 +61,23 @@ def test_maxpool_forward_and_fused_backward_bit_exact(shape):
     assert torch.equal(fz.relu_mask_bwd(y, gtap, g2), torch.where(y > 0, gtap + g2, torch.zeros_like(gtap)))
 
 
+@pytest.mark.parametrize("shape", [(2, 64, 32, 48), (3, 8, 7, 5), (1, 16, 1, 9), (2, 64, 128, 128)])
+def test_maxpool3x3s2_forward_and_backward_bit_exact(shape):
+    """MaxPool2d(3, 2, 1) of the ResNet stem (odd sizes, borders, exact ties): values and input gradient == ATen in bf16."""
+    fz = _fz()
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    x = _relu_like(shape, gen, ties=shape[2] % 2 == 0 and shape[3] % 2 == 0)
+    y_ref = F.max_pool2d(x, 3, 2, 1)
+    assert torch.equal(fz.maxpool3x3s2(x), y_ref)  # no-grad path (no index tensor)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ya, yb = fz.maxpool3x3s2(xa), F.max_pool2d(xb, 3, 2, 1)
+    assert torch.equal(ya, yb) and ya.is_contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(yb.shape, device="cuda", generator=gen).bfloat16().contiguous(memory_format=torch.channels_last)
+    ya.backward(gy)
+    yb.backward(gy)
+    assert torch.equal(xa.grad, xb.grad)
+
+
 def test_frozen_ops_reject_bad_arguments():
     import viscoin_next_b200 as V
     fz = _fz()

@@ -108,7 +108,31 @@ def collect(device, peaks, time_fn, iters=10, include_cudnn=True, n=8):
         3 * ycl.numel() * 2, key="modconv_bwd_cl_finish")
     hbm("modulate_pack_cl_rows_kernel<bf16> [%d,128,256,256] bf16 NHWC" % n2, lambda: M.modulate_pack(ycl, d), 2 * ycl.numel() * 2,
         key="modulate_pack_cl_rows_kernel")
-    del ycl, dycl, dxh, hold
+    del dxh, hold
+    # LPIPS tap (relu1_2 of VGG-16: 64 channels at full resolution), forward and backward, and the ToRGB backward pack
+    lin = torch.rand(64, device=device) / 64
+    fa = ycl[:, :64].contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    fb = dycl[:, :64].contiguous(memory_format=torch.channels_last)
+    hbm("lpips_tap_kernel<bf16,fwd> [%d,64,256,256] x2 bf16 NHWC" % n2, lambda: V.lpips_tap.lpips_tap(fa.detach(), fb, lin),
+        2 * fa.numel() * 2, key="lpips_tap_fwd")
+    import ctypes
+    gv = torch.ones(n2, device=device)
+    da = torch.empty_like(fb)
+    fad = fa.detach()
+    s4 = lambda t: ctypes.byref((ctypes.c_int64 * 4)(*[int(v) for v in t.stride()]))
+    lib = _lib.load()
+
+    def lp_bwd():
+        _lib.check(lib.vcn_lpips_tap_bwd(_lib.ptr(fad), _lib.ptr(fb), _lib.dtype_code(fad.dtype), s4(fad), s4(fb), _lib.ptr(lin),
+                                         _lib.ptr(gv), _lib.ptr(da), n2, 64, 256, 256, _lib.current_stream(fad.device)), "lpips_tap_bwd")
+
+    hbm("lpips_tap_kernel<bf16,bwd> [%d,64,256,256] bf16 NHWC (2 reads + 1 write)" % n2, lp_bwd, 3 * fa.numel() * 2, key="lpips_tap_bwd")
+    del fa, fb, fad, da
+    dimg, yimg = rn(n2, 3, 256, 256), rn(n2, 3, 256, 256)
+    epi3, hold3 = M.make_epilogue(bias=rn(3), act="linear", clamp=256.0)
+    hbm("modconv_bwd_pack_smallc_kernel<float,bf16> ToRGB [%d,3,256,256] fp32 NCHW -> bf16 NHWC8" % n2,
+        lambda: M.bwd_pack(dimg, yimg, epi3, False, True), (2 * dimg.numel() * 4 + n2 * 65536 * 16), key="modconv_bwd_pack_smallc")
+    del ycl, dycl, dimg, yimg, hold3
 
     # ---- the convolutions: vcn_conv_igemm vs cuDNN on the layer shapes of SURVEY App. A (res >= 64: 91 % of the FLOPs) ---
     def cudnn_ms(kind, xin, w):

@@ -9,6 +9,7 @@
 // difference - without re-reading) and the backward reads them once more and writes da.  HBM-bound.
 //   backward:  da_c = g[n]/HW * ( 2 lin_c u_c / na  -  2 a_c T / (na^2 |a|) ),  u = a/na - b/nb,  T = sum_c lin_c u_c a_c,
 //              na = |a| + eps (the second term is 0 where |a| = 0).
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -131,6 +132,145 @@ __global__ void __launch_bounds__(256) lpips_tap_kernel(const LpipsArgs a, const
   }
 }
 
+// Bulk-copy staged variant (dense 16-bit channels-last maps): the register-staged kernel above keeps ~25 KB in flight per
+// SM (0.31 of the HBM peak on the [16,64,256,256] tap).  Here the TMA engine streams both maps into a shared-memory ring
+// (cp.async.bulk, 8 KB per map and stage, 4 stages, 3 CTAs per SM) and the lane groups read their channel vectors from it.
+constexpr int kLpStages = 4;
+constexpr uint32_t kLpStageBytes = 8192;  // per map and stage
+
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs a, const int G, const int NV, const int chunk) {
+  extern __shared__ __align__(128) unsigned char ring[];  // [kLpStages][2][kLpStageBytes]
+  __shared__ __align__(8) uint64_t full_bar[kLpStages];
+  __shared__ float red[8];
+  const int n = blockIdx.y, tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int sub = lane / G, gl = lane % G;
+  const int ppw = 32 / G;
+  const int hw = a.h * a.w;
+  const int p0 = blockIdx.x * chunk, p_end = min(hw, p0 + chunk);
+  const uint32_t row_bytes = (uint32_t)a.c * 2u;
+  const int sp = (int)(kLpStageBytes / row_bytes);  // pixels per stage, a multiple of 8 * ppw
+  const int nit = (p_end - p0 + sp - 1) / sp;
+  const unsigned char* ga = static_cast<const unsigned char*>(a.a) + ((int64_t)n * a.as[0] + (int64_t)p0 * a.c) * 2;
+  const unsigned char* gb = static_cast<const unsigned char*>(a.b) + ((int64_t)n * a.bs[0] + (int64_t)p0 * a.c) * 2;
+  auto fill = [&](int it) {
+    const int s = it % kLpStages;
+    const int px = min(sp, p_end - p0 - it * sp);
+    const uint32_t bytes = (uint32_t)px * row_bytes;
+    unsigned char* dst = ring + (size_t)s * 2 * kLpStageBytes;
+    mbar_expect_tx(full_bar + s, 2u * bytes);
+    bulk_load_1d(dst, ga + (int64_t)it * sp * row_bytes, bytes, full_bar + s);
+    bulk_load_1d(dst + kLpStageBytes, gb + (int64_t)it * sp * row_bytes, bytes, full_bar + s);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kLpStages; ++s) mbar_init(full_bar + s, 1);
+    fence_mbar_init();
+    for (int it = 0; it < min(nit, kLpStages); ++it) fill(it);
+  }
+  float lin[kMaxVec][8];
+#pragma unroll
+  for (int v = 0; v < kMaxVec; ++v)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) lin[v][k] = v < NV ? a.lin[(v * G + gl) * 8 + k] : 0.f;
+  const float g = BWD ? a.gval[n] * a.scale : 0.f;
+  float acc = 0.f;
+  __syncthreads();
+  for (int it = 0; it < nit; ++it) {
+    const int s = it % kLpStages;
+    mbar_wait(full_bar + s, (uint32_t)(it / kLpStages) & 1u);
+    const unsigned char* sa = ring + (size_t)s * 2 * kLpStageBytes;
+    for (int pl0 = warp * ppw; pl0 < sp; pl0 += 8 * ppw) {
+      const int pl = pl0 + sub;
+      const int p = p0 + it * sp + pl;
+      const bool ok = p < p_end;
+      float x[kMaxVec][8], y[kMaxVec][8];
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int v = 0; v < kMaxVec; ++v) {
+        if (v < NV && ok) {
+          const size_t off = (size_t)pl * row_bytes + (size_t)(v * G + gl) * 16;
+          const Vec16<T> va = *reinterpret_cast<const Vec16<T>*>(sa + off);
+          const Vec16<T> vb = *reinterpret_cast<const Vec16<T>*>(sa + kLpStageBytes + off);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { x[v][k] = to_acc<T>(va.v[k]); y[v][k] = to_acc<T>(vb.v[k]); }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) x[v][k] = y[v][k] = 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { s0 = fmaf(x[v][k], x[v][k], s0); s1 = fmaf(y[v][k], y[v][k], s1); }
+      }
+      s0 = group_sum(s0, G); s1 = group_sum(s1, G);
+      const float n0 = sqrtf(s0), ia = 1.f / (n0 + 1e-10f), ib = 1.f / (sqrtf(s1) + 1e-10f);
+      float d = 0.f;
+#pragma unroll
+      for (int v = 0; v < kMaxVec; ++v)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float u = x[v][k] * ia - y[v][k] * ib;
+          d = fmaf(lin[v][k] * u, BWD ? x[v][k] : u, d);
+        }
+      d = group_sum(d, G);
+      if (!BWD) {
+        if (ok && gl == 0) acc += d;
+      } else if (ok) {
+        const float k2 = n0 > 0.f ? 2.f * g * d * ia * ia / n0 : 0.f, k1 = 2.f * g * ia;
+#pragma unroll
+        for (int v = 0; v < kMaxVec; ++v) {
+          if (v < NV) {
+            const int c = (v * G + gl) * 8;
+            Vec16<T> ov;
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              ov.v[k] = from_acc<T>(k1 * lin[v][k] * (x[v][k] * ia - y[v][k] * ib) - k2 * x[v][k]);
+            st_stream<T>(static_cast<T*>(a.da) + ((int64_t)n * hw + p) * a.c + c, ov);
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && it + kLpStages < nit) {
+      fence_proxy_async();
+      fill(it + kLpStages);
+    }
+  }
+  if (!BWD) {
+    acc = warp_sum(acc);
+    if (lane == 0) red[warp] = acc;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 8; ++i) t += red[i];
+      atomicAdd(a.val + n, t * a.scale);
+    }
+  }
+}
+
+template <typename T, bool BWD>
+int launch_bulk(const LpipsArgs& a, int G, int NV, cudaStream_t st, const char* name) {
+  const int hw = a.h * a.w;
+  const int sp = (int)(kLpStageBytes / ((uint32_t)a.c * 2u));
+  int per_sample = (sm_count() * 3) / a.n;
+  if (per_sample < 1) per_sample = 1;
+  int chunk = (hw + per_sample - 1) / per_sample;
+  chunk = (chunk + sp - 1) / sp * sp;
+  if (chunk < 4 * sp) chunk = 4 * sp;
+  dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)a.n);
+  const size_t smem = (size_t)kLpStages * 2 * kLpStageBytes;
+  auto kern = lpips_tap_bulk_kernel<T, BWD>;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  VCN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  kern<<<grid, 256, smem, st>>>(a, G, NV, chunk);
+  VCN_LAUNCH_CHECK(name);
+  return VCN_OK;
+}
+
 template <bool BWD>
 int run(const void* fa, const void* fb, int dtype, const int64_t* as, const int64_t* bs, const float* lin, float* val,
         const float* gval, void* da, int n, int c, int h, int w, cudaStream_t st, const char* name) {
@@ -153,6 +293,15 @@ int run(const void* fa, const void* fb, int dtype, const int64_t* as, const int6
   for (int i = 0; i < 4; ++i) { a.as[i] = as[i]; a.bs[i] = bs[i]; }
   a.n = n; a.c = c; a.h = h; a.w = w; a.scale = 1.f / ((float)h * (float)w);
   const int hw = h * w;
+  {
+    // dense 16-bit channels-last maps of at least 4 MB: the bulk-copy staged kernel
+    static const bool allow = [] { const char* e = getenv("VCN_LPIPS_BULK"); return !e || atoi(e) != 0; }();
+    auto dense = [&](const int64_t* s) { return s[3] == c && s[2] == (int64_t)w * c && (s[0] * 2) % 16 == 0; };
+    if (allow && dtype != VCN_F32 && dense(as) && dense(bs) && (int64_t)n * hw * c >= (1 << 21) && 8192 % (c * 2) == 0) {
+      if (dtype == VCN_BF16) return launch_bulk<__nv_bfloat16, BWD>(a, G, NV, st, name);
+      return launch_bulk<__half, BWD>(a, G, NV, st, name);
+    }
+  }
   int chunk = hw;
   const int per_iter = 8 * (32 / G);
   while (chunk > 8 * per_iter && (int64_t)n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 16) chunk = (chunk + 1) / 2;

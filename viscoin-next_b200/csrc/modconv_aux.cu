@@ -277,6 +277,84 @@ __global__ void __launch_bounds__(256) modconv_bwd_pack_kernel(const BwdPackArgs
   }
 }
 
+// Few channels (c <= 8, c_pad == 8: the ToRGB layers, whose dy is the fp32 NCHW image gradient): the 64-channel tile above
+// keeps one warp in eight busy (230 us for [16,3,256,256]).  Here a thread owns a PIXEL: the per-channel reads are
+// coalesced along the pixels of a plane, the 8-channel NHWC operand row is one 16-byte (bf16) or two 16-byte (fp32) stores,
+// and the channel sums stay in registers until one block reduction.  grid (pixel chunks, n).
+template <typename T, typename TO>
+__global__ void __launch_bounds__(256) modconv_bwd_pack_smallc_kernel(const BwdPackArgs a, const int chunk) {
+  __shared__ float red[8][16];
+  const int n = blockIdx.y;
+  const int hw = a.h * a.w;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* dyn = static_cast<const T*>(a.dy) + (int64_t)n * a.dys[0];
+  const T* yn = a.y ? static_cast<const T*>(a.y) + (int64_t)n * a.ys[0] : nullptr;
+  float gacc[8], bacc[8], dc[8], bi[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    gacc[i] = bacc[i] = 0.f;
+    dc[i] = (a.dcoef && i < a.c) ? a.dcoef[(int64_t)n * a.c + i] : 1.f;
+    bi[i] = (a.bias && a.act && i < a.c) ? a.bias[i] : 0.f;
+  }
+  const int p_end = min(hw, (int)(blockIdx.x + 1) * chunk);
+  const bool dense_a = a.dys[3] == 1 && a.dys[2] == a.w, dense_y = a.ys[3] == 1 && a.ys[2] == a.w;
+  for (int p = blockIdx.x * chunk + threadIdx.x; p < p_end; p += 256) {
+    const int py = p / a.w, px = p - py * a.w;
+    const int64_t oa = dense_a ? (int64_t)p : (int64_t)py * a.dys[2] + (int64_t)px * a.dys[3];
+    const int64_t oy = dense_y ? (int64_t)p : (int64_t)py * a.ys[2] + (int64_t)px * a.ys[3];
+    const float nz = a.noise ? a.noise[(int64_t)n * a.noise_stride_n + p] : 0.f;
+    float out[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      out[i] = 0.f;
+      if (i < a.c) {
+        const float dyv = to_acc<T>(dyn[(int64_t)i * a.dys[1] + oa]);
+        const float yv = yn ? to_acc<T>(yn[(int64_t)i * a.ys[1] + oy]) : 0.f;
+        float dz = dyv, r = yv;
+        if (a.act) {  // same arithmetic as modconv_bwd_pack_kernel
+          const float yy = yv / a.gain;
+          dz = (a.act == VCN_ACT_LRELU && !(yy > 0.f)) ? dyv * a.alpha : dyv;
+          dz *= a.gain;
+          if (a.clamp >= 0.f && !(yv > -a.clamp && yv < a.clamp)) dz = 0.f;
+          r = (a.act == VCN_ACT_LRELU && !(yy > 0.f)) ? yy / a.alpha : yy;
+          r -= bi[i];
+        }
+        r -= nz;
+        gacc[i] = fmaf(dz, r, gacc[i]);
+        bacc[i] += dz;
+        out[i] = dz * dc[i];
+      }
+    }
+    TO* dst = static_cast<TO*>(a.dy0) + ((int64_t)n * hw + p) * 8;
+    if constexpr (sizeof(TO) == 2) {
+      Vec16<TO> o;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o.v[i] = from_acc<TO>(out[i]);
+      *reinterpret_cast<Vec16<TO>*>(dst) = o;
+    } else {
+      *reinterpret_cast<float4*>(dst) = make_float4(out[0], out[1], out[2], out[3]);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(out[4], out[5], out[6], out[7]);
+    }
+  }
+  if (!a.gsum && !a.db) return;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float g = warp_sum(gacc[i]), b = warp_sum(bacc[i]);
+    if (lane == 0) { red[warp][i] = g; red[warp][8 + i] = b; }
+  }
+  __syncthreads();
+  if (threadIdx.x < 16) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+    const int i = threadIdx.x & 7;
+    if (i < a.c) {
+      if (threadIdx.x < 8) { if (a.gsum) atomicAdd(a.gsum + (int64_t)n * a.c + i, t); }
+      else if (a.db) atomicAdd(a.db + i, t);
+    }
+  }
+}
+
 // dx = dxhat * s[n,c] (in place), ds1[n,c] += sum_p dxhat * x.  grid (chunks, c, n); dxhat fp32, any strides.
 template <typename T>
 __global__ void __launch_bounds__(256) modconv_bwd_finish_kernel(float* __restrict__ dxhat, const int64_t ds0, const int64_t ds1_,
@@ -560,6 +638,35 @@ int vcn_modconv_bwd_pack_ex(const void* dy, const void* y, int dtype, const int6
     const int rc = bwd_pack_cl_try(dy, y, dtype, a.dys, a.ys, epi, dy0, gsum, db, n, c, c_pad, h, w, a.act, a.alpha, a.gain,
                                    a.clamp, st);
     if (rc >= 0) return rc;
+  }
+  static const bool allow_smallc = [] { const char* e = getenv("VCN_BWD_PACK_SMALLC"); return !e || atoi(e) != 0; }();
+  if (allow_smallc && c_pad == 8 && (reinterpret_cast<uintptr_t>(dy0) & 15u) == 0) {
+    // few channels (ToRGB): one thread per pixel; about 4 CTAs per SM, at least 1024 pixels each
+    const int hw = h * w;
+    int chunk = hw;
+    while (chunk > 1024 && (int64_t)n * ((hw + chunk - 1) / chunk) < (int64_t)sm_count() * 4) chunk = (chunk + 1) / 2;
+    chunk = (chunk + 255) / 256 * 256;
+    dim3 sgrid((unsigned)((hw + chunk - 1) / chunk), (unsigned)n);
+    bool done = true;
+    if (dy0_dtype == VCN_F32) {
+      switch (dtype) {
+        case VCN_F32: modconv_bwd_pack_smallc_kernel<float, float><<<sgrid, 256, 0, st>>>(a, chunk); break;
+        case VCN_F16: modconv_bwd_pack_smallc_kernel<__half, float><<<sgrid, 256, 0, st>>>(a, chunk); break;
+        case VCN_BF16: modconv_bwd_pack_smallc_kernel<__nv_bfloat16, float><<<sgrid, 256, 0, st>>>(a, chunk); break;
+        default: done = false;
+      }
+    } else {
+      switch (dtype) {
+        case VCN_F32: modconv_bwd_pack_smallc_kernel<float, __nv_bfloat16><<<sgrid, 256, 0, st>>>(a, chunk); break;
+        case VCN_F16: modconv_bwd_pack_smallc_kernel<__half, __nv_bfloat16><<<sgrid, 256, 0, st>>>(a, chunk); break;
+        case VCN_BF16: modconv_bwd_pack_smallc_kernel<__nv_bfloat16, __nv_bfloat16><<<sgrid, 256, 0, st>>>(a, chunk); break;
+        default: done = false;
+      }
+    }
+    if (done) {
+      VCN_LAUNCH_CHECK("modconv_bwd_pack_smallc_kernel");
+      return VCN_OK;
+    }
   }
   if (dy0_dtype == VCN_F32) {
     switch (dtype) {

@@ -23,6 +23,7 @@ the plain fp32 modules (tests/test_gpu_frozen.py).
 """
 
 import ctypes
+import os
 
 import torch
 import torch.nn.functional as F
@@ -56,6 +57,13 @@ class _WeightCache:
 
 
 _weights = _WeightCache()
+
+# first convolution of VGG-16 (3 input channels): "cudnn" = the library kernel (default), "vcn" = this package's implicit GEMM
+# on an 8-channel NHWC copy of the image.  Measured in the step (profiles/r2l_ab.txt): vcn 16.13 ms vs cudnn 15.55 ms - a
+# 64-channel k-block carrying 8 real channels wastes 7/8 of the operand staging, so the library kernel stays.
+first_layer_impl = os.environ.get("VCN_VGG_FIRST", "cudnn")
+# MaxPool2d(3, 2, 1) of the ResNet stem: "vcn" = csrc/frozen_ops.cu, "aten" = torch's NHWC kernels
+stem_pool_impl = os.environ.get("VCN_STEM_POOL", "vcn")
 
 
 # ---- this package's kernels ---------------------------------------------------------------------------------------------
@@ -100,6 +108,46 @@ def maxpool2x2_relu_bwd(y, gpool, gtap=None):
     return dz
 
 
+class _MaxPool3x3s2(torch.autograd.Function):
+    """torch.nn.MaxPool2d(3, 2, 1) on 16-bit channels_last activations (the ResNet stem's pooler) on this package's kernels."""
+
+    @staticmethod
+    def forward(ctx, x):
+        n, c, h, w = x.shape
+        oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+        y = torch.empty([n, c, oh, ow], dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        need = ctx is not None and x.requires_grad
+        idx = torch.empty([n, oh, ow, c], dtype=torch.uint8, device=x.device) if need else None
+        with torch.cuda.device(x.device):
+            st = _lib.load().vcn_maxpool3x3s2_fwd(_lib.ptr(x), _lib.ptr(y), _lib.ptr(idx), _lib.dtype_code(x.dtype), n, h, w, c,
+                                                  _lib.current_stream(x.device))
+        _lib.check(st, "vcn_maxpool3x3s2_fwd")
+        if need:
+            ctx.save_for_backward(idx)
+            ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (idx,) = ctx.saved_tensors
+        n, c, h, w = ctx.shape
+        gy = _cl(gy)
+        gx = torch.empty([n, c, h, w], dtype=gy.dtype, device=gy.device, memory_format=torch.channels_last)
+        with torch.cuda.device(gy.device):
+            st = _lib.load().vcn_maxpool3x3s2_bwd(_lib.ptr(gy), _lib.ptr(idx), _lib.ptr(gx), _lib.dtype_code(gy.dtype), n, h, w, c,
+                                                  _lib.current_stream(gy.device))
+        _lib.check(st, "vcn_maxpool3x3s2_bwd")
+        return gx
+
+
+def maxpool3x3s2(x):
+    """MaxPool2d(3, 2, 1) of a 16-bit channels_last tensor; differentiable."""
+    assert x.is_contiguous(memory_format=torch.channels_last) and x.dtype in (torch.bfloat16, torch.float16) and x.shape[1] % 8 == 0
+    if torch.is_grad_enabled() and x.requires_grad:
+        return _MaxPool3x3s2.apply(x)
+    return _MaxPool3x3s2.forward(None, x)
+
+
 # ---- convolution + bias + ReLU (+ residual), input gradient only ----------------------------------------------------------
 
 
@@ -111,6 +159,18 @@ def _conv_fwd(x, w, b, stride, padding, relu=True, residual=None, impl="cudnn"):
         wt, _ = M._packed(w, False, False, False)
         out = torch.empty([x.shape[0], w.shape[0], x.shape[2], x.shape[3]], dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         # relu = lrelu with alpha 0: the compile-time lrelu epilogue of the GEMM (the generic activation switch is slower)
+        epi, hold = M.make_epilogue(bias=b, act="lrelu", alpha=0.0, gain=1.0)
+        M.conv_igemm(xh, wt, _lib.CONV_FPROP, w.shape[0], 3, 3, out=out, epilogue=epi)
+        del hold
+        return out
+    if (first_layer_impl == "vcn" and relu and residual is None and x.shape[1] < 8 and w.shape[-1] == 3 and stride == (1, 1)
+            and padding == (1, 1) and w.shape[0] % 64 == 0 and x.dtype == torch.bfloat16):
+        # 3-channel image -> 64 channels (VGG-16 conv1_1): cuDNN pads the input to 8 channels and runs a legacy sm80 kernel
+        # at 160-180 us for [16,3,256,256]; the implicit GEMM on an 8-channel NHWC copy of the image is write-bound
+        from . import modconv as M
+        xh = M.modulate_pack(x, None)  # bf16 NHWC [N,H,W,8], pad channels zero
+        wt, _ = M._packed(w, False, False, False)
+        out = torch.empty([x.shape[0], w.shape[0], x.shape[2], x.shape[3]], dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         epi, hold = M.make_epilogue(bias=b, act="lrelu", alpha=0.0, gain=1.0)
         M.conv_igemm(xh, wt, _lib.CONV_FPROP, w.shape[0], 3, 3, out=out, epilogue=epi)
         del hold
@@ -193,7 +253,12 @@ class FusedResNet:
         r = self.m.resnet
         x = _cl(images.to(torch.bfloat16))
         x = conv_relu(x, r.embedder.embedder.convolution)
-        x = F.max_pool2d(x, 3, 2, 1)
+        pool = r.embedder.pooler
+        if (stem_pool_impl == "vcn" and isinstance(pool, torch.nn.MaxPool2d) and pool.kernel_size in (3, (3, 3)) and pool.stride in (2, (2, 2))
+                and pool.padding in (1, (1, 1)) and not pool.ceil_mode and x.shape[1] % 8 == 0):
+            x = maxpool3x3s2(x)
+        else:
+            x = pool(x)
         hidden = []
         for stage in r.encoder.stages:
             hidden.append(x)
