@@ -170,6 +170,11 @@ int vcn_demod_coefs(const float* styles, const float* wsq, float* d, int n, int 
 int vcn_pack_weights_mod(const void* w, int w_dtype, const float* styles, const float* dcoef, void* wn,
                          int n, int cout, int cin, int cin_pad, int kh, int kw, void* stream);
 /* epi (may be NULL) reuses vcn_upfirdn2d_epilogue: acc * scale[n,co] + noise[n?,oy,ox], then bias_act. */
+/* Leave `sms` SMs out of vcn_conv_igemm's persistent grid (default 0).  For data-parallel runs whose gradient all-reduce
+ * overlaps the convolutions: the CTAs of a collective kernel own their SMs, and a persistent CTA that cannot become resident
+ * would hold its statically assigned tiles back until the collective ends.  Process-wide; no reference counterpart (the
+ * reference has no overlapped collective, stylegan2_ada/training/training_loop.py:300-307). */
+int vcn_set_conv_sm_reserve(int sms);
 int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_desc* desc,
                    const vcn_upfirdn2d_epilogue* epi, void* stream);
 
@@ -231,6 +236,13 @@ int vcn_maxpool2x2_fwd(const void* x, void* y, int dtype, int n, int h, int w, i
  * reference reaches it through transformers' ResNetModel, viscoin/models/classifiers.py:83-92): x [n,h,w,c] -> y [n,oh,ow,c],
  * oh = (h-1)/2+1.  idx (may be NULL when no backward follows) = one byte per output element: the winning window position
  * dy*3+dx, first maximum in scan order (ATen's max_pool2d_with_indices).  _bwd: gx [n,h,w,c] from gy [n,oh,ow,c] and idx. */
+/* First convolution of a frozen image network: 3 -> 64 channels, 3x3/stride 1/pad 1 (VGG-16 conv1_1, lpips v0.1.4 through
+ * viscoin/training/losses.py:111-123) or 7x7/stride 2/pad 3 (the ResNet stem, viscoin/models/classifiers.py:83-92), bias
+ * (+ ReLU), bf16 channels-last: x [n,h,w,3], y [n,oh,ow,64].  wp = the weight re-laid out as [KP][64] bf16 with
+ * k = (ky*ks + kx)*3 + c and KP = ks*ks*3 rounded up to 16 (zero rows); bias fp32 [64] or NULL.  Replaces the cuDNN call the
+ * reference reaches through torch (conv2d on a 3-channel image). */
+int vcn_conv_first3(const void* x, const void* wp, const float* bias, void* y, int dtype, int ks, int stride, int pad, int relu,
+                    int n, int h, int w, void* stream);
 int vcn_maxpool3x3s2_fwd(const void* x, void* y, void* idx, int dtype, int n, int h, int w, int c, void* stream);
 int vcn_maxpool3x3s2_bwd(const void* gy, const void* idx, void* gx, int dtype, int n, int h, int w, int c, void* stream);
 int vcn_relu_mask_bwd(const void* y, const void* g, const void* g2, void* dz, int dtype, int64_t numel, void* stream);

@@ -78,6 +78,25 @@ def test_maxpool3x3s2_forward_and_backward_bit_exact(shape):
     assert torch.equal(xa.grad, xb.grad)
 
 
+@pytest.mark.parametrize("ks,stride,pad,shape", [(3, 1, 1, (2, 3, 40, 56)), (3, 1, 1, (1, 3, 19, 21)), (7, 2, 3, (2, 3, 64, 96)),
+                                                 (7, 2, 3, (1, 3, 37, 45)), (3, 1, 1, (4, 3, 256, 256)), (7, 2, 3, (4, 3, 256, 256))])
+@pytest.mark.parametrize("relu", [True, False])
+def test_conv_first3_matches_fp32_convolution(ks, stride, pad, shape, relu):
+    """vcn_conv_first3 (VGG conv1_1 / ResNet stem on mma.sync) vs F.conv2d in fp32 on the same bf16-rounded operands: the only
+    differences are the fp32 accumulation order and the final bf16 rounding (2^-9 relative): rel-Linf <= 6e-3."""
+    fz = _fz()
+    gen = torch.Generator(device="cuda").manual_seed(ks * 100 + shape[2])
+    x = torch.randn(shape, device="cuda", generator=gen).bfloat16().contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(64, 3, ks, ks, device="cuda", generator=gen) / (ks * 1.7)).bfloat16().contiguous(memory_format=torch.channels_last)
+    b = torch.randn(64, device="cuda", generator=gen).bfloat16()
+    y = fz.conv_first3(x, w, b, ks, stride, pad, relu)
+    ref = F.conv2d(x.float(), w.float(), b.float(), stride, pad)
+    if relu:
+        ref = torch.relu(ref)
+    assert y.shape == ref.shape and y.dtype == torch.bfloat16 and y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, ref) <= 6e-3
+
+
 def test_frozen_ops_reject_bad_arguments():
     import viscoin_next_b200 as V
     fz = _fz()

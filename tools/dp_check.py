@@ -56,7 +56,12 @@ def main():
     tr = build(0)
     set_noise_strength(tr, 0.1)
     want, want_losses = grads_of(tr, slice(0, world * n))
-    del tr
+    # ... and the mean of the per-shard gradients computed one after the other on this GPU alone: what the all-reduce must
+    # reproduce (same kernels on the same shards - only the reduction order differs), separating the exchange machinery from
+    # the batch-size dependence of the bf16 arithmetic (cuDNN picks other kernels / split-k factors for other batch sizes)
+    shard_grads = [grads_of(tr, slice(r * n, (r + 1) * n))[0] for r in range(world)]
+    manual = {k: sum(sg[k] for sg in shard_grads) / world for k in want}
+    del tr, shard_grads
     torch.cuda.empty_cache()
 
     # phase 2: W ranks, one shard each
@@ -79,11 +84,16 @@ def main():
     for grp in ("concept_extractor", "explainer", "viscoin_gan"):
         keys = [k for k in want if k.startswith(grp + ".")]
         res["grads"][grp] = metrics(cat(got, keys), cat(want, keys))
+        res.setdefault("grads_vs_mean_of_shards", {})[grp] = metrics(cat(got, keys), cat(manual, keys))
     lt = torch.tensor([got_losses[k] for k in sorted(got_losses)], device=dev, dtype=torch.float64)
     dist.all_reduce(lt, op=dist.ReduceOp.AVG)
     # 'ortho' depends on parameters only; the other terms are batch means: mean over ranks == concatenated batch
     res["losses"] = {k: {"dp_mean": float(v), "single": want_losses[k]} for k, v in zip(sorted(got_losses), lt)}
-    ok = img_diff == 0.0 and all(v["rel_l2"] <= 2e-2 and v["cos"] >= 0.9995 for v in res["grads"].values()) and \
+    # gates: the exchange itself (NCCL mean of shard gradients vs the same mean formed on one GPU) is tight; the concatenated
+    # batch differs from the shards by bf16 rounding amplified through the random-init f / VGG (measured r2m: Psi rel-L2
+    # 4.7e-2, cosine 0.9989; mapping 8e-3; the same harness against the fp32 oracle gives Psi 1.2e-1, tests/test_gpu_step.py)
+    ok = img_diff == 0.0 and all(v["rel_l2"] <= 5e-3 and v["cos"] >= 0.9999 for v in res["grads_vs_mean_of_shards"].values()) and \
+        all(v["rel_l2"] <= 1e-1 and v["cos"] >= 0.995 for v in res["grads"].values()) and \
         all(abs(v["dp_mean"] - v["single"]) <= 2e-3 * max(1e-3, abs(v["single"])) for v in res["losses"].values())
     res["ok"] = bool(ok)
     if rank == 0:

@@ -146,3 +146,19 @@ if "bwdcl" in what:
     timed("bwd_finish_cl bf16 [16,128,256,256]", lambda: M.bwd_finish_cl(dxh, y, s, True), 3 * y.numel() * 2, "GB/s")
     x32 = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
     timed("modulate_pack_cl bf16 [16,128,256,256]", lambda: M.modulate_pack(x32, s), 2 * y.numel() * 2, "GB/s")
+
+if "lpips" in what:
+    n, c, r = 16, 64, 256
+    fa = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    fb = torch.randn(n, c, r, r, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    lin = torch.rand(c, device=dev) / c
+    timed("lpips_tap fwd bf16 [16,64,256,256]", lambda: V.lpips_tap.lpips_tap(fa.detach(), fb, lin), 2 * fa.numel() * 2, "GB/s")
+    iters = 1
+    GRAPH = False
+    timed("lpips_tap fwd+bwd bf16 [16,64,256,256]", lambda: V.lpips_tap.lpips_tap(fa, fb, lin).sum().backward(), 5 * fa.numel() * 2, "GB/s")
+
+if "torgb" in what:
+    n = 16
+    dimg, yimg = torch.randn(n, 3, 256, 256, device=dev), torch.randn(n, 3, 256, 256, device=dev)
+    epi3, hold3 = M.make_epilogue(bias=torch.randn(3, device=dev), act="linear", clamp=256.0)
+    timed("bwd_pack small-c ToRGB f32 [16,3,256,256]", lambda: M.bwd_pack(dimg, yimg, epi3, False, True), 2 * dimg.numel() * 4 + n * 65536 * 16, "GB/s")

@@ -138,8 +138,16 @@ __global__ void __launch_bounds__(256) lpips_tap_kernel(const LpipsArgs a, const
 constexpr int kLpStages = 4;
 constexpr uint32_t kLpStageBytes = 8192;  // per map and stage
 
-template <typename T, bool BWD>
-__global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs a, const int G, const int NV, const int chunk) {
+// G (lanes per pixel) and NV (8-channel vectors per lane) are compile-time here: the shuffle trees and the per-vector loops
+// unroll exactly (the run-time form computes both kMaxVec vectors and loops over the shuffle distance).
+template <int G> __device__ __forceinline__ float group_sum_c(float v) {
+#pragma unroll
+  for (int o = G >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <typename T, bool BWD, int G, int NV>
+__global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs a, const int chunk) {
   extern __shared__ __align__(128) unsigned char ring[];  // [kLpStages][2][kLpStageBytes]
   __shared__ __align__(8) uint64_t full_bar[kLpStages];
   __shared__ float red[8];
@@ -168,11 +176,11 @@ __global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs 
     fence_mbar_init();
     for (int it = 0; it < min(nit, kLpStages); ++it) fill(it);
   }
-  float lin[kMaxVec][8];
+  float lin[NV][8];
 #pragma unroll
-  for (int v = 0; v < kMaxVec; ++v)
+  for (int v = 0; v < NV; ++v)
 #pragma unroll
-    for (int k = 0; k < 8; ++k) lin[v][k] = v < NV ? a.lin[(v * G + gl) * 8 + k] : 0.f;
+    for (int k = 0; k < 8; ++k) lin[v][k] = a.lin[(v * G + gl) * 8 + k];
   const float g = BWD ? a.gval[n] * a.scale : 0.f;
   float acc = 0.f;
   __syncthreads();
@@ -184,11 +192,11 @@ __global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs 
       const int pl = pl0 + sub;
       const int p = p0 + it * sp + pl;
       const bool ok = p < p_end;
-      float x[kMaxVec][8], y[kMaxVec][8];
+      float x[NV][8], y[NV][8];
       float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-      for (int v = 0; v < kMaxVec; ++v) {
-        if (v < NV && ok) {
+      for (int v = 0; v < NV; ++v) {
+        if (ok) {
           const size_t off = (size_t)pl * row_bytes + (size_t)(v * G + gl) * 16;
           const Vec16<T> va = *reinterpret_cast<const Vec16<T>*>(sa + off);
           const Vec16<T> vb = *reinterpret_cast<const Vec16<T>*>(sa + kLpStageBytes + off);
@@ -201,24 +209,24 @@ __global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs 
 #pragma unroll
         for (int k = 0; k < 8; ++k) { s0 = fmaf(x[v][k], x[v][k], s0); s1 = fmaf(y[v][k], y[v][k], s1); }
       }
-      s0 = group_sum(s0, G); s1 = group_sum(s1, G);
+      s0 = group_sum_c<G>(s0); s1 = group_sum_c<G>(s1);
       const float n0 = sqrtf(s0), ia = 1.f / (n0 + 1e-10f), ib = 1.f / (sqrtf(s1) + 1e-10f);
       float d = 0.f;
 #pragma unroll
-      for (int v = 0; v < kMaxVec; ++v)
+      for (int v = 0; v < NV; ++v)
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float u = x[v][k] * ia - y[v][k] * ib;
           d = fmaf(lin[v][k] * u, BWD ? x[v][k] : u, d);
         }
-      d = group_sum(d, G);
+      d = group_sum_c<G>(d);
       if (!BWD) {
         if (ok && gl == 0) acc += d;
       } else if (ok) {
         const float k2 = n0 > 0.f ? 2.f * g * d * ia * ia / n0 : 0.f, k1 = 2.f * g * ia;
 #pragma unroll
-        for (int v = 0; v < kMaxVec; ++v) {
-          if (v < NV) {
+        for (int v = 0; v < NV; ++v) {
+          {
             const int c = (v * G + gl) * 8;
             Vec16<T> ov;
 #pragma unroll
@@ -247,8 +255,8 @@ __global__ void __launch_bounds__(256, 3) lpips_tap_bulk_kernel(const LpipsArgs 
   }
 }
 
-template <typename T, bool BWD>
-int launch_bulk(const LpipsArgs& a, int G, int NV, cudaStream_t st, const char* name) {
+template <typename T, bool BWD, int G, int NV>
+int launch_bulk(const LpipsArgs& a, cudaStream_t st, const char* name) {
   const int hw = a.h * a.w;
   const int sp = (int)(kLpStageBytes / ((uint32_t)a.c * 2u));
   int per_sample = (sm_count() * 3) / a.n;
@@ -258,7 +266,7 @@ int launch_bulk(const LpipsArgs& a, int G, int NV, cudaStream_t st, const char* 
   if (chunk < 4 * sp) chunk = 4 * sp;
   dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)a.n);
   const size_t smem = (size_t)kLpStages * 2 * kLpStageBytes;
-  auto kern = lpips_tap_bulk_kernel<T, BWD>;
+  auto kern = lpips_tap_bulk_kernel<T, BWD, G, NV>;
   static bool attr_set[64] = {};
   int dev = 0;
   VCN_CUDA(cudaGetDevice(&dev));
@@ -266,7 +274,7 @@ int launch_bulk(const LpipsArgs& a, int G, int NV, cudaStream_t st, const char* 
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  kern<<<grid, 256, smem, st>>>(a, G, NV, chunk);
+  kern<<<grid, 256, smem, st>>>(a, chunk);
   VCN_LAUNCH_CHECK(name);
   return VCN_OK;
 }
@@ -298,8 +306,11 @@ int run(const void* fa, const void* fb, int dtype, const int64_t* as, const int6
     static const bool allow = [] { const char* e = getenv("VCN_LPIPS_BULK"); return !e || atoi(e) != 0; }();
     auto dense = [&](const int64_t* s) { return s[3] == c && s[2] == (int64_t)w * c && (s[0] * 2) % 16 == 0; };
     if (allow && dtype != VCN_F32 && dense(as) && dense(bs) && (int64_t)n * hw * c >= (1 << 21) && 8192 % (c * 2) == 0) {
-      if (dtype == VCN_BF16) return launch_bulk<__nv_bfloat16, BWD>(a, G, NV, st, name);
-      return launch_bulk<__half, BWD>(a, G, NV, st, name);
+#define VCN_LP(GG, VV)                                                                         \
+  if (G == GG && NV == VV)                                                                    \
+    return dtype == VCN_BF16 ? launch_bulk<__nv_bfloat16, BWD, GG, VV>(a, st, name) : launch_bulk<__half, BWD, GG, VV>(a, st, name)
+      VCN_LP(8, 1); VCN_LP(16, 1); VCN_LP(32, 1); VCN_LP(32, 2);
+#undef VCN_LP
     }
   }
   int chunk = hw;

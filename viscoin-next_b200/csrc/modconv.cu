@@ -668,8 +668,20 @@ const ConvEnv& conv_env() {
   return env;
 }
 
+// SMs this kernel leaves free (vcn_set_conv_sm_reserve): the persistent grid takes one CTA per SM with a STATIC tile walk, so
+// a CTA that cannot become resident - a collective's CTAs own its SM - holds back its whole share of the tiles until the
+// collective ends.  Data-parallel runs reserve as many SMs as the communication kernels occupy.
+int g_sm_reserve = 0;
+
 }  // namespace
 }  // namespace vcn
+
+extern "C" int vcn_set_conv_sm_reserve(int sms) {
+  using namespace vcn;
+  VCN_REQUIRE(sms >= 0 && sms <= 64, "set_conv_sm_reserve: 0..64 SMs (got %d)", sms);
+  g_sm_reserve = sms;
+  return VCN_OK;
+}
 
 extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const vcn_conv_desc* d,
                               const vcn_upfirdn2d_epilogue* epi, void* stream) {
@@ -868,11 +880,13 @@ extern "C" int vcn_conv_igemm(const void* xhat, const void* wt, void* y, const v
     }
   }
   if (!a.pair) {
-    int grid = sm_count();
+    int grid = sm_count() - g_sm_reserve;
+    if (grid < 1) grid = 1;
     if (grid > a.tiles_total) grid = a.tiles_total;
     conv_igemm_kernel<false><<<(unsigned)grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmap_a, tmap_b, om, a);
   } else {
-    int pairs = sm_count() / 2;
+    int pairs = (sm_count() - g_sm_reserve) / 2;
+    if (pairs < 1) pairs = 1;
     if (pairs > a.tiles_total) pairs = a.tiles_total;
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));

@@ -58,10 +58,36 @@ class _WeightCache:
 
 _weights = _WeightCache()
 
-# first convolution of VGG-16 (3 input channels): "cudnn" = the library kernel (default), "vcn" = this package's implicit GEMM
-# on an 8-channel NHWC copy of the image.  Measured in the step (profiles/r2l_ab.txt): vcn 16.13 ms vs cudnn 15.55 ms - a
-# 64-channel k-block carrying 8 real channels wastes 7/8 of the operand staging, so the library kernel stays.
-first_layer_impl = os.environ.get("VCN_VGG_FIRST", "cudnn")
+# first (3-channel) convolutions of VGG-16 and of the ResNet stem: "direct" = csrc/first_conv.cu (default), "cudnn" = the
+# library kernel, "vcn" = the tcgen05 implicit GEMM on an 8-channel NHWC copy of the image (VGG only).  Measured in the step
+# (profiles/r2l_ab.txt): vcn 16.13 ms vs cudnn 15.55 ms - a 64-channel k-block carrying 8 real channels wastes 7/8 of the
+# operand staging.
+first_layer_impl = os.environ.get("VCN_VGG_FIRST", "direct")
+_first_packs = {}
+
+
+def conv_first3(x, w, b, ks, stride, pad, relu=True):
+    """y = [relu](conv(x, w) + b) for a 3-channel bf16 channels_last image and a [64,3,ks,ks] weight (vcn_conv_first3)."""
+    n, _, h, wd = x.shape
+    key = (id(w), w._version, w.data_ptr())
+    hit = _first_packs.get(id(w))
+    if hit is None or hit[0] != key:
+        if torch.cuda.is_current_stream_capturing():
+            raise _lib.VcnError("frozen_nets: weight pack miss inside a CUDA graph capture (run one eager step first)")
+        k = ks * ks * 3
+        kp = (k + 15) // 16 * 16
+        wp = torch.zeros([kp, 64], dtype=torch.bfloat16, device=w.device)
+        wp[:k] = w.detach().permute(2, 3, 1, 0).reshape(k, 64).to(torch.bfloat16)
+        hit = (key, wp, b.detach().float().contiguous() if b is not None else None, w)
+        _first_packs[id(w)] = hit
+    _, wp, bias, _ = hit
+    oh, ow = (h + 2 * pad - ks) // stride + 1, (wd + 2 * pad - ks) // stride + 1
+    y = torch.empty([n, 64, oh, ow], dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    with torch.cuda.device(x.device):
+        st = _lib.load().vcn_conv_first3(_lib.ptr(x), _lib.ptr(wp), _lib.ptr(bias), _lib.ptr(y), _lib.dtype_code(x.dtype), ks, stride,
+                                         pad, int(relu), n, h, wd, _lib.current_stream(x.device))
+    _lib.check(st, "vcn_conv_first3")
+    return y
 # MaxPool2d(3, 2, 1) of the ResNet stem: "vcn" = csrc/frozen_ops.cu, "aten" = torch's NHWC kernels
 stem_pool_impl = os.environ.get("VCN_STEM_POOL", "vcn")
 
@@ -163,6 +189,10 @@ def _conv_fwd(x, w, b, stride, padding, relu=True, residual=None, impl="cudnn"):
         M.conv_igemm(xh, wt, _lib.CONV_FPROP, w.shape[0], 3, 3, out=out, epilogue=epi)
         del hold
         return out
+    if (first_layer_impl == "direct" and residual is None and x.shape[1] == 3 and w.shape[0] == 64 and x.dtype == torch.bfloat16
+            and ((w.shape[-1] == 3 and stride == (1, 1) and padding == (1, 1)) or (w.shape[-1] == 7 and stride == (2, 2) and padding == (3, 3)))
+            and x.is_contiguous(memory_format=torch.channels_last)):
+        return conv_first3(x, w, b, int(w.shape[-1]), int(stride[0]), int(padding[0]), relu)
     if (first_layer_impl == "vcn" and relu and residual is None and x.shape[1] < 8 and w.shape[-1] == 3 and stride == (1, 1)
             and padding == (1, 1) and w.shape[0] % 64 == 0 and x.dtype == torch.bfloat16):
         # 3-channel image -> 64 channels (VGG-16 conv1_1): cuDNN pads the input to 8 channels and runs a legacy sm80 kernel

@@ -167,6 +167,11 @@ class VisCoINTrainer:
         gan_params = list(self.viscoin_gan.mapping.parameters())
         main_params = list(itertools.chain(self.concept_extractor.parameters(), self.explainer.parameters()))
         # backward reaches the mapping network before Psi: register in forward order, buckets fill in reverse
+        if self.buckets_world() > 1 and self.device.type == "cuda":
+            # the all-reduce kernels own a few SMs while they run: keep the persistent GEMM grids off that many SMs so that
+            # no statically scheduled CTA waits for a collective to finish (bench.py caps NCCL at the same number of CTAs)
+            from .. import _lib
+            _lib.check(_lib.load().vcn_set_conv_sm_reserve(int(os.environ.get("VCN_DP_RESERVE_SMS", "8"))), "vcn_set_conv_sm_reserve")
         self.buckets = _dp.GradBuckets(main_params + gan_params, bucket_bytes=int(os.environ.get("VCN_DP_BUCKET_MB", "32")) << 20)
         fused = (self.device.type == "cuda") if fused_adam is None else fused_adam
         # capturable: step counters and lr live on the device, so the update can sit inside a CUDA graph (step_graphed)
@@ -179,6 +184,11 @@ class VisCoINTrainer:
         self.prefetch_fake = os.environ.get("VCN_PREFETCH_FAKE", "1") == "1"
         self.graph_launches = 0  # libvcn kernel launches replayed from graphs so far
         self._eager_calls = {}
+
+    @staticmethod
+    def buckets_world():
+        import torch.distributed as dist
+        return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
 
     def oracle_state(self):
         """CPU copies of every state_dict the oracle's ``step_losses`` needs (tests / parity tooling; needs keep_unfolded
