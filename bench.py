@@ -109,10 +109,9 @@ def dist_setup(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # the all-reduce runs under backward: few, long-lived NCCL CTAs (NVLink/NVSwitch needs no more) on SMs the persistent
-        # GEMM grids leave free (VisCoINTrainer reserves VCN_DP_RESERVE_SMS = 8)
-        if int(os.environ.get("VCN_DP_RESERVE_SMS", "8")) > 0:
-            os.environ.setdefault("NCCL_MAX_CTAS", os.environ.get("VCN_DP_RESERVE_SMS", "8"))
+        # opt-in SM partitioning (VCN_DP_RESERVE_SMS = k): NCCL capped at k CTAs on SMs the persistent GEMM grids leave free
+        if int(os.environ.get("VCN_DP_RESERVE_SMS", "0")) > 0:
+            os.environ.setdefault("NCCL_MAX_CTAS", os.environ["VCN_DP_RESERVE_SMS"])
         backend = "nccl" if torch.cuda.is_available() and args.impl == "ours" else "gloo"
         if torch.cuda.is_available():
             torch.cuda.set_device(local)

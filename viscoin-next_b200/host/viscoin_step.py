@@ -167,11 +167,12 @@ class VisCoINTrainer:
         gan_params = list(self.viscoin_gan.mapping.parameters())
         main_params = list(itertools.chain(self.concept_extractor.parameters(), self.explainer.parameters()))
         # backward reaches the mapping network before Psi: register in forward order, buckets fill in reverse
-        if self.buckets_world() > 1 and self.device.type == "cuda":
-            # the all-reduce kernels own a few SMs while they run: keep the persistent GEMM grids off that many SMs so that
-            # no statically scheduled CTA waits for a collective to finish (bench.py caps NCCL at the same number of CTAs)
+        if self.buckets_world() > 1 and self.device.type == "cuda" and int(os.environ.get("VCN_DP_RESERVE_SMS", "0")) > 0:
+            # opt-in SM partitioning: keep the persistent GEMM grids off the SMs the all-reduce kernels own while they run
+            # (bench.py caps NCCL at the same number of CTAs).  Measured on 2 B200s (profiles/r2p_dp_ab.txt): capping NCCL at
+            # 4 / 8 / 16 CTAs costs more (17.7 / 15.8 / 15.5 ms) than the contention it removes (15.4 ms unpartitioned) - off.
             from .. import _lib
-            _lib.check(_lib.load().vcn_set_conv_sm_reserve(int(os.environ.get("VCN_DP_RESERVE_SMS", "8"))), "vcn_set_conv_sm_reserve")
+            _lib.check(_lib.load().vcn_set_conv_sm_reserve(int(os.environ["VCN_DP_RESERVE_SMS"])), "vcn_set_conv_sm_reserve")
         self.buckets = _dp.GradBuckets(main_params + gan_params, bucket_bytes=int(os.environ.get("VCN_DP_BUCKET_MB", "32")) << 20)
         fused = (self.device.type == "cuda") if fused_adam is None else fused_adam
         # capturable: step counters and lr live on the device, so the update can sit inside a CUDA graph (step_graphed)
