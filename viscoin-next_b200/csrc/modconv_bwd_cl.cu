@@ -290,6 +290,84 @@ __global__ void __launch_bounds__(256, 3) modconv_bwd_cl_bulk_kernel(const BwdCl
   if (!FINISH && a.sum_c) group_reduce_add(red, acc1, tid, groups, rows, a.sum_c, a.c);
 }
 
+// ---- fused backward of a ToRGB layer (1x1 modulated convolution to <= 4 channels, no demodulation; networks.py:307-323) ----
+//   dxhat[n,p,c] = sum_o W[o,c] * dy0[n,p,o]      (the input-gradient "GEMM" is a rank-<=4 expansion: memory-bound)
+//   dx[n,p,c]    = dxhat * s[n,c]                  dsum[n,c] = sum_p dxhat * x[n,p,c]
+// One pass over x (read) and dx (write) instead of GEMM (write dxhat) + finish (read dxhat, x; write dx).  Same ring as above:
+// a stage = 2 * rows pixels of x (8 KB) plus their 16-byte dy0 rows.
+template <typename T>
+__global__ void __launch_bounds__(256, 3) torgb_bwd_bulk_kernel(const T* __restrict__ x, const __nv_bfloat16* __restrict__ dy0,
+                                                                const float* __restrict__ wgt, const float* __restrict__ styles,
+                                                                T* __restrict__ dx, float* __restrict__ dsum, int n_, int c,
+                                                                int hw, int cout, int chunk) {
+  extern __shared__ __align__(128) unsigned char ring[];  // [kStagesBulk][kStageTensorBytes + 1024]
+  __shared__ float red[256][8];
+  __shared__ __align__(8) uint64_t full_bar[kStagesBulk];
+  constexpr uint32_t kStage = kStageTensorBytes + 1024;   // x rows + up to 64 dy0 rows of 16 bytes
+  const int tid = threadIdx.x, n = blockIdx.y;
+  const int groups = c >> 3, rows = 256 / groups;
+  const int g = tid % groups, row = tid / groups;
+  const int c0 = g * 8;
+  const int p0 = blockIdx.x * chunk, p_end = min(hw, p0 + chunk);
+  const int sp = 2 * rows;
+  const int nit = (p_end - p0 + sp - 1) / sp;
+  const uint32_t row_bytes = (uint32_t)c * 2u;
+  const unsigned char* gx = reinterpret_cast<const unsigned char*>(x) + ((int64_t)n * hw + p0) * row_bytes;
+  const unsigned char* gd = reinterpret_cast<const unsigned char*>(dy0) + ((int64_t)n * hw + p0) * 16;
+  auto fill = [&](int it) {
+    const int s = it % kStagesBulk;
+    const int px = min(sp, p_end - p0 - it * sp);
+    unsigned char* dst = ring + (size_t)s * kStage;
+    mbar_expect_tx(full_bar + s, (uint32_t)px * (row_bytes + 16u));
+    bulk_load_1d(dst, gx + (int64_t)it * sp * row_bytes, (uint32_t)px * row_bytes, full_bar + s);
+    bulk_load_1d(dst + kStageTensorBytes, gd + (int64_t)it * sp * 16, (uint32_t)px * 16u, full_bar + s);
+  };
+  if (tid == 0) {
+    for (int s = 0; s < kStagesBulk; ++s) mbar_init(full_bar + s, 1);
+    fence_mbar_init();
+    for (int it = 0; it < min(nit, kStagesBulk); ++it) fill(it);
+  }
+  float wv[4][8], sc[8], acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sc[k] = styles ? styles[(int64_t)n * c + c0 + k] : 1.f;
+    acc[k] = 0.f;
+#pragma unroll
+    for (int o = 0; o < 4; ++o) wv[o][k] = o < cout ? wgt[(int64_t)o * c + c0 + k] : 0.f;
+  }
+  __syncthreads();
+  for (int it = 0; it < nit; ++it) {
+    const int s = it % kStagesBulk;
+    mbar_wait(full_bar + s, (uint32_t)(it / kStagesBulk) & 1u);
+    const unsigned char* sa = ring + (size_t)s * kStage;
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int pl = row + b * rows;
+      const int p = p0 + it * sp + pl;
+      if (p < p_end) {
+        const Vec16<T> xv = *reinterpret_cast<const Vec16<T>*>(sa + (size_t)pl * row_bytes + g * 16);
+        const uint2 dv = *reinterpret_cast<const uint2*>(sa + kStageTensorBytes + (size_t)pl * 16);  // channels 0..3 of dy0
+        const float d0 = __uint_as_float(dv.x << 16), d1 = __uint_as_float(dv.x & 0xffff0000u);
+        const float d2 = __uint_as_float(dv.y << 16), d3 = __uint_as_float(dv.y & 0xffff0000u);
+        Vec16<T> o;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float t = fmaf(wv[0][k], d0, fmaf(wv[1][k], d1, fmaf(wv[2][k], d2, wv[3][k] * d3)));
+          acc[k] = fmaf(t, to_acc<T>(xv.v[k]), acc[k]);
+          o.v[k] = from_acc<T>(t * sc[k]);
+        }
+        st_stream<T>(dx + ((int64_t)n * hw + p) * c + c0, o);
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && it + kStagesBulk < nit) {
+      fence_proxy_async();
+      fill(it + kStagesBulk);
+    }
+  }
+  if (dsum) group_reduce_add(red, acc, tid, groups, rows, dsum + (int64_t)n * c, c);
+}
+
 // dense [n,h,w,c_pad] 16-bit tensor with c == c_pad, 16-byte aligned
 inline bool dense_nhwc(const void* p, const int64_t s[4], int c, int c_pad, int h, int w) {
   return c == c_pad && s[1] == 1 && s[3] == c_pad && s[2] == (int64_t)w * c_pad && s[0] == (int64_t)h * w * c_pad &&
@@ -404,4 +482,37 @@ extern "C" int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, 
   a.scale = styles; a.sum_nc = dsum;
   a.n = n; a.c = c; a.c_pad = c_pad; a.h = h; a.w = w;
   return launch<true>(a, dtype, static_cast<cudaStream_t>(stream), "modconv_bwd_finish_cl_kernel");
+}
+
+extern "C" int vcn_torgb_bwd_fused(const void* x, const void* dy0, const float* wgt, const float* styles, void* dx, float* dsum,
+                                   int dtype, int n, int c, int h, int w, int cout, void* stream) {
+  using namespace vcn;
+  VCN_REQUIRE(dtype == VCN_BF16, "torgb_bwd_fused: x / dx must be bf16 channels-last");
+  VCN_REQUIRE(n >= 0 && h >= 1 && w >= 1 && cout >= 1 && cout <= 4, "torgb_bwd_fused: 1..4 output channels (got %d)", cout);
+  const int groups = c >> 3;
+  VCN_REQUIRE(c >= 64 && c % 8 == 0 && groups <= 256 && (groups & (groups - 1)) == 0,
+              "torgb_bwd_fused: channels (%d) must be a power of two in [64, 2048]", c);
+  if (n == 0) return VCN_OK;
+  VCN_REQUIRE(x && dy0 && wgt && dx && aligned16(x) && aligned16(dy0) && aligned16(dx), "torgb_bwd_fused: NULL / misaligned pointer");
+  const int hw = h * w;
+  const int rows = 256 / groups, sp = 2 * rows;
+  int per_sample = (sm_count() * 3) / n;
+  if (per_sample < 1) per_sample = 1;
+  int chunk = (hw + per_sample - 1) / per_sample;
+  chunk = (chunk + sp - 1) / sp * sp;
+  if (chunk < 4 * sp) chunk = 4 * sp;
+  dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)n);
+  const size_t smem = (size_t)kStagesBulk * (kStageTensorBytes + 1024);
+  auto kern = torgb_bwd_bulk_kernel<__nv_bfloat16>;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  VCN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  kern<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy0),
+                                                               wgt, styles, static_cast<__nv_bfloat16*>(dx), dsum, n, c, hw, cout, chunk);
+  VCN_LAUNCH_CHECK("torgb_bwd_bulk_kernel");
+  return VCN_OK;
 }

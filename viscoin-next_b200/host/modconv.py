@@ -202,6 +202,25 @@ def bwd_pack(dy, y, epilogue, want_gsum, want_db, out_dtype=torch.bfloat16):
     return dy0, gsum, db
 
 
+torgb_fused = os.environ.get("VCN_TORGB_FUSED", "1") == "1"
+
+
+def torgb_bwd_fused(x, dy0, weight, styles, want_dsum):
+    """vcn_torgb_bwd_fused: (dx bf16 channels_last like x, dsum [N,C] or None) from the packed ToRGB gradient rows dy0 [N,H,W,8]."""
+    lib = _lib.load()
+    n, c, h, w = x.shape
+    cout = weight.shape[0]
+    wgt = weight.detach().reshape(cout, c).to(torch.float32).contiguous()
+    dx = torch.empty_like(x, memory_format=torch.channels_last)
+    dsum = torch.zeros([n, c], dtype=torch.float32, device=x.device) if want_dsum else None
+    assert dy0.dtype == torch.bfloat16 and tuple(dy0.shape) == (n, h, w, 8) and dy0.is_contiguous()
+    with torch.cuda.device(x.device):
+        st = lib.vcn_torgb_bwd_fused(_lib.ptr(x), _lib.ptr(dy0), _lib.ptr(wgt), _lib.ptr(styles), _lib.ptr(dx), _lib.ptr(dsum),
+                                     _lib.dtype_code(x.dtype), n, c, h, w, cout, _lib.current_stream(x.device))
+    _lib.check(st, "vcn_torgb_bwd_fused")
+    return dx, dsum
+
+
 def bwd_finish(dxhat, x, styles, want_dsum):
     """vcn_modconv_bwd_finish: dxhat (fp32) *= s in place; returns dsum [N,C] = sum_p dxhat*x (or None)."""
     lib = _lib.load()
@@ -370,7 +389,15 @@ class _ModConvLayer(torch.autograd.Function):
             dz = _upfirdn2d.launch(dy0.permute(0, 3, 1, 2), f, 1, 1, 1, 1, 2, 2, 2, 2, True, 4.0)
             dz = dz.permute(0, 2, 3, 1)
             assert dz.is_contiguous()
-        if need_x or need_s:
+        fused_rgb = (torgb_fused and resident and up == 1 and kh == 1 and kw == 1 and cout <= 4 and op == torch.bfloat16 and not demodulate
+                     and x.dtype == torch.bfloat16 and cin >= 64 and cin & (cin - 1) == 0 and x.is_contiguous(memory_format=torch.channels_last)
+                     and n * h * w * cin >= (1 << 21))
+        if fused_rgb and (need_x or need_s):
+            # ToRGB: the input-gradient GEMM is a rank-<=4 expansion - one streaming pass (vcn_torgb_bwd_fused)
+            dx, ds = torgb_bwd_fused(x, dy0, weight, styles32, need_s and styles32 is not None)
+            if not need_x:
+                dx = None
+        elif need_x or need_s:
             if up == 1:
                 wt_t, _ = _packed(weight, True, False, False, op)
                 kind = _lib.CONV_DGRAD if flip_weight else _lib.CONV_FPROP
