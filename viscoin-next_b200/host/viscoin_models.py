@@ -205,14 +205,18 @@ class LPIPS(nn.Module):
         f = f.float()
         return f / ((f.square().sum(dim=1, keepdim=True) + 1e-30).sqrt() + eps)
 
-    def forward(self, in0, in1):
+    def forward(self, in0, in1, target_features=None):
         """in0: the image that may carry a gradient (rebuilt), in1: the target.  On a CUDA device each tap's distance is
         ONE fused kernel forward and one backward (lpips_tap) instead of ~20 full-size fp32 elementwise passes; the
-        target's features are computed without a graph."""
+        target's features are computed without a graph (or passed in: `target_features = self.features(in1)` computed
+        earlier, e.g. on a side stream - they depend on nothing but the target images)."""
         if in0.is_cuda and self.fused:
             from . import lpips_tap as _tap
-            with torch.no_grad():
-                f1 = self.features(in1)
+            if target_features is not None:
+                f1 = target_features
+            else:
+                with torch.no_grad():
+                    f1 = self.features(in1)
             f0 = self.features(in0)
             val = 0
             for k in range(len(f0)):

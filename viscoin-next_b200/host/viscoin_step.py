@@ -181,6 +181,8 @@ class VisCoINTrainer:
         self.gan_optimizer = torch.optim.Adam(gan_params, lr=lr, fused=fused, capturable=cap)
         self.optimizer = torch.optim.Adam(main_params, lr=lr, fused=fused, capturable=cap)
         self._graphs = {}
+        self.lpips_side_stream = os.environ.get("VCN_LPIPS_SIDE_STREAM", "0") == "1" and self.device.type == "cuda"
+        self._lpips_stream = None
         self._z_ahead = {}  # per graph key: the z already drawn for the next iteration (step_graphed's generator pipelining)
         self.prefetch_fake = os.environ.get("VCN_PREFETCH_FAKE", "1") == "1"
         self.graph_launches = 0  # libvcn kernel launches replayed from graphs so far
@@ -226,6 +228,22 @@ class VisCoINTrainer:
         if fake_images is None:
             fake_images = synthetic_samples(self.generator_gan, len(real_images), self.device, z_generator)
         all_images = torch.cat([real_images, fake_images.to(real_images.dtype)])
+        target_feats = None
+        if self.lpips_side_stream and all_images.is_cuda and getattr(self.lpips, "fused", False):
+            # (opt-in; measured neutral on one B200, profiles/r2r_ab.txt: 14.58 vs 14.59 ms - the single-stream graph leaves no
+            # idle SMs worth filling)
+            # The LPIPS features of the TARGET images depend on nothing but the images: a second stream computes them (16 images
+            # through VGG-16, dense convolutions) while this one walks f -> Psi -> Theta -> mapping -> the low-resolution
+            # synthesis layers, a chain of short launches that leaves SMs idle between and inside kernels.
+            if self._lpips_stream is None:
+                self._lpips_stream = torch.cuda.Stream(device=self.device)
+            main = torch.cuda.current_stream(self.device)
+            self._lpips_stream.wait_stream(main)
+            with torch.cuda.stream(self._lpips_stream), torch.no_grad():
+                src = all_images.contiguous(memory_format=torch.channels_last) if self.channels_last else all_images
+                target_feats = self.lpips.features(src)
+                for t in target_feats:
+                    t.record_stream(main)
         classes, hidden = self._f(all_images)
         with torch.autocast("cuda", dtype=self.amp_psi or torch.bfloat16, enabled=self.amp_psi is not None):
             if self.amp_psi is None and self.amp is not None:
@@ -241,9 +259,12 @@ class VisCoINTrainer:
         rebuilt_images, gan_latents = self.viscoin_gan(z1=encoded_concepts, z2=extra_info, return_latents=True,
                                                        **self.synthesis_kwargs)
         rebuilt_classes, _ = self._f(rebuilt_images)
+        if target_feats is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._lpips_stream)
         with self._autocast():
             lp = lambda a, b: self.lpips(a.contiguous(memory_format=torch.channels_last) if self.channels_last else a,
-                                         b.contiguous(memory_format=torch.channels_last) if self.channels_last else b)
+                                         b.contiguous(memory_format=torch.channels_last) if self.channels_last else b,
+                                         **({"target_features": target_feats} if target_feats is not None else {}))
             losses["rec"] = reconstruction_loss(rebuilt_images, all_images, rebuilt_classes, classes, lp, p.gamma, p.beta)
         losses["gan"] = gan_regularization_loss(gan_latents, self.viscoin_gan)
         return losses
