@@ -242,6 +242,17 @@ int vcn_maxpool2x2_fwd(const void* x, void* y, int dtype, int n, int h, int w, i
  * reference reaches it through transformers' ResNetModel, viscoin/models/classifiers.py:83-92): x [n,h,w,c] -> y [n,oh,ow,c],
  * oh = (h-1)/2+1.  idx (may be NULL when no backward follows) = one byte per output element: the winning window position
  * dy*3+dx, first maximum in scan order (ATen's max_pool2d_with_indices).  _bwd: gx [n,h,w,c] from gy [n,oh,ow,c] and idx. */
+/* Fused elementwise passes over the [n,3,h,w] fp32 images of the iteration (csrc/image_ops.cu).
+ *   vcn_image_prep_fwd  y[n,h,w,3] bf16 = (x - shift[c]) * inv_scale[c]  (NULL shift / inv_scale = 0 / 1): the input conversion of
+ *                       the frozen f and LPIPS's ScalingLayer (lpips v0.1.4; viscoin/training/losses.py:111-123)
+ *   vcn_image_prep_bwd  gx[n,3,h,w] fp32 = gy[n,h,w,3] * inv_scale[c]
+ *   vcn_l1l2_fwd        out2[0] += sum |a-b|, out2[1] += sum (a-b)^2  (out2 zeroed by the caller; losses.py:125-157 L1 + L2 terms)
+ *   vcn_l1l2_bwd        ga = g2[0] * sign(a-b) + 2 * g2[1] * (a-b), g2 = device pointer to the two upstream scale factors */
+int vcn_image_prep_fwd(const float* x, void* y, const float* shift, const float* inv_scale, int n, int h, int w, void* stream);
+int vcn_image_prep_bwd(const void* gy, float* gx, const float* inv_scale, int n, int h, int w, void* stream);
+int vcn_l1l2_fwd(const float* a, const float* b, float* out2, int64_t numel, void* stream);
+int vcn_l1l2_bwd(const float* a, const float* b, const float* g2, float* ga, int64_t numel, void* stream);
+
 /* First convolution of a frozen image network: 3 -> 64 channels, 3x3/stride 1/pad 1 (VGG-16 conv1_1, lpips v0.1.4 through
  * viscoin/training/losses.py:111-123) or 7x7/stride 2/pad 3 (the ResNet stem, viscoin/models/classifiers.py:83-92), bias
  * (+ ReLU), bf16 channels-last: x [n,h,w,3], y [n,oh,ow,64].  wp = the weight re-laid out as [KP][64] bf16 with

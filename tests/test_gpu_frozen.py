@@ -213,3 +213,29 @@ def test_fused_vgg_taps_and_lpips_gradient(impl):
     e_v, e_g = abs(float(got) - float(want)) / abs(float(want)), _rel2(ga, ga_ref)
     print("FusedVGG[%s]: taps %s value %.2e d(img) rel-L2 %.2e" % (impl, ["%.1e" % e for e in e_taps], e_v, e_g))
     assert max(e_taps) <= 3e-2 and e_v <= 2e-2 and e_g <= 1.5e-1
+
+
+def test_image_prep_and_l1l2_match_torch():
+    """csrc/image_ops.cu: (x - shift) / scale -> bf16 channels_last and its adjoint; mean |a-b|, mean (a-b)^2 and their gradient."""
+    from viscoin_next_b200.host import image_ops as io
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(3, 3, 37, 52, device="cuda", generator=gen).requires_grad_(True)
+    shift = torch.tensor([-0.030, -0.088, -0.188], device="cuda")
+    scale = torch.tensor([0.458, 0.448, 0.450], device="cuda")
+    y = io.image_prep(x, shift, 1.0 / scale)
+    ref = ((x.detach() - shift.view(1, 3, 1, 1)) / scale.view(1, 3, 1, 1)).bfloat16()
+    assert y.is_contiguous(memory_format=torch.channels_last) and _rel(y, ref) <= 8e-3  # 1 bf16 ulp: (x-s)*(1/c) vs (x-s)/c
+    gy = torch.randn(3, 3, 37, 52, device="cuda", generator=gen).bfloat16()
+    y.backward(gy)
+    assert _rel(x.grad, gy.float() / scale.view(1, 3, 1, 1)) <= 1e-6
+    assert torch.equal(io.image_prep(x.detach()), x.detach().bfloat16())
+    a = torch.randn(4, 3, 64, 64, device="cuda", generator=gen).requires_grad_(True)
+    b = torch.randn(4, 3, 64, 64, device="cuda", generator=gen)
+    a2 = a.detach().clone().requires_grad_(True)
+    v = io.l1_l2(a, b)
+    d = a2 - b
+    vr = torch.stack([d.abs().mean(), d.square().mean()])
+    assert _rel(v, vr) <= 1e-5
+    (v[0] * 0.7 + v[1] * 1.3).backward()
+    (vr[0] * 0.7 + vr[1] * 1.3).backward()
+    assert _rel(a.grad, a2.grad) <= 1e-5

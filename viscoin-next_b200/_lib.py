@@ -72,6 +72,10 @@ SIGNATURES = {
     "vcn_conv_wgrad": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "vcn_demod_grad": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
     "vcn_maxpool2x2_fwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "vcn_image_prep_fwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "vcn_image_prep_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "vcn_l1l2_fwd": (_i, [_vp, _vp, _vp, _i64, _vp]),
+    "vcn_l1l2_bwd": (_i, [_vp, _vp, _vp, _vp, _i64, _vp]),
     "vcn_conv_first3": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "vcn_maxpool3x3s2_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_maxpool3x3s2_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),

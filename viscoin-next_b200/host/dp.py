@@ -62,6 +62,20 @@ class GradBuckets:
             flat.zero_()
         self._pending = [len(m) for m in self.members]
         self._handles = []
+        self._fresh = set(self.params)  # parameters whose slice still holds the zeros written by reset()
+
+    def deposit(self, p, g):
+        """Hand over the gradient of `p` from outside autograd's accumulation (psi_fast._ShadowWeight): `g` may have another
+        dtype / memory format; the first contribution of a step is written into the (zeroed) bucket slice with one fused
+        cast-copy, later ones are added.  The caller's backward returns None for `p`: autograd still runs the parameter's
+        AccumulateGrad node (a no-op on an undefined gradient) and fires the post-accumulate hook AFTER this call - that hook is
+        the parameter's arrival for the bucket's all-reduce, exactly as on the ordinary path."""
+        with torch.no_grad():
+            if p in self._fresh:
+                self._fresh.discard(p)
+                p.grad.copy_(g)
+            else:
+                p.grad.add_(g.to(p.grad.dtype))
 
     def _on_grad(self, p):
         b = self._bucket_of[p]

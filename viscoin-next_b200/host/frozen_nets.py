@@ -29,6 +29,7 @@ import torch
 import torch.nn.functional as F
 
 from .. import _lib
+from . import image_ops as _image_ops
 
 
 def _cl(t):
@@ -64,6 +65,7 @@ _weights = _WeightCache()
 # operand staging.
 first_layer_impl = os.environ.get("VCN_VGG_FIRST", "direct")
 _first_packs = {}
+fused_image_ops = os.environ.get("VCN_FUSED_IMAGE_OPS", "1") == "1"
 
 
 def conv_first3(x, w, b, ks, stride, pad, relu=True):
@@ -246,9 +248,28 @@ class _ConvReLU(torch.autograd.Function):
         return dx, None, None, dres, None, None, None
 
 
-def conv_relu(x, conv, relu=True, residual=None):
-    """`conv`: a frozen torch.nn.Conv2d with bias (BatchNorm already folded).  Differentiable w.r.t. x / residual only."""
-    w, b = _weights.get(conv.weight), _weights.get(conv.bias)
+_bias_sums = {}
+
+
+def _summed_bias(p, q):
+    """bf16(p + q) of two frozen bias vectors, cached per parameter versions."""
+    key = (id(p), id(q))
+    ver = (p._version, q._version, p.data_ptr(), q.data_ptr())
+    hit = _bias_sums.get(key)
+    if hit is None or hit[0] != ver:
+        if p.is_cuda and torch.cuda.is_current_stream_capturing():
+            raise _lib.VcnError("frozen_nets: bias cache miss inside a CUDA graph capture (run one eager step first)")
+        with torch.no_grad():
+            hit = (ver, (p.detach().float() + q.detach().float()).to(torch.bfloat16), p, q)
+        _bias_sums[key] = hit
+    return hit[1]
+
+
+def conv_relu(x, conv, relu=True, residual=None, no_bias=False, add_bias_of=None):
+    """`conv`: a frozen torch.nn.Conv2d with bias (BatchNorm already folded).  Differentiable w.r.t. x / residual only.
+    no_bias: leave the bias out (it is added by the consumer); add_bias_of: another frozen conv whose bias is added too."""
+    w = _weights.get(conv.weight)
+    b = None if no_bias else (_weights.get(conv.bias) if add_bias_of is None else _summed_bias(conv.bias, add_bias_of.bias))
     stride, padding = tuple(conv.stride), tuple(conv.padding)
     if torch.is_grad_enabled() and (x.requires_grad or (residual is not None and residual.requires_grad)):
         return _ConvReLU.apply(x, w, b, residual, stride, padding, relu)
@@ -274,14 +295,21 @@ class FusedResNet:
         if len(convs) != 3:
             raise _lib.VcnError("FusedResNet: only bottleneck layers are implemented")
         sc = layer.shortcut
-        res = x if isinstance(sc, torch.nn.Identity) else conv_relu(x, sc.convolution, relu=False)
+        proj = not isinstance(sc, torch.nn.Identity)
+        # projection shortcut: its output only ever meets the third convolution's fused (+ residual, + bias, ReLU) epilogue,
+        # so its bias rides along there (b3 + b_sc, summed once in fp32) instead of costing a separate bias-add pass per call
+        res = conv_relu(x, sc.convolution, relu=False, no_bias=True) if proj else x
         h = conv_relu(x, convs[0].convolution)
         h = conv_relu(h, convs[1].convolution)
-        return conv_relu(h, convs[2].convolution, relu=True, residual=res)  # += residual, then the block's ReLU
+        return conv_relu(h, convs[2].convolution, relu=True, residual=res,  # += residual, then the block's ReLU
+                         add_bias_of=sc.convolution if proj else None)
 
     def __call__(self, images):
         r = self.m.resnet
-        x = _cl(images.to(torch.bfloat16))
+        if fused_image_ops and _image_ops.supported(images):
+            x = _image_ops.image_prep(images)  # fp32 NCHW -> bf16 channels_last in one pass (and one pass back)
+        else:
+            x = _cl(images.to(torch.bfloat16))
         x = conv_relu(x, r.embedder.embedder.convolution)
         pool = r.embedder.pooler
         if (stem_pool_impl == "vcn" and isinstance(pool, torch.nn.MaxPool2d) and pool.kernel_size in (3, (3, 3)) and pool.stride in (2, (2, 2))
@@ -387,10 +415,20 @@ class FusedVGGFeatures:
             plan.append("t")
         self.plan, self.convs = tuple(plan), convs
 
+    def _shift_scale(self):
+        lp = self.lpips
+        key = (lp.shift._version, lp.scale._version, lp.shift.data_ptr())
+        if getattr(self, "_ss", None) is None or self._ss[0] != key:
+            self._ss = (key, lp.shift.detach().reshape(3).float().contiguous(), (1.0 / lp.scale.detach().reshape(3).float()).contiguous())
+        return self._ss[1], self._ss[2]
+
     def __call__(self, x):
         """x: fp32 / bf16 [N,3,H,W] image batch -> list of 5 bf16 channels_last feature maps."""
         lp = self.lpips
-        x = _cl(((x.float() - lp.shift) / lp.scale).to(torch.bfloat16))
+        if fused_image_ops and _image_ops.supported(x):
+            x = _image_ops.image_prep(x, self._shift_scale()[0], self._shift_scale()[1])
+        else:
+            x = _cl(((x.float() - lp.shift) / lp.scale).to(torch.bfloat16))
         wb = []
         for c in self.convs:
             wb += [_weights.get(c.weight), _weights.get(c.bias)]

@@ -22,8 +22,13 @@ import torch
 import torch.nn.functional as F
 
 from . import dp as _dp
+from . import image_ops as _image_ops
 from . import networks as _networks
+from . import psi_fast as _psi_fast
 from . import viscoin_models as _models
+
+
+fused_image_ops = os.environ.get("VCN_FUSED_IMAGE_OPS", "1") == "1"
 
 
 # ---- losses (viscoin/training/losses.py) ------------------------------------------------------------------------------
@@ -58,8 +63,12 @@ def output_fidelity_loss(original_classes, explainer_classes):
 def reconstruction_loss(reconstructed, original, reconstructed_classes, original_classes, lpips_net, lambda_classes=0.1,
                         lambda_lpips=3.0):
     """losses.py:125-157.  L1 and L2 share one pass over the difference."""
-    diff = reconstructed.float() - original.float()
-    return (diff.abs().mean() + diff.square().mean()
+    if fused_image_ops and _image_ops.l1_l2_supported(reconstructed, original):
+        l12 = _image_ops.l1_l2(reconstructed, original).sum()  # one pass forward, one backward (csrc/image_ops.cu)
+    else:
+        diff = reconstructed.float() - original.float()
+        l12 = diff.abs().mean() + diff.square().mean()
+    return (l12
             + lambda_classes * cross_cross_entropy_loss(reconstructed_classes, original_classes.detach())
             + lambda_lpips * lpips_net(reconstructed, original).mean())
 
@@ -181,6 +190,7 @@ class VisCoINTrainer:
         self.gan_optimizer = torch.optim.Adam(gan_params, lr=lr, fused=fused, capturable=cap)
         self.optimizer = torch.optim.Adam(main_params, lr=lr, fused=fused, capturable=cap)
         self._graphs = {}
+        self.psi_fast = os.environ.get("VCN_PSI_FAST", "1") == "1" and self.device.type == "cuda"
         self.lpips_side_stream = os.environ.get("VCN_LPIPS_SIDE_STREAM", "0") == "1" and self.device.type == "cuda"
         self._lpips_stream = None
         self._z_ahead = {}  # per graph key: the z already drawn for the next iteration (step_graphed's generator pipelining)
@@ -240,15 +250,20 @@ class VisCoINTrainer:
             main = torch.cuda.current_stream(self.device)
             self._lpips_stream.wait_stream(main)
             with torch.cuda.stream(self._lpips_stream), torch.no_grad():
-                src = all_images.contiguous(memory_format=torch.channels_last) if self.channels_last else all_images
+                src = all_images
                 target_feats = self.lpips.features(src)
                 for t in target_feats:
                     t.record_stream(main)
         classes, hidden = self._f(all_images)
-        with torch.autocast("cuda", dtype=self.amp_psi or torch.bfloat16, enabled=self.amp_psi is not None):
-            if self.amp_psi is None and self.amp is not None:
-                hidden = [h.float() for h in hidden[-3:]]
-            encoded_concepts, extra_info = self.concept_extractor(hidden[-3:])
+        if (self.psi_fast and self.amp_psi == torch.bfloat16 and torch.is_grad_enabled()
+                and _psi_fast.supported(self.concept_extractor, hidden[-3:])):
+            # explicit bf16 path: one-pass weight shadows, gradients deposited straight into the flat buckets (psi_fast.py)
+            encoded_concepts, extra_info = _psi_fast.forward(self.concept_extractor, hidden[-3:], self.buckets)
+        else:
+            with torch.autocast("cuda", dtype=self.amp_psi or torch.bfloat16, enabled=self.amp_psi is not None):
+                if self.amp_psi is None and self.amp is not None:
+                    hidden = [h.float() for h in hidden[-3:]]
+                encoded_concepts, extra_info = self.concept_extractor(hidden[-3:])
         encoded_concepts, extra_info = encoded_concepts.float(), extra_info.float()
         explainer_classes = self.explainer(encoded_concepts)
         losses = {"acc": F.cross_entropy(classes[: len(labels)], labels)}
@@ -262,8 +277,10 @@ class VisCoINTrainer:
         if target_feats is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._lpips_stream)
         with self._autocast():
-            lp = lambda a, b: self.lpips(a.contiguous(memory_format=torch.channels_last) if self.channels_last else a,
-                                         b.contiguous(memory_format=torch.channels_last) if self.channels_last else b,
+            # the fused feature stack converts layout and dtype itself (one pass, image_ops.image_prep)
+            pre_cl = self.channels_last and getattr(self.lpips, "feature_fn", None) is None
+            lp = lambda a, b: self.lpips(a.contiguous(memory_format=torch.channels_last) if pre_cl else a,
+                                         b.contiguous(memory_format=torch.channels_last) if pre_cl else b,
                                          **({"target_features": target_feats} if target_feats is not None else {}))
             losses["rec"] = reconstruction_loss(rebuilt_images, all_images, rebuilt_classes, classes, lp, p.gamma, p.beta)
         losses["gan"] = gan_regularization_loss(gan_latents, self.viscoin_gan)
