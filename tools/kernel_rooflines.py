@@ -132,7 +132,20 @@ def collect(device, peaks, time_fn, iters=10, include_cudnn=True, n=8):
     epi3, hold3 = M.make_epilogue(bias=rn(3), act="linear", clamp=256.0)
     hbm("modconv_bwd_pack_smallc_kernel<float,bf16> ToRGB [%d,3,256,256] fp32 NCHW -> bf16 NHWC8" % n2,
         lambda: M.bwd_pack(dimg, yimg, epi3, False, True), (2 * dimg.numel() * 4 + n2 * 65536 * 16), key="modconv_bwd_pack_smallc")
-    del ycl, dycl, dimg, yimg, hold3
+    xr = ycl
+    dy0r = rn(n2, 256, 256, 8).bfloat16()
+    w3 = rn(3, 128, 1, 1)
+    hbm("torgb_bwd_bulk_kernel<bf16> fused ToRGB backward [%d,128,256,256] bf16 NHWC (read x, write dx)" % n2,
+        lambda: M.torgb_bwd_fused(xr, dy0r, w3, d, True), 2 * xr.numel() * 2 + dy0r.numel() * 2, key="torgb_bwd_fused")
+    import viscoin_next_b200.host.frozen_nets as fz
+    img = rn(n2, 3, 256, 256).bfloat16().contiguous(memory_format=torch.channels_last)
+    for ks, st_, pd in [(3, 1, 1), (7, 2, 3)]:
+        wf = (rn(64, 3, ks, ks) / ks).bfloat16().contiguous(memory_format=torch.channels_last)
+        bf = rn(64).bfloat16()
+        oh = (256 + 2 * pd - ks) // st_ + 1
+        hbm("first_conv_kernel<%d,%d> 3->64 ch + bias + ReLU [%d,3,256,256] bf16 NHWC (write-bound)" % (ks, st_, n2),
+            lambda: fz.conv_first3(img, wf, bf, ks, st_, pd, True), n2 * oh * oh * 64 * 2 + img.numel() * 2, key="first_conv_%d" % ks)
+    del ycl, dycl, dimg, yimg, hold3, xr, dy0r, img
 
     # ---- the convolutions: vcn_conv_igemm vs cuDNN on the layer shapes of SURVEY App. A (res >= 64: 91 % of the FLOPs) ---
     def cudnn_ms(kind, xin, w):

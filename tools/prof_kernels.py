@@ -162,3 +162,19 @@ if "torgb" in what:
     dimg, yimg = torch.randn(n, 3, 256, 256, device=dev), torch.randn(n, 3, 256, 256, device=dev)
     epi3, hold3 = M.make_epilogue(bias=torch.randn(3, device=dev), act="linear", clamp=256.0)
     timed("bwd_pack small-c ToRGB f32 [16,3,256,256]", lambda: M.bwd_pack(dimg, yimg, epi3, False, True), 2 * dimg.numel() * 4 + n * 65536 * 16, "GB/s")
+
+    xr = torch.randn(n, 128, 256, 256, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    dy0r = torch.randn(n, 256, 256, 8, device=dev).bfloat16()
+    w3 = torch.randn(3, 128, 1, 1, device=dev)
+    s3 = torch.rand(n, 128, device=dev) + 0.5
+    timed("torgb_bwd_fused bf16 [16,128,256,256]", lambda: M.torgb_bwd_fused(xr, dy0r, w3, s3, True), 2 * xr.numel() * 2 + dy0r.numel() * 2, "GB/s")
+
+if "first" in what:
+    import viscoin_next_b200.host.frozen_nets as fz
+    img = torch.randn(16, 3, 256, 256, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    for ks, st_, pd in [(3, 1, 1), (7, 2, 3)]:
+        w = (torch.randn(64, 3, ks, ks, device=dev) / ks).bfloat16().contiguous(memory_format=torch.channels_last)
+        bb = torch.randn(64, device=dev).bfloat16()
+        oh = (256 + 2 * pd - ks) // st_ + 1
+        timed("conv_first3 %dx%d/s%d bf16 [16,3,256,256]->64ch" % (ks, ks, st_), lambda: fz.conv_first3(img, w, bb, ks, st_, pd, True),
+              16 * oh * oh * 64 * 2 + img.numel() * 2, "GB/s")

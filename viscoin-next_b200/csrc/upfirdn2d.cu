@@ -1066,7 +1066,15 @@ TileGeom make_geom(const UpfirdnArgs& a, int up, int down) {
       g.tw = bw; g.tx = btx; g.th = bh; g.ty = bh / kMR;
     }
   }
-  g.tp = max_threads / (g.tx * g.ty);
+  // down = 2, fp32 (pattern B': FIR + decimation, the backward of the RGB up-sampling and the discriminator-side down-sampling):
+  // a 32 x 32 output tile stages 66 x 66 inputs - the register-staged path STG 2 with 64 of the 256 threads filtering (the
+  // 4-byte cp.async path it replaces was issue-bound at 128 threads: 0.33 of the HBM peak)
+  bool reg_down2 = false;
+  if (sizeof(T) == 4 && up == 1 && down == 2 && a.out_w >= 32 && a.out_h >= 32) {
+    g.tw = 32; g.tx = 32 / MC; g.th = 32; g.ty = 32 / kMR;
+    reg_down2 = true;
+  }
+  g.tp = reg_down2 ? 1 : max_threads / (g.tx * g.ty);
   const int planes = a.n * a.c;
   while (g.tp > 1 && g.tp / 2 >= planes && g.tx * g.ty * (g.tp / 2) >= 32) g.tp /= 2;
   const int span_x = (g.tw - 1) * down + kF, span_y = (g.th - 1) * down + kF;
@@ -1112,7 +1120,7 @@ int launch_tile_epi(const UpfirdnArgs& a, TileGeom g, int dtype, cudaStream_t st
   if (!g.use_tma && e == 4 && g.iwp > 160) { set_error("upfirdn2d: staged pitch %d exceeds the cp.async path", g.iwp); return VCN_ERR_UNSUPPORTED; }
   const size_t buf_bytes = ((size_t)g.tp * g.ih * g.iwp * e + 127) & ~(size_t)127;
   const size_t smem = 2 * buf_bytes + kF * kF * sizeof(float) + 16;
-  const bool reg_ok = kCanReg && !g.use_tma && g.tp == 1 && g.tx * g.ty <= 256 && g.tx * g.ty >= 192;
+  const bool reg_ok = kCanReg && !g.use_tma && g.tp == 1 && g.tx * g.ty <= 256 && (g.tx * g.ty >= 192 || DOWN == 2);
   const int reg_path = !reg_ok ? 0 : (g.ih <= 40 && g.iwp <= 160) ? 1 : (g.ih <= 72 && g.iwp <= 96) ? 2 : 0;
   const int64_t tiles = (int64_t)g.tiles_x * g.tiles_y * g.tiles_p;
   if (tiles > 0x7fffffffLL) { set_error("upfirdn2d: too many tiles"); return VCN_ERR_INVALID; }
