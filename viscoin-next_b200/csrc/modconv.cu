@@ -165,11 +165,25 @@ template <bool PAIR>
 __device__ __forceinline__ TileCoord decode_tile(const IgemmArgs& a, int tile, int rank) {
   // m-tiles fastest: consecutive CTAs share the weight tile (L2 reuse of B), then phases, then out-channel tiles.
   // pair mode: `tile` indexes pair tiles (two half tiles along pair_dim); this CTA owns half `rank`.
-  int mt = tile % a.tiles_m;
-  int r = tile / a.tiles_m;
+  int mt, r;
   TileCoord t;
-  t.phase = r % a.num_phases;
-  t.co0 = (r / a.num_phases) * a.n_tile;
+  if (a.num_phases > 1) {
+    // transposed conv: the 4 output phases of one pixel tile run on neighbouring CTAs at the same time - they read the same
+    // input tile (one DRAM fetch instead of up to four) and interleave their writes into the same output rows (a phase
+    // writes every other pixel: apart in time, every 32-byte sector of an fp32 / NCHW output was read-modify-written -
+    // ncu: 685 MB written + 807 MB read for 270 MB of output).  The phase is rotated by the group index: with a static
+    // walk tile = cta + k * grid and grid % 4 == 0 a CTA would otherwise keep the 4-tap (or the 1-tap) phase for good.
+    const int per_co = a.tiles_m * a.num_phases;
+    const int rem = tile % per_co;
+    mt = rem / a.num_phases;
+    t.phase = (rem % a.num_phases + mt) % a.num_phases;
+    t.co0 = (tile / per_co) * a.n_tile;
+  } else {
+    mt = tile % a.tiles_m;
+    r = tile / a.tiles_m;
+    t.phase = 0;
+    t.co0 = r * a.n_tile;
+  }
   const int wi = mt % a.tiles_w; mt /= a.tiles_w;
   const int hi = mt % a.tiles_h;
   const int ni = mt / a.tiles_h;
