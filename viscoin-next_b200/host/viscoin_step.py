@@ -111,6 +111,7 @@ class VisCoINTrainer:
         # Psi (trainable) may run at a different precision than the frozen f / VGG-16: "same" = follow `amp`
         self.amp_psi = self.amp if amp_psi == "same" else (amp_psi if self.device.type == "cuda" else None)
         self._resident_override = resident_bf16
+        self.psi_fast = os.environ.get("VCN_PSI_FAST", "1") == "1" and self.device.type == "cuda"
         self.channels_last = channels_last and self.device.type == "cuda"
         torch.manual_seed(seed)
         if models is None:
@@ -182,7 +183,16 @@ class VisCoINTrainer:
             # 4 / 8 / 16 CTAs costs more (17.7 / 15.8 / 15.5 ms) than the contention it removes (15.4 ms unpartitioned) - off.
             from .. import _lib
             _lib.check(_lib.load().vcn_set_conv_sm_reserve(int(os.environ["VCN_DP_RESERVE_SMS"])), "vcn_set_conv_sm_reserve")
-        self.buckets = _dp.GradBuckets(main_params + gan_params, bucket_bytes=int(os.environ.get("VCN_DP_BUCKET_MB", "32")) << 20)
+        # with peers, the big weights of Psi (psi_fast: bf16 gradients, deposit-only) are exchanged in bf16 - half the bytes of
+        # the all-reduce tail (dp.GradBuckets)
+        low = []
+        if (self.psi_fast and self.amp_psi == torch.bfloat16 and os.environ.get("VCN_DP_BF16_COMM", "1") == "1"
+                and all(hasattr(self.concept_extractor, k) for k in ("conv1", "conv2", "conv3", "conv4", "linear1", "linear2"))):
+            ce = self.concept_extractor
+            low = [ce.conv1.weight, ce.conv2.weight, ce.conv3.weight, ce.conv4.weight, ce.linear1.weight, ce.linear2.weight]
+        self.buckets = _dp.GradBuckets(main_params + gan_params, bucket_bytes=int(os.environ.get("VCN_DP_BUCKET_MB", "32")) << 20,
+                                       bf16_comm=low)
+        self._psi_low = any(c is not None for c in self.buckets.comm)
         fused = (self.device.type == "cuda") if fused_adam is None else fused_adam
         # capturable: step counters and lr live on the device, so the update can sit inside a CUDA graph (step_graphed)
         cap = fused and self.device.type == "cuda"
@@ -190,7 +200,6 @@ class VisCoINTrainer:
         self.gan_optimizer = torch.optim.Adam(gan_params, lr=lr, fused=fused, capturable=cap)
         self.optimizer = torch.optim.Adam(main_params, lr=lr, fused=fused, capturable=cap)
         self._graphs = {}
-        self.psi_fast = os.environ.get("VCN_PSI_FAST", "1") == "1" and self.device.type == "cuda"
         self.lpips_side_stream = os.environ.get("VCN_LPIPS_SIDE_STREAM", "0") == "1" and self.device.type == "cuda"
         self._lpips_stream = None
         self._z_ahead = {}  # per graph key: the z already drawn for the next iteration (step_graphed's generator pipelining)
@@ -260,6 +269,8 @@ class VisCoINTrainer:
             # explicit bf16 path: one-pass weight shadows, gradients deposited straight into the flat buckets (psi_fast.py)
             encoded_concepts, extra_info = _psi_fast.forward(self.concept_extractor, hidden[-3:], self.buckets)
         else:
+            if getattr(self, "_psi_low", False) and torch.is_grad_enabled():
+                raise RuntimeError("Psi's bf16 communication buckets need the psi_fast path (set VCN_DP_BF16_COMM=0 to train Psi under autocast)")
             with torch.autocast("cuda", dtype=self.amp_psi or torch.bfloat16, enabled=self.amp_psi is not None):
                 if self.amp_psi is None and self.amp is not None:
                     hidden = [h.float() for h in hidden[-3:]]
