@@ -429,3 +429,57 @@ def test_conv2d_resample_grouped_per_sample(g, cin, cout, res, k, up, flip_weigh
     e = (_rel(y, y_ref), _rel(dx, dx_ref), _rel(dw, dw_ref))
     print("grouped", (g, cin, cout, res, k, up), "y/dx/dw", e)
     assert e[0] <= TOL_FWD and e[1] <= TOL_GRAD and e[2] <= TOL_GRAD, e
+
+
+def test_torgb_fused_backward_matches_gemm_path():
+    """vcn_torgb_bwd_fused (one streaming pass) against the GEMM + finish path it replaces, on the resident bf16 ToRGB layer of
+    the 128^2 block: dx and dstyles agree to bf16 rounding (the fused pass keeps W in fp32 and does not round dxhat to bf16,
+    so it is the more accurate of the two: both are gated against an fp32 torch formulation)."""
+    import viscoin_next_b200 as V
+    M = V.modconv
+    g = torch.Generator(device="cuda").manual_seed(21)
+    n, c, r = 4, 256, 64
+    x = torch.randn(n, c, r, r, device="cuda", generator=g).bfloat16().contiguous(memory_format=torch.channels_last)
+    w = torch.randn(3, c, 1, 1, device="cuda", generator=g) / c ** 0.5
+    b = torch.randn(3, device="cuda", generator=g)
+    s0 = torch.randn(n, c, device="cuda", generator=g) + 1
+    gy = torch.randn(n, 3, r, r, device="cuda", generator=g)
+    outs = {}
+    for fused in (True, False):
+        M.torgb_fused = fused
+        try:
+            xi, si = x.clone().requires_grad_(True), s0.clone().requires_grad_(True)
+            y = M.modconv_layer(xi, w, si, bias=b, demodulate=False, act="linear", clamp=256.0)
+            y.backward(gy.to(y.dtype))
+            outs[fused] = (y.detach().float(), xi.grad.float(), si.grad.float())
+        finally:
+            M.torgb_fused = True
+    xr, sr = x.float().requires_grad_(True), s0.clone().requires_grad_(True)
+    yr = torch.clamp(torch.nn.functional.conv2d(xr * sr.view(n, c, 1, 1), w, b), -256, 256)
+    yr.backward(gy)
+    rel = lambda a, ref: float((a - ref).norm() / ref.norm())
+    assert torch.equal(outs[True][0], outs[False][0])
+    for k, (name, ref) in enumerate((("y", yr.detach()), ("dx", xr.grad), ("dstyles", sr.grad))):
+        e_f, e_g = rel(outs[True][k], ref), rel(outs[False][k], ref)
+        print("%-8s fused %.2e  gemm %.2e" % (name, e_f, e_g))
+        assert e_f <= 1e-2 and e_g <= 1.5e-2, (name, e_f, e_g)
+
+
+def test_conv_sm_reserve_does_not_change_results():
+    """vcn_set_conv_sm_reserve only shrinks the persistent grid: the tiles are the same."""
+    import viscoin_next_b200 as V
+    from viscoin_next_b200 import _lib
+    M = V.modconv
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(4, 256, 32, 32, device="cuda", generator=g).bfloat16().contiguous(memory_format=torch.channels_last)
+    w = torch.randn(256, 256, 3, 3, device="cuda", generator=g)
+    s = torch.randn(4, 256, device="cuda", generator=g) + 1
+    lib = _lib.load()
+    y0 = M.modconv_layer(x, w, s)
+    try:
+        _lib.check(lib.vcn_set_conv_sm_reserve(20), "vcn_set_conv_sm_reserve")
+        y1 = M.modconv_layer(x, w, s)
+    finally:
+        _lib.check(lib.vcn_set_conv_sm_reserve(0), "vcn_set_conv_sm_reserve")
+    assert torch.equal(y0, y1)
+    assert lib.vcn_set_conv_sm_reserve(1000) != 0
