@@ -24,6 +24,7 @@ the plain fp32 modules (tests/test_gpu_frozen.py).
 
 import ctypes
 import os
+import weakref
 
 import torch
 import torch.nn.functional as F
@@ -45,7 +46,9 @@ class _WeightCache:
     def get(self, p, dtype=torch.bfloat16):
         key = id(p)
         hit = self._c.get(key)
-        if hit is not None and hit[0] == (p._version, p.data_ptr(), dtype):
+        # the entry holds a weak reference to ITS parameter: a recycled id (+ recycled storage address, same version) of a dead
+        # parameter must not serve another network's weights
+        if hit is not None and hit[2]() is p and hit[0] == (p._version, p.data_ptr(), dtype):
             return hit[1]
         if p.is_cuda and torch.cuda.is_current_stream_capturing():
             raise _lib.VcnError("frozen_nets: weight cache miss inside a CUDA graph capture (run one eager step first)")
@@ -53,7 +56,10 @@ class _WeightCache:
             q = p.detach().to(dtype)
             if q.ndim == 4:
                 q = _cl(q)
-        self._c[key] = ((p._version, p.data_ptr(), dtype), q)
+        if len(self._c) > 1024:
+            for k in [k for k, v in self._c.items() if v[2]() is None]:
+                del self._c[k]
+        self._c[key] = ((p._version, p.data_ptr(), dtype), q, weakref.ref(p))
         return q
 
 
@@ -66,6 +72,7 @@ _weights = _WeightCache()
 first_layer_impl = os.environ.get("VCN_VGG_FIRST", "direct")
 _first_packs = {}
 fused_image_ops = os.environ.get("VCN_FUSED_IMAGE_OPS", "1") == "1"
+resnet_fork = os.environ.get("VCN_RESNET_FORK", "1") == "1"
 
 
 def conv_first3(x, w, b, ks, stride, pad, relu=True):
@@ -231,21 +238,31 @@ class _ConvReLU(torch.autograd.Function):
     """One frozen convolution + bias + [residual] + [ReLU]; backward = ReLU mask (this package's kernel) + library dgrad."""
 
     @staticmethod
-    def forward(ctx, x, w, b, residual, stride, padding, relu):
+    def forward(ctx, x, w, b, residual, stride, padding, relu, fork=False):
         y = _conv_fwd(x, w, b, stride, padding, relu=relu, residual=residual)
-        ctx.cfg = (stride, padding, relu, residual is not None)
+        ctx.cfg = (stride, padding, relu, residual is not None, fork)
         ctx.save_for_backward(x, w, y if relu else None)
+        if fork:
+            # two handles on the same activation (the next bottleneck reads it as convolution input AND as residual): their
+            # gradients come back separately and are summed inside the ReLU-mask pass instead of by a torch add kernel
+            return y, y.view_as(y)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dy2=None):
         x, w, y = ctx.saved_tensors
-        stride, padding, relu, has_res = ctx.cfg
-        dy = _cl(dy) if dy.dtype == x.dtype else _cl(dy.to(x.dtype))
-        dz = relu_mask_bwd(y, dy) if relu else dy
+        stride, padding, relu, has_res, fork = ctx.cfg
+        prep = lambda t: None if t is None else (_cl(t) if t.dtype == x.dtype else _cl(t.to(x.dtype)))
+        dy, dy2 = prep(dy), prep(dy2)
+        if dy is None:
+            dy, dy2 = dy2, None
+        if relu:
+            dz = relu_mask_bwd(y, dy, dy2)
+        else:
+            dz = dy if dy2 is None else dy + dy2
         dx = _conv_dgrad(dz, x.shape, x, w, stride, padding) if ctx.needs_input_grad[0] else None
         dres = dz if (has_res and ctx.needs_input_grad[3]) else None
-        return dx, None, None, dres, None, None, None
+        return dx, None, None, dres, None, None, None, None
 
 
 _bias_sums = {}
@@ -265,15 +282,17 @@ def _summed_bias(p, q):
     return hit[1]
 
 
-def conv_relu(x, conv, relu=True, residual=None, no_bias=False, add_bias_of=None):
+def conv_relu(x, conv, relu=True, residual=None, no_bias=False, add_bias_of=None, fork=False):
     """`conv`: a frozen torch.nn.Conv2d with bias (BatchNorm already folded).  Differentiable w.r.t. x / residual only.
-    no_bias: leave the bias out (it is added by the consumer); add_bias_of: another frozen conv whose bias is added too."""
+    no_bias: leave the bias out (it is added by the consumer); add_bias_of: another frozen conv whose bias is added too;
+    fork: return the output twice (see _ConvReLU.forward)."""
     w = _weights.get(conv.weight)
     b = None if no_bias else (_weights.get(conv.bias) if add_bias_of is None else _summed_bias(conv.bias, add_bias_of.bias))
     stride, padding = tuple(conv.stride), tuple(conv.padding)
     if torch.is_grad_enabled() and (x.requires_grad or (residual is not None and residual.requires_grad)):
-        return _ConvReLU.apply(x, w, b, residual, stride, padding, relu)
-    return _conv_fwd(x, w, b, stride, padding, relu=relu, residual=residual)
+        return _ConvReLU.apply(x, w, b, residual, stride, padding, relu, fork)
+    y = _conv_fwd(x, w, b, stride, padding, relu=relu, residual=residual)
+    return (y, y) if fork else y
 
 
 # ---- ResNet-50 (HF ResNetModel after fold_batchnorm) ------------------------------------------------------------------------
@@ -290,7 +309,10 @@ class FusedResNet:
         if not (isinstance(emb.normalization, torch.nn.Identity) and emb.convolution.bias is not None):
             raise _lib.VcnError("FusedResNet needs a BatchNorm-folded classifier (viscoin_models.fold_batchnorm)")
 
-    def _bottleneck(self, layer, x):
+    def _bottleneck(self, layer, x, x_res=None, fork=False):
+        """x: the block input as the convolutions read it; x_res: the same activation as the identity shortcut reads it (the
+        second handle of the previous block's forked output); fork: return this block's output twice."""
+        x_res = x if x_res is None else x_res
         convs = list(layer.layer)
         if len(convs) != 3:
             raise _lib.VcnError("FusedResNet: only bottleneck layers are implemented")
@@ -298,11 +320,11 @@ class FusedResNet:
         proj = not isinstance(sc, torch.nn.Identity)
         # projection shortcut: its output only ever meets the third convolution's fused (+ residual, + bias, ReLU) epilogue,
         # so its bias rides along there (b3 + b_sc, summed once in fp32) instead of costing a separate bias-add pass per call
-        res = conv_relu(x, sc.convolution, relu=False, no_bias=True) if proj else x
+        res = conv_relu(x_res, sc.convolution, relu=False, no_bias=True) if proj else x_res
         h = conv_relu(x, convs[0].convolution)
         h = conv_relu(h, convs[1].convolution)
         return conv_relu(h, convs[2].convolution, relu=True, residual=res,  # += residual, then the block's ReLU
-                         add_bias_of=sc.convolution if proj else None)
+                         add_bias_of=sc.convolution if proj else None, fork=fork)
 
     def __call__(self, images):
         r = self.m.resnet
@@ -318,10 +340,17 @@ class FusedResNet:
         else:
             x = pool(x)
         hidden = []
-        for stage in r.encoder.stages:
-            hidden.append(x)
-            for layer in stage.layers:
-                x = self._bottleneck(layer, x)
+        # every bottleneck output but the last is read twice by the next block (convolution input + shortcut): forked outputs
+        # let the two gradients meet inside the ReLU-mask kernel (frozen_ops.cu, HAS2) instead of a torch add pass each
+        layers = [(si, layer) for si, stage in enumerate(r.encoder.stages) for layer in stage.layers]
+        x_res, last_stage = None, -1
+        for k, (si, layer) in enumerate(layers):
+            if si != last_stage:
+                hidden.append(x)
+                last_stage = si
+            fork = resnet_fork and k + 1 < len(layers) and x.requires_grad
+            out = self._bottleneck(layer, x, x_res, fork=fork)
+            x, x_res = out if fork else (out, None)
         hidden.append(x)
         pooled = x.float().mean(dim=[2, 3])
         lin = self.m.linear
