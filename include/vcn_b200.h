@@ -209,9 +209,11 @@ int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, const int64
 /* Fused backward of a ToRGB layer (networks.py:307-323: 1x1 modulated convolution to cout <= 4 channels, no demodulation) in
  * the resident bf16 channels-last pipeline: dxhat[n,p,c] = sum_o wgt[o,c] * dy0[n,p,o] (dy0 = the [n,h,w,8] operand rows of
  * vcn_modconv_bwd_pack), dx = dxhat * styles[n,c], dsum[n,c] += sum_p dxhat * x - one pass instead of vcn_conv_igemm +
- * vcn_modconv_bwd_finish_cl.  x, dx: dense bf16 [n,h,w,c], c a power of two >= 64; wgt fp32 [cout,c]; dsum may be NULL. */
-int vcn_torgb_bwd_fused(const void* x, const void* dy0, const float* wgt, const float* styles, void* dx, float* dsum,
-                        int dtype, int n, int c, int h, int w, int cout, void* stream);
+ * vcn_modconv_bwd_finish_cl.  x, dx: dense bf16 [n,h,w,c], c a power of two >= 64; wgt fp32 [cout,c]; dsum may be NULL;
+ * acc (may be NULL): a second gradient of the same activation, dense bf16 [n,h,w,c], added to dx in the same pass (the skip
+ * architecture reads x twice, networks.py:411-423). */
+int vcn_torgb_bwd_fused(const void* x, const void* dy0, const float* wgt, const float* styles, const void* acc, void* dx,
+                        float* dsum, int dtype, int n, int c, int h, int w, int cout, void* stream);
 int vcn_conv_wgrad(const void* dy0, const void* xhat, float* dw, int kind, int n, int h, int w, int cin_pad, int cin,
                    int cout_pad, int cout, int kh, int kw, int dy_h, int dy_w, void* stream);
 int vcn_demod_grad(float* ds, const float* styles, const float* gsum, const float* dcoef, const float* wsq,

@@ -483,3 +483,35 @@ def test_conv_sm_reserve_does_not_change_results():
         _lib.check(lib.vcn_set_conv_sm_reserve(0), "vcn_set_conv_sm_reserve")
     assert torch.equal(y0, y1)
     assert lib.vcn_set_conv_sm_reserve(1000) != 0
+
+
+def test_torgb_tap_folds_the_second_gradient():
+    """modconv_layer(..., tap=True) returns (rgb, x2): the gradient arriving through x2 is added to the ToRGB input gradient
+    inside the fused backward (vcn_torgb_bwd_fused with `acc`).  Against the same graph without the tap (autograd's own add):
+    equal to one bf16 rounding of the sum."""
+    import viscoin_next_b200 as V
+    M = V.modconv
+    g = torch.Generator(device="cuda").manual_seed(33)
+    n, c, r = 4, 128, 64
+    x0 = torch.randn(n, c, r, r, device="cuda", generator=g).bfloat16().contiguous(memory_format=torch.channels_last)
+    w = torch.randn(3, c, 1, 1, device="cuda", generator=g) / c ** 0.5
+    b = torch.randn(3, device="cuda", generator=g)
+    s0 = torch.randn(n, c, device="cuda", generator=g) + 1
+    gy = torch.randn(n, 3, r, r, device="cuda", generator=g)
+    gx2 = torch.randn(n, c, r, r, device="cuda", generator=g).bfloat16().contiguous(memory_format=torch.channels_last)
+    res = {}
+    for tap in (True, False):
+        x, s = x0.clone().requires_grad_(True), s0.clone().requires_grad_(True)
+        if tap:
+            y, x2 = M.modconv_layer(x, w, s, bias=b, demodulate=False, act="linear", clamp=256.0, tap=True)
+            assert x2.data_ptr() == x.data_ptr()
+        else:
+            y, x2 = M.modconv_layer(x, w, s, bias=b, demodulate=False, act="linear", clamp=256.0), x
+        torch.autograd.backward([y, x2 * 1.0], [gy.to(y.dtype), gx2])
+        res[tap] = (y.detach().float(), x.grad.float(), s.grad.float())
+    assert torch.equal(res[True][0], res[False][0])
+    # the style gradient is a sum of per-CTA partials added with atomics: equal up to the fp32 summation order
+    assert float((res[True][2] - res[False][2]).abs().max() / res[False][2].abs().max()) <= 1e-5
+    e = float((res[True][1] - res[False][1]).abs().max() / res[False][1].abs().max())
+    print("tap vs autograd add: dx rel-Linf %.2e" % e)
+    assert e <= 8e-3  # the reference path rounds the ToRGB gradient to bf16 before the add, the fused pass adds in fp32

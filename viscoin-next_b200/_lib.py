@@ -60,7 +60,7 @@ SIGNATURES = {
                                      _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "vcn_demod_coefs": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "vcn_pack_weights_mod": (_i, [_vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
-    "vcn_torgb_bwd_fused": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
+    "vcn_torgb_bwd_fused": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "vcn_set_conv_sm_reserve": (_i, [_i]),
     "vcn_conv_igemm": (_i, [_vp, _vp, _vp, _c.POINTER(ConvDesc), _c.POINTER(UpfirdnEpilogue), _vp]),
     "vcn_modconv_bwd_pack": (_i, [_vp, _vp, _i, _c.POINTER(_i64 * 4), _c.POINTER(_i64 * 4), _c.POINTER(UpfirdnEpilogue),

@@ -295,15 +295,19 @@ __global__ void __launch_bounds__(256, 3) modconv_bwd_cl_bulk_kernel(const BwdCl
 //   dx[n,p,c]    = dxhat * s[n,c]                  dsum[n,c] = sum_p dxhat * x[n,p,c]
 // One pass over x (read) and dx (write) instead of GEMM (write dxhat) + finish (read dxhat, x; write dx).  Same ring as above:
 // a stage = 2 * rows pixels of x (8 KB) plus their 16-byte dy0 rows.
-template <typename T>
+// ACC: dx = acc + dxhat * s - `acc` is the gradient that reaches the same activation through the next block (the skip
+// architecture reads x twice: ToRGB and the next block's first convolution); folding it in here replaces a torch add pass.
+template <typename T, bool ACC>
 __global__ void __launch_bounds__(256, 3) torgb_bwd_bulk_kernel(const T* __restrict__ x, const __nv_bfloat16* __restrict__ dy0,
                                                                 const float* __restrict__ wgt, const float* __restrict__ styles,
-                                                                T* __restrict__ dx, float* __restrict__ dsum, int n_, int c,
-                                                                int hw, int cout, int chunk) {
-  extern __shared__ __align__(128) unsigned char ring[];  // [kStagesBulk][kStageTensorBytes + 1024]
+                                                                const T* __restrict__ acc_in, T* __restrict__ dx,
+                                                                float* __restrict__ dsum, int n_, int c, int hw, int cout, int chunk) {
+  constexpr int kSt = ACC ? 3 : kStagesBulk;              // three stages with the third stream: 3 CTAs per SM still fit
+  extern __shared__ __align__(128) unsigned char ring[];  // [kSt][(1 + ACC) * kStageTensorBytes + 1024]
   __shared__ float red[256][8];
   __shared__ __align__(8) uint64_t full_bar[kStagesBulk];
-  constexpr uint32_t kStage = kStageTensorBytes + 1024;   // x rows + up to 64 dy0 rows of 16 bytes
+  constexpr uint32_t kAccOff = kStageTensorBytes + 1024;  // x rows + up to 64 dy0 rows of 16 bytes (+ acc rows)
+  constexpr uint32_t kStage = kAccOff + (ACC ? kStageTensorBytes : 0);
   const int tid = threadIdx.x, n = blockIdx.y;
   const int groups = c >> 3, rows = 256 / groups;
   const int g = tid % groups, row = tid / groups;
@@ -314,18 +318,20 @@ __global__ void __launch_bounds__(256, 3) torgb_bwd_bulk_kernel(const T* __restr
   const uint32_t row_bytes = (uint32_t)c * 2u;
   const unsigned char* gx = reinterpret_cast<const unsigned char*>(x) + ((int64_t)n * hw + p0) * row_bytes;
   const unsigned char* gd = reinterpret_cast<const unsigned char*>(dy0) + ((int64_t)n * hw + p0) * 16;
+  const unsigned char* gacc = ACC ? reinterpret_cast<const unsigned char*>(acc_in) + ((int64_t)n * hw + p0) * row_bytes : nullptr;
   auto fill = [&](int it) {
-    const int s = it % kStagesBulk;
+    const int s = it % kSt;
     const int px = min(sp, p_end - p0 - it * sp);
     unsigned char* dst = ring + (size_t)s * kStage;
-    mbar_expect_tx(full_bar + s, (uint32_t)px * (row_bytes + 16u));
+    mbar_expect_tx(full_bar + s, (uint32_t)px * ((ACC ? 2u : 1u) * row_bytes + 16u));
     bulk_load_1d(dst, gx + (int64_t)it * sp * row_bytes, (uint32_t)px * row_bytes, full_bar + s);
     bulk_load_1d(dst + kStageTensorBytes, gd + (int64_t)it * sp * 16, (uint32_t)px * 16u, full_bar + s);
+    if (ACC) bulk_load_1d(dst + kAccOff, gacc + (int64_t)it * sp * row_bytes, (uint32_t)px * row_bytes, full_bar + s);
   };
   if (tid == 0) {
-    for (int s = 0; s < kStagesBulk; ++s) mbar_init(full_bar + s, 1);
+    for (int s = 0; s < kSt; ++s) mbar_init(full_bar + s, 1);
     fence_mbar_init();
-    for (int it = 0; it < min(nit, kStagesBulk); ++it) fill(it);
+    for (int it = 0; it < min(nit, kSt); ++it) fill(it);
   }
   float wv[4][8], sc[8], acc[8];
 #pragma unroll
@@ -337,8 +343,8 @@ __global__ void __launch_bounds__(256, 3) torgb_bwd_bulk_kernel(const T* __restr
   }
   __syncthreads();
   for (int it = 0; it < nit; ++it) {
-    const int s = it % kStagesBulk;
-    mbar_wait(full_bar + s, (uint32_t)(it / kStagesBulk) & 1u);
+    const int s = it % kSt;
+    mbar_wait(full_bar + s, (uint32_t)(it / kSt) & 1u);
     const unsigned char* sa = ring + (size_t)s * kStage;
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
@@ -349,20 +355,21 @@ __global__ void __launch_bounds__(256, 3) torgb_bwd_bulk_kernel(const T* __restr
         const uint2 dv = *reinterpret_cast<const uint2*>(sa + kStageTensorBytes + (size_t)pl * 16);  // channels 0..3 of dy0
         const float d0 = __uint_as_float(dv.x << 16), d1 = __uint_as_float(dv.x & 0xffff0000u);
         const float d2 = __uint_as_float(dv.y << 16), d3 = __uint_as_float(dv.y & 0xffff0000u);
-        Vec16<T> o;
+        Vec16<T> o, av;
+        if (ACC) av = *reinterpret_cast<const Vec16<T>*>(sa + kAccOff + (size_t)pl * row_bytes + g * 16);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float t = fmaf(wv[0][k], d0, fmaf(wv[1][k], d1, fmaf(wv[2][k], d2, wv[3][k] * d3)));
           acc[k] = fmaf(t, to_acc<T>(xv.v[k]), acc[k]);
-          o.v[k] = from_acc<T>(t * sc[k]);
+          o.v[k] = from_acc<T>(ACC ? fmaf(t, sc[k], to_acc<T>(av.v[k])) : t * sc[k]);
         }
         st_stream<T>(dx + ((int64_t)n * hw + p) * c + c0, o);
       }
     }
     __syncthreads();
-    if (tid == 0 && it + kStagesBulk < nit) {
+    if (tid == 0 && it + kSt < nit) {
       fence_proxy_async();
-      fill(it + kStagesBulk);
+      fill(it + kSt);
     }
   }
   if (dsum) group_reduce_add(red, acc, tid, groups, rows, dsum + (int64_t)n * c, c);
@@ -484,8 +491,8 @@ extern "C" int vcn_modconv_bwd_finish_cl(void* dxhat, const void* x, int dtype, 
   return launch<true>(a, dtype, static_cast<cudaStream_t>(stream), "modconv_bwd_finish_cl_kernel");
 }
 
-extern "C" int vcn_torgb_bwd_fused(const void* x, const void* dy0, const float* wgt, const float* styles, void* dx, float* dsum,
-                                   int dtype, int n, int c, int h, int w, int cout, void* stream) {
+extern "C" int vcn_torgb_bwd_fused(const void* x, const void* dy0, const float* wgt, const float* styles, const void* acc,
+                                   void* dx, float* dsum, int dtype, int n, int c, int h, int w, int cout, void* stream) {
   using namespace vcn;
   VCN_REQUIRE(dtype == VCN_BF16, "torgb_bwd_fused: x / dx must be bf16 channels-last");
   VCN_REQUIRE(n >= 0 && h >= 1 && w >= 1 && cout >= 1 && cout <= 4, "torgb_bwd_fused: 1..4 output channels (got %d)", cout);
@@ -502,17 +509,20 @@ extern "C" int vcn_torgb_bwd_fused(const void* x, const void* dy0, const float* 
   chunk = (chunk + sp - 1) / sp * sp;
   if (chunk < 4 * sp) chunk = 4 * sp;
   dim3 grid((unsigned)((hw + chunk - 1) / chunk), (unsigned)n);
-  const size_t smem = (size_t)kStagesBulk * (kStageTensorBytes + 1024);
-  auto kern = torgb_bwd_bulk_kernel<__nv_bfloat16>;
-  static bool attr_set[64] = {};
+  VCN_REQUIRE(!acc || aligned16(acc), "torgb_bwd_fused: acc must be 16-byte aligned");
+  const size_t smem = acc ? (size_t)3 * (2 * kStageTensorBytes + 1024) : (size_t)kStagesBulk * (kStageTensorBytes + 1024);
+  auto kern = acc ? torgb_bwd_bulk_kernel<__nv_bfloat16, true> : torgb_bwd_bulk_kernel<__nv_bfloat16, false>;
+  static bool attr_set[2][64] = {};
   int dev = 0;
   VCN_CUDA(cudaGetDevice(&dev));
-  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+  const int ai = acc ? 1 : 0;
+  if (dev < 0 || dev >= 64 || !attr_set[ai][dev]) {
     VCN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    if (dev >= 0 && dev < 64) attr_set[ai][dev] = true;
   }
   kern<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(dy0),
-                                                               wgt, styles, static_cast<__nv_bfloat16*>(dx), dsum, n, c, hw, cout, chunk);
+                                                               wgt, styles, static_cast<const __nv_bfloat16*>(acc),
+                                                               static_cast<__nv_bfloat16*>(dx), dsum, n, c, hw, cout, chunk);
   VCN_LAUNCH_CHECK("torgb_bwd_bulk_kernel");
   return VCN_OK;
 }

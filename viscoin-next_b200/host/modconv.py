@@ -205,8 +205,9 @@ def bwd_pack(dy, y, epilogue, want_gsum, want_db, out_dtype=torch.bfloat16):
 torgb_fused = os.environ.get("VCN_TORGB_FUSED", "1") == "1"
 
 
-def torgb_bwd_fused(x, dy0, weight, styles, want_dsum):
-    """vcn_torgb_bwd_fused: (dx bf16 channels_last like x, dsum [N,C] or None) from the packed ToRGB gradient rows dy0 [N,H,W,8]."""
+def torgb_bwd_fused(x, dy0, weight, styles, want_dsum, acc=None):
+    """vcn_torgb_bwd_fused: (dx bf16 channels_last like x, dsum [N,C] or None) from the packed ToRGB gradient rows dy0 [N,H,W,8];
+    acc (bf16 channels_last like x, optional) is added to dx in the same pass."""
     lib = _lib.load()
     n, c, h, w = x.shape
     cout = weight.shape[0]
@@ -215,7 +216,9 @@ def torgb_bwd_fused(x, dy0, weight, styles, want_dsum):
     dsum = torch.zeros([n, c], dtype=torch.float32, device=x.device) if want_dsum else None
     assert dy0.dtype == torch.bfloat16 and tuple(dy0.shape) == (n, h, w, 8) and dy0.is_contiguous()
     with torch.cuda.device(x.device):
-        st = lib.vcn_torgb_bwd_fused(_lib.ptr(x), _lib.ptr(dy0), _lib.ptr(wgt), _lib.ptr(styles), _lib.ptr(dx), _lib.ptr(dsum),
+        if acc is not None:
+            assert acc.shape == x.shape and acc.dtype == x.dtype and acc.is_contiguous(memory_format=torch.channels_last)
+        st = lib.vcn_torgb_bwd_fused(_lib.ptr(x), _lib.ptr(dy0), _lib.ptr(wgt), _lib.ptr(styles), _lib.ptr(acc), _lib.ptr(dx), _lib.ptr(dsum),
                                      _lib.dtype_code(x.dtype), n, c, h, w, cout, _lib.current_stream(x.device))
     _lib.check(st, "vcn_torgb_bwd_fused")
     return dx, dsum
@@ -319,7 +322,8 @@ class _ModConvLayer(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, styles, noise, bias, resample_filter, cfg):
-        up, demodulate, flip_weight, act, alpha, gain, clamp = cfg
+        up, demodulate, flip_weight, act, alpha, gain, clamp = cfg[:7]
+        tap = len(cfg) > 7 and bool(cfg[7])  # also return x (pass-through handle): its gradient is folded into this backward
         _lib.require_device(x.device.index)
         n, cin, h, w = x.shape
         cout, cin_w, kh, kw = weight.shape
@@ -360,12 +364,16 @@ class _ModConvLayer(torch.autograd.Function):
         ctx.has = (styles is not None, noise is not None, bias is not None)
         ctx.save_for_backward(x, weight, styles32, noise, bias, resample_filter, d, wsq, y)
         del hold
+        if tap:
+            return y, x.view_as(x)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dx_pass=None):
         x, weight, styles32, noise, bias, resample_filter, d, wsq, y = ctx.saved_tensors
-        up, demodulate, flip_weight, act, alpha, gain, clamp = ctx.cfg
+        up, demodulate, flip_weight, act, alpha, gain, clamp = ctx.cfg[:7]
+        if dy is None:  # only the pass-through handle was used downstream
+            return dx_pass, None, None, None, None, None, None
         need_x, need_w, need_s, need_noise, need_b = ctx.needs_input_grad[:5]
         n, cin, h, w = x.shape
         cout, _, kh, kw = weight.shape
@@ -394,7 +402,11 @@ class _ModConvLayer(torch.autograd.Function):
                      and n * h * w * cin >= (1 << 21))
         if fused_rgb and (need_x or need_s):
             # ToRGB: the input-gradient GEMM is a rank-<=4 expansion - one streaming pass (vcn_torgb_bwd_fused)
-            dx, ds = torgb_bwd_fused(x, dy0, weight, styles32, need_s and styles32 is not None)
+            acc = None
+            if dx_pass is not None and need_x:
+                acc = dx_pass.to(x.dtype).contiguous(memory_format=torch.channels_last)
+                dx_pass = None
+            dx, ds = torgb_bwd_fused(x, dy0, weight, styles32, need_s and styles32 is not None, acc=acc)
             if not need_x:
                 dx = None
         elif need_x or need_s:
@@ -448,6 +460,8 @@ class _ModConvLayer(torch.autograd.Function):
             dnoise = dnoise.sum_to_size(noise.shape) if noise.ndim == 4 else dnoise.sum(dim=[0, 1]).sum_to_size(noise.shape)
             dnoise = dnoise.to(noise.dtype)
         del hold
+        if dx_pass is not None and need_x:  # pass-through gradient on a path without the fused kernel
+            dx = dx_pass.to(dx.dtype) + dx if dx is not None else dx_pass
         return dx, dw, ds, dnoise, (db.to(bias.dtype) if db is not None else None), None, None
 
 
@@ -458,7 +472,7 @@ def _check_cuda(x, what):
 
 @_profiled
 def modconv_layer(x, weight, styles, noise=None, bias=None, up=1, padding=None, resample_filter=None, demodulate=True,
-                  flip_weight=True, act="lrelu", alpha=None, gain=None, clamp=None):
+                  flip_weight=True, act="lrelu", alpha=None, gain=None, clamp=None, tap=False):
     """Fused SynthesisLayer / ToRGBLayer body: bias_act(modulated_conv2d(...), bias, act, gain, clamp)
     (networks.py:299-304, 322-323) in one GEMM epilogue.  Activations other than linear / lrelu run bias_act
     as a second kernel."""
@@ -471,6 +485,12 @@ def modconv_layer(x, weight, styles, noise=None, bias=None, up=1, padding=None, 
     if styles is None:
         demodulate = False
         cfg = (up, False, bool(flip_weight), cfg[3], alpha, gain, clamp)
+    if tap:
+        # `tap`: returns (y, x2) where x2 is a second handle on x - the caller hands x2 to whatever else consumes x, and the sum
+        # of the two gradients of x is formed inside this layer's backward (ToRGB: inside vcn_torgb_bwd_fused) instead of by a
+        # separate add pass over the full activation
+        assert fuse, "tap needs a fusable activation"
+        return _ModConvLayer.apply(x, weight, styles, noise, bias, resample_filter, cfg + (True,))
     y = _ModConvLayer.apply(x, weight, styles, noise, bias if fuse else None, resample_filter, cfg)
     if not fuse:
         y = _bias_act.bias_act(y, bias.to(y.dtype) if bias is not None else None, act=act, alpha=alpha, gain=gain, clamp=clamp)

@@ -14,6 +14,7 @@ convolution operands are bf16 on the tensor cores (tolerances in 
 """
 
 import math
+import os
 
 import numpy as np
 import torch
@@ -27,6 +28,9 @@ from . import upfirdn2d as _upfirdn2d
 @_profiled
 def normalize_2nd_moment(x, dim=1, eps=1e-8):
     return x * (x.square().mean(dim=dim, keepdim=True) + eps).rsqrt()
+
+
+rgb_tap = os.environ.get("VCN_RGB_TAP", "1") == "1"
 
 
 class FullyConnectedLayer(torch.nn.Module):
@@ -121,11 +125,12 @@ class ToRGBLayer(torch.nn.Module):
         self.bias = torch.nn.Parameter(torch.zeros([out_channels]))
         self.weight_gain = 1 / math.sqrt(in_channels * (kernel_size ** 2))
 
-    def forward(self, x, w, fused_modconv=True, styles=None):
+    def forward(self, x, w, fused_modconv=True, styles=None, tap=False):
+        """tap=True: returns (rgb, x2) with x2 a second handle on x for the next block (modconv.modconv_layer)."""
         if styles is None:
             styles = self.affine(w) * self.weight_gain
         return _modconv.modconv_layer(x, self.weight, styles, bias=self.bias, demodulate=False, act="linear",
-                                      clamp=self.conv_clamp)
+                                      clamp=self.conv_clamp, tap=tap)
 
     def forward_nhwc(self, act, w, styles=None):
         """bf16 NHWC activation -> fp32 NCHW RGB: per-sample 1x1 weights, no pass over the activation besides the GEMM."""
@@ -236,7 +241,15 @@ class SynthesisBlock(torch.nn.Module):
         if img is not None:
             img = _upfirdn2d.upsample2d(img, self.resample_filter)
         if self.is_last or self.architecture == "skip":
-            y = self.torgb(x, next(w_iter), styles=st.get(self.torgb)).to(torch.float32)
+            # training on the resident pipeline: x is read by ToRGB and by the next block - the ToRGB layer hands back a second
+            # handle on x so that both gradients meet inside its fused backward (one pass instead of two + a torch add)
+            tap = (rgb_tap and resident and not self.is_last and torch.is_grad_enabled() and x.requires_grad
+                   and x.dtype == torch.bfloat16 and _modconv.torgb_fused)
+            if tap:
+                y, x = self.torgb(x, next(w_iter), styles=st.get(self.torgb), tap=True)
+                y = y.to(torch.float32)
+            else:
+                y = self.torgb(x, next(w_iter), styles=st.get(self.torgb)).to(torch.float32)
             img = img.add_(y) if img is not None else y
         return x, img
 
